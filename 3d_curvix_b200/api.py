@@ -1,0 +1,268 @@
+"""ctypes binding of libcurvix_b200.so (the C-ABI in include/curvix_b200.h).
+
+There is no CPU path: if the CUDA library is missing or no device is present this module raises.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libcurvix_b200.so")
+
+# every symbol include/curvix_b200.h declares
+SYMBOLS = [
+    "cvx_default_config", "cvx_create", "cvx_destroy", "cvx_last_error", "cvx_set_cameras", "cvx_set_view_edges",
+    "cvx_set_hypothesis_pair", "cvx_run_edge_sketch", "cvx_get_counts", "cvx_get_h2_angles", "cvx_get_h1_wedges",
+    "cvx_get_h1_table", "cvx_get_rows", "cvx_get_support_matrix", "cvx_get_intermediates", "cvx_get_valid_rows",
+    "cvx_get_pairs", "cvx_get_reference_order", "cvx_finalize", "cvx_get_device_results", "cvx_get_timings", "cvx_synchronize",
+    "cvx_support_problem_create", "cvx_support_problem_run", "cvx_support_problem_result", "cvx_support_problem_destroy",
+]
+
+
+class CvxConfig(C.Structure):
+    _fields_ = [
+        ("delta", C.c_double), ("delta_theta_deg", C.c_double), ("parallel_angle_deg", C.c_double),
+        ("lowes_ratio", C.c_double), ("epip_tangency_displ_thresh", C.c_double),
+        ("location_perturbation", C.c_double), ("orient_perturbation", C.c_double),
+        ("cluster_dist_thresh", C.c_double), ("cluster_orient_thresh_deg", C.c_double),
+        ("cluster_gauss_sigma", C.c_double), ("pi_truncated", C.c_double),
+        ("n_views", C.c_int32), ("img_rows", C.c_int32), ("img_cols", C.c_int32),
+        ("max_support_views", C.c_int32), ("max_cluster_size", C.c_int32), ("reserved", C.c_int32),
+    ]
+
+
+class CvxCounts(C.Structure):
+    _fields_ = [(n, C.c_int64) for n in (
+        "n_h1_total", "n_h1_processed", "n_candidates", "n_hypotheses", "n_validations", "n_valid_rows",
+        "n_pairs", "n_degenerate_wedges", "n_supported", "n_parallel")]
+
+    def as_dict(self):
+        return {n: int(getattr(self, n)) for n, _ in self._fields_}
+
+
+class CvxTimings(C.Structure):
+    _fields_ = [("set_pair_ms", C.c_float), ("run_ms", C.c_float), ("finalize_ms", C.c_float), ("form_ms", C.c_float),
+                ("reproject_ms", C.c_float), ("support_ms", C.c_float), ("select_ms", C.c_float),
+                ("kernel_launches", C.c_int32), ("pad", C.c_int32)]
+
+    def as_dict(self):
+        return {n: getattr(self, n) for n, _ in self._fields_ if n != "pad"}
+
+
+class CvxDeviceResults(C.Structure):
+    _fields_ = [("n_pairs", C.c_int64), ("n_vali_views", C.c_int32), ("pad", C.c_int32),
+                ("pair_h1", C.c_void_p), ("pair_h2rep", C.c_void_p), ("pair_count", C.c_void_p), ("pair_supports", C.c_void_p),
+                ("gamma_cam", C.c_void_p), ("gamma_world", C.c_void_p), ("tangent_world", C.c_void_p)]
+
+
+_lib = None
+
+
+def load():
+    """Load the CUDA library.  Raises (never falls back) when it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(f"{LIB_PATH} is missing: run `python 3d_curvix_b200/build.py` (there is no CPU fallback)")
+    lib = C.CDLL(LIB_PATH)
+    lib.cvx_last_error.restype = C.c_char_p
+    lib.cvx_last_error.argtypes = [C.c_void_p]
+    lib.cvx_create.argtypes = [C.POINTER(CvxConfig), C.c_int, C.POINTER(C.c_void_p)]
+    lib.cvx_support_problem_create.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p] + [C.c_void_p] * 7 + \
+        [C.c_double, C.c_double, C.POINTER(C.c_void_p)]
+    _lib = lib
+    return lib
+
+
+def default_config(**kw):
+    cfg = CvxConfig()
+    load().cvx_default_config(C.byref(cfg))
+    for k, v in kw.items():
+        setattr(cfg, k, v)
+    return cfg
+
+
+def _vp(a):
+    return None if a is None else C.c_void_p(a.ctypes.data)
+
+
+class CurvixError(RuntimeError):
+    pass
+
+
+class EdgeSketch:
+    """One context on one GPU.  Call order mirrors EdgeSketch_Core as driven by cmd/main.cpp:114-155:
+    set_cameras -> set_view_edges (all views) -> per pass: set_pair -> run -> getters / finalize."""
+
+    def __init__(self, cfg, device=0):
+        self.lib = load()
+        self.cfg = cfg
+        self.h = C.c_void_p()
+        rc = self.lib.cvx_create(C.byref(cfg), device, C.byref(self.h))
+        if rc != 0:
+            raise CurvixError(f"cvx_create failed with status {rc} (no CUDA device? there is no CPU fallback)")
+        self.V = cfg.n_views - 2
+        self.n_edges = [0] * cfg.n_views
+        self._keep = []
+
+    def _ck(self, rc):
+        if rc != 0:
+            raise CurvixError(f"status {rc}: {self.lib.cvx_last_error(self.h).decode()}")
+
+    def close(self):
+        if self.h:
+            self.lib.cvx_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_cameras(self, R, T, K):
+        R = np.ascontiguousarray(R, np.float64).reshape(-1, 9)
+        T = np.ascontiguousarray(T, np.float64).reshape(-1, 3)
+        K = np.ascontiguousarray(K, np.float64)
+        per_view = 1 if (K.size == 9 * R.shape[0] and R.shape[0] > 1) else 0
+        self._ck(self.lib.cvx_set_cameras(self.h, R.shape[0], _vp(R), _vp(T), _vp(K), per_view))
+
+    def set_view_edges(self, v, edges):
+        e = np.asarray(edges, np.float64)
+        cols = [np.ascontiguousarray(e[:, k]) for k in range(3)]
+        self.set_view_edges_soa(v, *cols)
+
+    def set_view_edges_soa(self, v, x, y, th):
+        """x, y, th: contiguous float64 arrays (numpy) or raw host pointers with explicit n via (ptr, n) tuples."""
+        n = len(x)
+        self._ck(self.lib.cvx_set_view_edges(self.h, v, n, _vp(x), _vp(y), _vp(th), None))
+        self.n_edges[v] = n
+
+    def set_view_edges_ptr(self, v, n, px, py, pth):
+        self._ck(self.lib.cvx_set_view_edges(self.h, v, n, C.c_void_p(px), C.c_void_p(py), C.c_void_p(pth), None))
+        self.n_edges[v] = n
+
+    def set_pair(self, h1, h2):
+        self._ck(self.lib.cvx_set_hypothesis_pair(self.h, h1, h2))
+        self.h1, self.h2 = h1, h2
+
+    def run(self, h1_begin=0, h1_end=-1):
+        self._ck(self.lib.cvx_run_edge_sketch(self.h, h1_begin, h1_end))
+        return self
+
+    def counts(self):
+        c = CvxCounts()
+        self._ck(self.lib.cvx_get_counts(self.h, C.byref(c)))
+        return c.as_dict()
+
+    def timings(self):
+        t = CvxTimings()
+        self._ck(self.lib.cvx_get_timings(self.h, C.byref(t)))
+        return t.as_dict()
+
+    def synchronize(self):
+        self._ck(self.lib.cvx_synchronize(self.h))
+
+    def h2_angles(self):
+        out = np.empty(self.n_edges[self.h2])
+        self._ck(self.lib.cvx_get_h2_angles(self.h, _vp(out)))
+        return out
+
+    def h1_wedges(self):
+        E = self.n_edges[self.h1]
+        w = np.empty((E, 2)); f = np.empty(E, np.int32)
+        self._ck(self.lib.cvx_get_h1_wedges(self.h, _vp(w), _vp(f)))
+        return w, f
+
+    def h1_table(self):
+        E = self.n_edges[self.h1]
+        m = np.empty(E, np.int32); n = np.empty(E, np.int32); off = np.empty(E, np.int64)
+        self._ck(self.lib.cvx_get_h1_table(self.h, _vp(m), _vp(n), _vp(off)))
+        return dict(m=m, n=n, off=off)
+
+    def rows(self):
+        H = self.counts()["n_hypotheses"]
+        ints = {k: np.empty(H, np.int32) for k in ("h1", "h2_orig", "local_idx", "raw_at_local", "label", "h2_rep", "count")}
+        dbl = {k: np.empty(H) for k in ("xc", "yc", "theta_orig", "xbar", "ybar", "thbar")}
+        self._ck(self.lib.cvx_get_rows(self.h, _vp(ints["h1"]), _vp(ints["h2_orig"]), _vp(ints["local_idx"]), _vp(ints["raw_at_local"]),
+                                       _vp(dbl["xc"]), _vp(dbl["yc"]), _vp(dbl["theta_orig"]), _vp(dbl["xbar"]), _vp(dbl["ybar"]),
+                                       _vp(dbl["thbar"]), _vp(ints["label"]), _vp(ints["h2_rep"]), _vp(ints["count"])))
+        ints.update(dbl)
+        return ints
+
+    def support_matrix(self):
+        H = self.counts()["n_hypotheses"]
+        out = np.empty((H, self.V), np.int32)
+        self._ck(self.lib.cvx_get_support_matrix(self.h, _vp(out)))
+        return out
+
+    def intermediates(self):
+        H = self.counts()["n_hypotheses"]
+        E1 = self.n_edges[self.h1]
+        w31 = np.empty((E1, self.V, 2)); w32 = np.empty((H, self.V, 2)); tgt = np.empty((H, self.V, 2))
+        self._ck(self.lib.cvx_get_intermediates(self.h, _vp(w31), _vp(w32), _vp(tgt)))
+        return dict(wedge31=w31, wedge32=w32, tgt=tgt)
+
+    def valid_rows(self):
+        n = self.counts()["n_valid_rows"]
+        a = {k: np.empty(n, np.int32) for k in ("h1", "row", "count", "selected")}
+        self._ck(self.lib.cvx_get_valid_rows(self.h, _vp(a["h1"]), _vp(a["row"]), _vp(a["count"]), _vp(a["selected"])))
+        return a
+
+    def pairs(self, with_supports=True):
+        P = self.counts()["n_pairs"]
+        a = {k: np.empty(P, np.int32) for k in ("h1", "h2rep", "row", "count")}
+        sup = np.empty((P, self.V), np.int32) if with_supports else None
+        self._ck(self.lib.cvx_get_pairs(self.h, _vp(a["h1"]), _vp(a["h2rep"]), _vp(a["row"]), _vp(a["count"]), _vp(sup)))
+        a["supports"] = sup
+        return a
+
+    def reference_order(self):
+        """Indices into pairs()/finalize() arrays in the reference's paired_edge order (host std::sort step + capacity)."""
+        P = self.counts()["n_pairs"]
+        idx = np.empty(max(P, 1), np.int64); n = C.c_int64()
+        self._ck(self.lib.cvx_get_reference_order(self.h, _vp(idx), C.byref(n)))
+        return idx[:n.value].copy()
+
+    def finalize(self):
+        P = self.counts()["n_pairs"]
+        gc = np.empty((P, 3)); gw = np.empty((P, 3)); tw = np.empty((P, 3)); h2c = np.empty((P, 2)); nf = np.empty(P, np.int32)
+        self._ck(self.lib.cvx_finalize(self.h, _vp(gc), _vp(gw), _vp(tw), _vp(h2c), _vp(nf)))
+        return dict(gamma_cam=gc, gamma_world=gw, tangent_world=tw, h2_corrected=h2c, nan_flag=nf)
+
+    def device_results(self):
+        r = CvxDeviceResults()
+        self._ck(self.lib.cvx_get_device_results(self.h, C.byref(r)))
+        return r
+
+
+class SupportProblem:
+    """Stand-alone support test on pre-formed hypotheses (BASELINE.json config 5)."""
+
+    def __init__(self, sketch, group_off, view_off, ang31, ang32, cs, sn, wedge31, wedge32, tgt, cos_thresh, parallel_deg):
+        self.sk = sketch
+        self.lib = sketch.lib
+        a = [np.ascontiguousarray(group_off, np.int64), np.ascontiguousarray(view_off, np.int64)] + \
+            [np.ascontiguousarray(t, np.float64) for t in (ang31, ang32, cs, sn, wedge31, wedge32, tgt)]
+        self.G = len(a[0]) - 1; self.V = len(a[1]) - 1; self.H = int(a[0][-1])
+        self.p = C.c_void_p()
+        rc = self.lib.cvx_support_problem_create(sketch.h, self.G, _vp(a[0]), self.V, _vp(a[1]), *[_vp(t) for t in a[2:]],
+                                                 float(cos_thresh), float(parallel_deg), C.byref(self.p))
+        sketch._ck(rc)
+
+    def run(self):
+        ms = C.c_float()
+        self.sk._ck(self.lib.cvx_support_problem_run(self.p, C.byref(ms)))
+        return ms.value
+
+    def result(self):
+        out = np.empty((self.V, self.H), np.int32)
+        self.sk._ck(self.lib.cvx_support_problem_result(self.p, _vp(out)))
+        return out
+
+    def close(self):
+        if self.p:
+            self.lib.cvx_support_problem_destroy(self.p)
+            self.p = C.c_void_p()

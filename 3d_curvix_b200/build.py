@@ -1,0 +1,68 @@
+"""In-tree build of the CUDA extension (libcurvix_b200.so) for sm_100a, and of the C++ host drop-in.
+
+nvcc cross-compiles without a GPU.  Flags that matter:
+  -gencode arch=compute_100a,code=sm_100a   B200 only, no other targets
+  -fmad=false                               un-fused FP64 so accept/reject decisions match an un-fused CPU build
+  -lineinfo                                 ncu source page
+"""
+import os
+import subprocess
+import sys
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+CSRC = os.path.join(HERE, "csrc")
+LIB = os.path.join(HERE, "libcurvix_b200.so")
+HOST_BIN = os.path.join(HERE, "host", "curvix_main")
+
+NVCC_FLAGS = [
+    "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-lineinfo", "-fmad=false",
+    "-Xcompiler", "-fPIC,-O2,-ffp-contract=off,-Wall", "--expt-relaxed-constexpr",
+]
+
+
+def _stale(target, sources):
+    if not os.path.exists(target):
+        return True
+    t = os.path.getmtime(target)
+    return any(os.path.getmtime(s) > t for s in sources)
+
+
+def _cxx():
+    # $CXX in this image points at a g++ without OpenMP specs; /usr/bin/g++ is complete
+    return "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++"
+
+
+def build_cuda(force=False, verbose=False):
+    srcs = [os.path.join(CSRC, f) for f in ("cvx_kernels.cu", "cvx_api.cu")]
+    deps = srcs + [os.path.join(CSRC, f) for f in ("cvx_kernels.cuh", "cvx_math.cuh")] + [os.path.join(ROOT, "include", "curvix_b200.h")]
+    if not force and not _stale(LIB, deps):
+        return LIB
+    nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+    cmd = [nvcc] + NVCC_FLAGS + ["-ccbin", _cxx(), "-shared", "-o", LIB] + srcs
+    if verbose:
+        cmd.insert(1, "-Xptxas=-v")
+        print(" ".join(cmd))
+    subprocess.run(cmd, check=True)
+    return LIB
+
+
+def build_host(force=False):
+    """C++ host drop-in (EdgeSketch_Core shim + curvix_main) linked against libcurvix_b200.so."""
+    hdir = os.path.join(HERE, "host")
+    srcs = [os.path.join(hdir, f) for f in ("EdgeSketch_Core.cpp", "main.cpp")]
+    if not all(os.path.exists(s) for s in srcs):
+        return None
+    deps = srcs + [os.path.join(hdir, f) for f in os.listdir(hdir) if f.endswith(".hpp")]
+    if not force and not _stale(HOST_BIN, deps + [LIB]):
+        return HOST_BIN
+    cmd = [_cxx(), "-O2", "-std=c++17", "-ffp-contract=off", "-Wall", "-I", os.path.join(ROOT, "include"), "-o", HOST_BIN] + srcs + \
+          ["-L", HERE, "-lcurvix_b200", "-Wl,-rpath," + HERE, "-Wl,-rpath,/usr/local/cuda/lib64"]
+    subprocess.run(cmd, check=True)
+    return HOST_BIN
+
+
+if __name__ == "__main__":
+    build_cuda(force="--force" in sys.argv, verbose="-v" in sys.argv)
+    build_host(force="--force" in sys.argv)
+    print("built", LIB)

@@ -1,0 +1,779 @@
+// =====================================================================================
+// cvx_api.cu -- the C-ABI (include/curvix_b200.h): context, device memory, per-pass constants, launch order.
+//
+// Host work here is limited to what the reference does once per pass on a handful of 3x3 matrices
+// (Set_Hypothesis_Views_Camera, EdgeSketch_Core.cpp:115-143, and the per-view F / epipoles that the
+// reference recomputes inside every getOre* call).  Everything per edge / per hypothesis runs on the GPU.
+// =====================================================================================
+#include "../../include/curvix_b200.h"
+
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "cvx_kernels.cuh"
+
+using namespace cvx;
+
+namespace {
+
+// ----------------------------------------------------------------------------- host 3x3 helpers (same op order as the device code)
+struct M3 { double m[9]; };
+struct V3 { double v[3]; };
+inline double hdot3(double a0, double a1, double a2, double b0, double b1, double b2) { return (a0 * b0 + a1 * b1) + a2 * b2; }
+M3 h_mul(const M3& a, const M3& b) {
+    M3 c;
+    for (int i = 0; i < 3; i++)
+        for (int j = 0; j < 3; j++) c.m[i * 3 + j] = hdot3(a.m[i * 3], a.m[i * 3 + 1], a.m[i * 3 + 2], b.m[j], b.m[3 + j], b.m[6 + j]);
+    return c;
+}
+V3 h_mv(const M3& a, const V3& x) {
+    V3 r;
+    for (int i = 0; i < 3; i++) r.v[i] = hdot3(a.m[i * 3], a.m[i * 3 + 1], a.m[i * 3 + 2], x.v[0], x.v[1], x.v[2]);
+    return r;
+}
+M3 h_tr(const M3& a) {
+    M3 t;
+    for (int i = 0; i < 3; i++) for (int j = 0; j < 3; j++) t.m[i * 3 + j] = a.m[j * 3 + i];
+    return t;
+}
+// Eigen Matrix3d::inverse(): cofactors times 1/det
+double h_cof(const M3& a, int i, int j) {
+    const int i1 = (i + 1) % 3, i2 = (i + 2) % 3, j1 = (j + 1) % 3, j2 = (j + 2) % 3;
+    return a.m[i1 * 3 + j1] * a.m[i2 * 3 + j2] - a.m[i1 * 3 + j2] * a.m[i2 * 3 + j1];
+}
+M3 h_inv(const M3& a) {
+    const double det = (h_cof(a, 0, 0) * a.m[0] + h_cof(a, 1, 0) * a.m[3]) + h_cof(a, 2, 0) * a.m[6];
+    const double invdet = 1.0 / det;
+    M3 r;
+    for (int i = 0; i < 3; i++) for (int j = 0; j < 3; j++) r.m[j * 3 + i] = h_cof(a, i, j) * invdet;
+    return r;
+}
+struct PairGeomH { M3 R21; V3 T21; M3 F; V3 e1pix, e2pix; };
+// util.cpp:44-66 (relative pose, fundamental matrix) + getOrientationList.cpp:47-50 (epipoles)
+PairGeomH h_pair_geometry(const M3& R1, const V3& T1, const M3& R2, const V3& T2, const M3& K1, const M3& K2) {
+    PairGeomH g;
+    g.R21 = h_mul(R2, h_tr(R1));
+    M3 nR1t = h_tr(R1), nR2t = h_tr(R2);
+    for (int i = 0; i < 9; i++) { nR1t.m[i] = -1 * nR1t.m[i]; nR2t.m[i] = -1 * nR2t.m[i]; }
+    const V3 C1 = h_mv(nR1t, T1), C2 = h_mv(nR2t, T2);
+    const V3 d = {{C1.v[0] - C2.v[0], C1.v[1] - C2.v[1], C1.v[2] - C2.v[2]}};
+    g.T21 = h_mv(R2, d);
+    const M3 Tx = {{0., -g.T21.v[2], g.T21.v[1], g.T21.v[2], 0., -g.T21.v[0], -g.T21.v[1], g.T21.v[0], 0.}};
+    g.F = h_mul(h_mul(h_tr(h_inv(K2)), h_mul(Tx, g.R21)), h_inv(K1));
+    const V3 rt = h_mv(h_tr(g.R21), g.T21);
+    const V3 met1 = {{rt.v[0] / rt.v[2], rt.v[1] / rt.v[2], 1.0}};
+    const V3 met2 = {{g.T21.v[0] / g.T21.v[2], g.T21.v[1] / g.T21.v[2], 1.0}};
+    g.e1pix = h_mv(K1, met1);
+    g.e2pix = h_mv(K2, met2);
+    return g;
+}
+
+template <typename T>
+struct DevBuf {   // grow-only device buffer
+    T* p = nullptr;
+    size_t cap = 0;
+    cudaError_t reserve(size_t n) {
+        if (n <= cap) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr; cap = 0;
+        size_t want = n + n / 8 + 64;
+        cudaError_t e = cudaMalloc(&p, want * sizeof(T));
+        if (e == cudaSuccess) cap = want;
+        return e;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+};
+
+}  // namespace
+
+struct cvx_ctx {
+    cvx_config cfg;
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    std::string err;
+    // cameras (host)
+    int n_views = 0;
+    std::vector<M3> R, K;
+    std::vector<V3> T;
+    bool multi_K = false, have_cams = false;
+    // edge arena
+    size_t arena_cap = 0, arena_used = 0;
+    EdgeArena ea = {};
+    std::vector<int64_t> edge_off;   // per view
+    std::vector<int32_t> edge_n, edge_cap;
+    DevBuf<int64_t> d_edge_off;
+    DevBuf<int32_t> d_edge_n;
+    bool tables_dirty = true;
+    // pass
+    int h1 = -1, h2 = -1, n_vali = 0;
+    PassConst pc;
+    std::vector<int32_t> vali_views;
+    DevBuf<ViewConst> d_vc;
+    DevBuf<int32_t> d_vali, d_bins;
+    BinGrid bg = {};
+    DevBuf<double> d_ang2;
+    DevBuf<double2> d_wedge_h1;
+    DevBuf<int32_t> d_wflag_h1;
+    // run
+    bool have_run = false, have_final = false;
+    int run_begin = 0, run_end = 0;
+    DevBuf<int32_t> d_m, d_n, d_nvalid, d_nsel;
+    DevBuf<int64_t> d_row_off, d_valid_off, d_pair_off;
+    int64_t H = 0, n_valid = 0, P = 0;
+    // row table storage
+    DevBuf<int32_t> r_h1, r_h2orig, r_local, r_rawat, r_label, r_h2rep, r_count, r_flags;
+    DevBuf<double> r_xc, r_yc, r_th, r_xbar, r_ybar, r_thbar, r_thn, r_orient;
+    DevBuf<double2> d_w31, d_w32, d_tgt;
+    int64_t inter_rows = 0;   // rows covered by d_w32/d_tgt (== H when the run was not chunked)
+    DevBuf<int32_t> d_support, d_support_t;
+    DevBuf<DevCounters> d_ctr;
+    DevBuf<int32_t> v_h1, v_row, v_count, v_sel, p_h1, p_h2rep, p_row, p_count, p_sup, f_nan;
+    DevBuf<double> f_gc, f_gw, f_tw, f_h2c;
+    std::vector<int64_t> h_row_off;
+    cvx_counts counts;
+    cvx_timings tm;
+    cudaEvent_t ev[8];
+    size_t inter_budget_bytes = size_t(12) << 30;
+};
+
+struct cvx_support_problem {
+    cvx_ctx* ctx;
+    int G, V;
+    int64_t H, n_edges;
+    DevBuf<int64_t> group_off, view_off;
+    DevBuf<int32_t> vali, bins, support, bin_tmp, s_idx, edge_n;
+    DevBuf<double> a31, a32, cs, sn, s_a31, s_a32, s_cs, s_sn;
+    DevBuf<double2> w31, w32, tgt;
+    BinGrid bg;
+    double thr, par;
+    cudaEvent_t e0, e1;
+};
+
+namespace {
+
+int fail(cvx_ctx* c, int code, const std::string& msg) {
+    if (c) c->err = msg;
+    return code;
+}
+#define CU(call)                                                                                                  \
+    do {                                                                                                          \
+        cudaError_t _e = (call);                                                                                  \
+        if (_e != cudaSuccess)                                                                                    \
+            return fail(ctx, CVX_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(_e));                   \
+    } while (0)
+
+RowTable row_table(cvx_ctx* c) {
+    RowTable rt;
+    rt.h1 = c->r_h1.p; rt.h2orig = c->r_h2orig.p; rt.local = c->r_local.p; rt.rawat = c->r_rawat.p; rt.label = c->r_label.p;
+    rt.h2rep = c->r_h2rep.p; rt.count = c->r_count.p; rt.flags = c->r_flags.p;
+    rt.xc = c->r_xc.p; rt.yc = c->r_yc.p; rt.th = c->r_th.p; rt.xbar = c->r_xbar.p; rt.ybar = c->r_ybar.p; rt.thbar = c->r_thbar.p;
+    rt.thn = c->r_thn.p; rt.orient = c->r_orient.p;
+    return rt;
+}
+
+int grow_arena(cvx_ctx* ctx, size_t need) {
+    if (need <= ctx->arena_cap) return CVX_OK;
+    size_t cap = std::max(need, ctx->arena_cap * 2);
+    cap = (cap + 1023) & ~size_t(1023);
+    EdgeArena n = {};
+    double** dp_new[] = {&n.x, &n.y, &n.th, &n.cs, &n.sn, &n.a31, &n.a32, &n.s_a31, &n.s_a32, &n.s_cs, &n.s_sn};
+    double** dp_old[] = {&ctx->ea.x, &ctx->ea.y, &ctx->ea.th, &ctx->ea.cs, &ctx->ea.sn, &ctx->ea.a31, &ctx->ea.a32, &ctx->ea.s_a31,
+                         &ctx->ea.s_a32, &ctx->ea.s_cs, &ctx->ea.s_sn};
+    for (int k = 0; k < 11; k++) {
+        CU(cudaMalloc(dp_new[k], cap * sizeof(double)));
+        if (k < 5 && ctx->arena_used) CU(cudaMemcpyAsync(*dp_new[k], *dp_old[k], ctx->arena_used * sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream));
+    }
+    CU(cudaMalloc(&n.bin, cap * sizeof(int32_t)));
+    CU(cudaMalloc(&n.s_idx, cap * sizeof(int32_t)));
+    CU(cudaStreamSynchronize(ctx->stream));
+    for (int k = 0; k < 11; k++) if (*dp_old[k]) cudaFree(*dp_old[k]);
+    if (ctx->ea.bin) cudaFree(ctx->ea.bin);
+    if (ctx->ea.s_idx) cudaFree(ctx->ea.s_idx);
+    ctx->ea = n;
+    ctx->arena_cap = cap;
+    return CVX_OK;
+}
+
+int sync_tables(cvx_ctx* ctx) {
+    if (!ctx->tables_dirty) return CVX_OK;
+    CU(ctx->d_edge_off.reserve(ctx->n_views + 1));
+    CU(ctx->d_edge_n.reserve(ctx->n_views));
+    CU(cudaMemcpyAsync(ctx->d_edge_off.p, ctx->edge_off.data(), ctx->n_views * sizeof(int64_t), cudaMemcpyHostToDevice, ctx->stream));
+    CU(cudaMemcpyAsync(ctx->d_edge_n.p, ctx->edge_n.data(), ctx->n_views * sizeof(int32_t), cudaMemcpyHostToDevice, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    ctx->tables_dirty = false;
+    return CVX_OK;
+}
+
+const M3& K_of(const cvx_ctx* c, int v) { return c->multi_K ? c->K[v] : c->K[0]; }
+
+int pick_bins(int max_edges) {
+    // B uniform angular bins over [0,180]: fine enough that a bin holds O(1) edges even when the whole view
+    // lies inside a few degrees of epipolar angle
+    int B = 1 << 16;
+    while (B < 4 * max_edges && B < (1 << 20)) B <<= 1;
+    return B;
+}
+
+}  // namespace
+
+extern "C" {
+
+void cvx_default_config(cvx_config* c) {
+    std::memset(c, 0, sizeof(*c));
+    c->delta = 0.4; c->delta_theta_deg = 15; c->parallel_angle_deg = 15;
+    c->lowes_ratio = 0.6; c->epip_tangency_displ_thresh = 3; c->location_perturbation = 0.4; c->orient_perturbation = 0.174533;
+    c->cluster_dist_thresh = 1; c->cluster_orient_thresh_deg = 20.0; c->cluster_gauss_sigma = 2.0; c->pi_truncated = 3.1415926;
+    c->n_views = 50; c->img_rows = 800; c->img_cols = 800; c->max_support_views = 4; c->max_cluster_size = 10;
+}
+
+int cvx_create(const cvx_config* cfg, int device, cvx_ctx** out) {
+    if (!cfg || !out || cfg->n_views < 3) return CVX_ERR_INVALID;
+    *out = nullptr;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return CVX_ERR_NO_DEVICE;   // no CPU fallback by design
+    if (device < 0 || device >= ndev) return CVX_ERR_INVALID;
+    cvx_ctx* ctx = new cvx_ctx();
+    ctx->cfg = *cfg; ctx->device = device; ctx->n_views = cfg->n_views;
+    ctx->edge_off.assign(cfg->n_views, 0); ctx->edge_n.assign(cfg->n_views, 0); ctx->edge_cap.assign(cfg->n_views, 0);
+    std::memset(&ctx->counts, 0, sizeof(ctx->counts));
+    std::memset(&ctx->tm, 0, sizeof(ctx->tm));
+    if (const char* b = getenv("CVX_INTER_BUDGET_MB")) ctx->inter_budget_bytes = size_t(atoll(b)) << 20;
+    if (cudaSetDevice(device) != cudaSuccess || cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) {
+        delete ctx;
+        return CVX_ERR_CUDA;
+    }
+    for (auto& e : ctx->ev) cudaEventCreate(&e);
+    if (ctx->d_ctr.reserve(1) != cudaSuccess) { delete ctx; return CVX_ERR_NOMEM; }
+    *out = ctx;
+    return CVX_OK;
+}
+
+int cvx_destroy(cvx_ctx* ctx) {
+    if (!ctx) return CVX_ERR_INVALID;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    double* dp[] = {ctx->ea.x, ctx->ea.y, ctx->ea.th, ctx->ea.cs, ctx->ea.sn, ctx->ea.a31, ctx->ea.a32, ctx->ea.s_a31, ctx->ea.s_a32, ctx->ea.s_cs, ctx->ea.s_sn};
+    for (double* p : dp) if (p) cudaFree(p);
+    if (ctx->ea.bin) cudaFree(ctx->ea.bin);
+    if (ctx->ea.s_idx) cudaFree(ctx->ea.s_idx);
+    ctx->d_edge_off.release(); ctx->d_edge_n.release(); ctx->d_vc.release(); ctx->d_vali.release(); ctx->d_bins.release();
+    ctx->d_ang2.release(); ctx->d_wedge_h1.release(); ctx->d_wflag_h1.release(); ctx->d_m.release(); ctx->d_n.release();
+    ctx->d_nvalid.release(); ctx->d_nsel.release(); ctx->d_row_off.release(); ctx->d_valid_off.release(); ctx->d_pair_off.release();
+    DevBuf<int32_t>* ib[] = {&ctx->r_h1, &ctx->r_h2orig, &ctx->r_local, &ctx->r_rawat, &ctx->r_label, &ctx->r_h2rep, &ctx->r_count, &ctx->r_flags,
+                             &ctx->d_support, &ctx->d_support_t, &ctx->v_h1, &ctx->v_row, &ctx->v_count, &ctx->v_sel, &ctx->p_h1, &ctx->p_h2rep,
+                             &ctx->p_row, &ctx->p_count, &ctx->p_sup, &ctx->f_nan};
+    for (auto* b : ib) b->release();
+    DevBuf<double>* db[] = {&ctx->r_xc, &ctx->r_yc, &ctx->r_th, &ctx->r_xbar, &ctx->r_ybar, &ctx->r_thbar, &ctx->r_thn, &ctx->r_orient,
+                            &ctx->f_gc, &ctx->f_gw, &ctx->f_tw, &ctx->f_h2c};
+    for (auto* b : db) b->release();
+    ctx->d_w31.release(); ctx->d_w32.release(); ctx->d_tgt.release(); ctx->d_ctr.release();
+    for (auto& e : ctx->ev) cudaEventDestroy(e);
+    cudaStreamDestroy(ctx->stream);
+    delete ctx;
+    return CVX_OK;
+}
+
+const char* cvx_last_error(const cvx_ctx* ctx) { return ctx ? ctx->err.c_str() : "null context"; }
+
+int cvx_set_cameras(cvx_ctx* ctx, int n, const double* R, const double* T, const double* K, int k_per_view) {
+    if (!ctx || !R || !T || !K || n != ctx->n_views) return fail(ctx, CVX_ERR_INVALID, "cvx_set_cameras: bad arguments");
+    ctx->R.resize(n); ctx->T.resize(n);
+    for (int i = 0; i < n; i++) { std::memcpy(ctx->R[i].m, R + 9 * i, 72); std::memcpy(ctx->T[i].v, T + 3 * i, 24); }
+    ctx->multi_K = k_per_view != 0;
+    ctx->K.resize(ctx->multi_K ? n : 1);
+    for (size_t i = 0; i < ctx->K.size(); i++) std::memcpy(ctx->K[i].m, K + 9 * i, 72);
+    ctx->have_cams = true;
+    return CVX_OK;
+}
+
+int cvx_set_view_edges(cvx_ctx* ctx, int view, int n, const double* x, const double* y, const double* theta, const double* strength) {
+    (void)strength;   // carried through by the host shim only; never used in any computation on the path
+    if (!ctx || view < 0 || view >= ctx->n_views || n < 0 || (n > 0 && (!x || !y || !theta)))
+        return fail(ctx, CVX_ERR_INVALID, "cvx_set_view_edges: bad arguments");
+    CU(cudaSetDevice(ctx->device));
+    if (n > ctx->edge_cap[view]) {   // new slot at the end of the arena (256-byte aligned)
+        const size_t slot = (size_t(n) + 31) & ~size_t(31);
+        const int rc = grow_arena(ctx, ctx->arena_used + slot);
+        if (rc) return rc;
+        ctx->edge_off[view] = int64_t(ctx->arena_used);
+        ctx->edge_cap[view] = int32_t(slot);
+        ctx->arena_used += slot;
+    }
+    ctx->edge_n[view] = n;
+    ctx->tables_dirty = true;
+    const int64_t off = ctx->edge_off[view];
+    if (n > 0) {
+        CU(cudaMemcpyAsync(ctx->ea.x + off, x, size_t(n) * 8, cudaMemcpyHostToDevice, ctx->stream));
+        CU(cudaMemcpyAsync(ctx->ea.y + off, y, size_t(n) * 8, cudaMemcpyHostToDevice, ctx->stream));
+        CU(cudaMemcpyAsync(ctx->ea.th + off, theta, size_t(n) * 8, cudaMemcpyHostToDevice, ctx->stream));
+        launch_edge_trig(ctx->ea.th + off, ctx->ea.cs + off, ctx->ea.sn + off, n, ctx->stream);
+        ctx->tm.kernel_launches++;
+    }
+    ctx->have_run = false;
+    return CVX_OK;
+}
+
+int cvx_set_hypothesis_pair(cvx_ctx* ctx, int h1, int h2) {
+    if (!ctx || !ctx->have_cams || h1 < 0 || h2 < 0 || h1 >= ctx->n_views || h2 >= ctx->n_views || h1 == h2)
+        return fail(ctx, CVX_ERR_INVALID, "cvx_set_hypothesis_pair: bad view indices or cameras not set");
+    CU(cudaSetDevice(ctx->device));
+    const cvx_config& cfg = ctx->cfg;
+    ctx->h1 = h1; ctx->h2 = h2;
+    // ---- Set_Hypothesis_Views_Camera, EdgeSketch_Core.cpp:115-143
+    const M3 K1 = K_of(ctx, h1), K2 = K_of(ctx, h2);
+    const PairGeomH g21 = h_pair_geometry(ctx->R[h1], ctx->T[h1], ctx->R[h2], ctx->T[h2], K1, K2);
+    PassConst& pc = ctx->pc;
+    std::memset(&pc, 0, sizeof(pc));
+    std::memcpy(pc.F21, g21.F.m, 72); std::memcpy(pc.R21, g21.R21.m, 72); std::memcpy(pc.T21, g21.T21.v, 24);
+    pc.e1_21[0] = g21.e1pix.v[0]; pc.e1_21[1] = g21.e1pix.v[1]; pc.e2_21[0] = g21.e2pix.v[0]; pc.e2_21[1] = g21.e2pix.v[1];
+    const M3 K1i = h_inv(K1), K2i = h_inv(K2);
+    std::memcpy(pc.K1inv, K1i.m, 72); std::memcpy(pc.K2inv, K2i.m, 72);
+    std::memcpy(pc.R1, ctx->R[h1].m, 72); std::memcpy(pc.T1, ctx->T[h1].v, 24);
+    pc.delta = cfg.delta;
+    pc.cos_thresh = std::cos(double(cfg.delta_theta_deg) / 180 * cfg.pi_truncated);   // getSupportedEdgels.cpp:35 (host libm, as the reference)
+    pc.parallel_deg = cfg.parallel_angle_deg;
+    pc.loc_pert = cfg.location_perturbation; pc.tang_thresh = cfg.epip_tangency_displ_thresh; pc.orient_pert = cfg.orient_perturbation;
+    pc.cl_dist = cfg.cluster_dist_thresh;
+    pc.cl_orient_rad = cfg.cluster_orient_thresh_deg * (M_PI / 180.0);                // util.hpp deg_to_rad
+    pc.cl_wrap_deg = -90.0 + (cfg.cluster_orient_thresh_deg / 2.0);                   // EdgeClusterer.cpp:41
+    pc.cl_sigma = cfg.cluster_gauss_sigma; pc.lowes_ratio = cfg.lowes_ratio;
+    pc.rows = cfg.img_rows; pc.cols = cfg.img_cols; pc.max_support = cfg.max_support_views; pc.max_cluster = cfg.max_cluster_size;
+    ctx->vali_views.clear();
+    for (int v = 0; v < ctx->n_views; v++) if (v != h1 && v != h2) ctx->vali_views.push_back(v);
+    const int V = int(ctx->vali_views.size());
+    ctx->n_vali = V; pc.n_vali = V;
+    std::vector<ViewConst> vc(V);
+    int max_edges = 1;
+    for (int i = 0; i < V; i++) {
+        const int v = ctx->vali_views[i];
+        const M3 K3 = K_of(ctx, v);
+        const PairGeomH g31 = h_pair_geometry(ctx->R[h1], ctx->T[h1], ctx->R[v], ctx->T[v], K1, K3);
+        const PairGeomH g32 = h_pair_geometry(ctx->R[h2], ctx->T[h2], ctx->R[v], ctx->T[v], K2, K3);
+        ViewConst& c = vc[i];
+        std::memset(&c, 0, sizeof(c));
+        std::memcpy(c.F31, g31.F.m, 72); c.e1_31[0] = g31.e1pix.v[0]; c.e1_31[1] = g31.e1pix.v[1]; c.e2_31[0] = g31.e2pix.v[0]; c.e2_31[1] = g31.e2pix.v[1];
+        std::memcpy(c.F32, g32.F.m, 72); c.e1_32[0] = g32.e1pix.v[0]; c.e1_32[1] = g32.e1pix.v[1]; c.e2_32[0] = g32.e2pix.v[0]; c.e2_32[1] = g32.e2pix.v[1];
+        std::memcpy(c.R31, g31.R21.m, 72); std::memcpy(c.T31, g31.T21.v, 24);
+        max_edges = std::max(max_edges, ctx->edge_n[v]);
+    }
+    int rc = sync_tables(ctx);
+    if (rc) return rc;
+    CU(ctx->d_vc.reserve(V)); CU(ctx->d_vali.reserve(V));
+    cudaEventRecord(ctx->ev[0], ctx->stream);
+    CU(cudaMemcpyAsync(ctx->d_vc.p, vc.data(), V * sizeof(ViewConst), cudaMemcpyHostToDevice, ctx->stream));
+    CU(cudaMemcpyAsync(ctx->d_vali.p, ctx->vali_views.data(), V * sizeof(int32_t), cudaMemcpyHostToDevice, ctx->stream));
+    // ---- stage every validation view into its bin grid (hoisted getOreListVali + cos/sin, EdgeSketch_Core.cpp:315-342)
+    ctx->bg.B = pick_bins(max_edges); ctx->bg.BS = ctx->bg.B + 1; ctx->bg.scale = ctx->bg.B / 180.0;
+    CU(ctx->d_bins.reserve(size_t(V) * ctx->bg.BS));
+    ctx->bg.bins = ctx->d_bins.p;
+    launch_stage_views(ctx->ea, ctx->d_edge_off.p, ctx->d_edge_n.p, ctx->d_vali.p, V, max_edges, ctx->d_vc.p, ctx->bg, ctx->stream,
+                       &ctx->tm.kernel_launches);
+    // ---- Set_Hypothesis_Views_Edgels, EdgeSketch_Core.cpp:145-166
+    const int E1 = ctx->edge_n[h1], E2 = ctx->edge_n[h2];
+    CU(ctx->d_ang2.reserve(std::max(E2, 1))); CU(ctx->d_wedge_h1.reserve(std::max(E1, 1))); CU(ctx->d_wflag_h1.reserve(std::max(E1, 1)));
+    launch_h2_angles(ctx->ea.x + ctx->edge_off[h2], ctx->ea.y + ctx->edge_off[h2], E2, pc.e2_21[0], pc.e2_21[1], ctx->d_ang2.p, ctx->stream);
+    launch_h1_wedges(pc, ctx->ea.x + ctx->edge_off[h1], ctx->ea.y + ctx->edge_off[h1], E1, ctx->d_wedge_h1.p, ctx->d_wflag_h1.p, ctx->stream);
+    ctx->tm.kernel_launches += 2;
+    cudaEventRecord(ctx->ev[1], ctx->stream);
+    CU(cudaStreamSynchronize(ctx->stream));   // vc (host vector) must outlive the copy
+    cudaEventElapsedTime(&ctx->tm.set_pair_ms, ctx->ev[0], ctx->ev[1]);
+    CU(cudaGetLastError());
+    ctx->have_run = false; ctx->have_final = false;
+    return CVX_OK;
+}
+
+int cvx_run_edge_sketch(cvx_ctx* ctx, int h1_begin, int h1_end) {
+    if (!ctx || ctx->h1 < 0) return fail(ctx, CVX_ERR_INVALID, "cvx_run_edge_sketch: no hypothesis pair set");
+    CU(cudaSetDevice(ctx->device));
+    const int E1 = ctx->edge_n[ctx->h1], E2 = ctx->edge_n[ctx->h2], V = ctx->n_vali;
+    if (h1_begin < 0) h1_begin = 0;
+    if (h1_end < 0 || h1_end > E1) h1_end = E1;
+    if (h1_begin > h1_end) h1_begin = h1_end;
+    ctx->run_begin = h1_begin; ctx->run_end = h1_end;
+    cudaStream_t st = ctx->stream;
+    const PassConst& pc = ctx->pc;
+    const double *x1 = ctx->ea.x + ctx->edge_off[ctx->h1], *y1 = ctx->ea.y + ctx->edge_off[ctx->h1], *th1 = ctx->ea.th + ctx->edge_off[ctx->h1];
+    const double *x2 = ctx->ea.x + ctx->edge_off[ctx->h2], *y2 = ctx->ea.y + ctx->edge_off[ctx->h2], *th2 = ctx->ea.th + ctx->edge_off[ctx->h2];
+    const int E1a = std::max(E1, 1);
+    CU(ctx->d_m.reserve(E1a)); CU(ctx->d_n.reserve(E1a)); CU(ctx->d_nvalid.reserve(E1a)); CU(ctx->d_nsel.reserve(E1a));
+    CU(ctx->d_row_off.reserve(E1a + 1)); CU(ctx->d_valid_off.reserve(E1a + 1)); CU(ctx->d_pair_off.reserve(E1a + 1));
+    CU(cudaMemsetAsync(ctx->d_m.p, 0, E1a * 4, st)); CU(cudaMemsetAsync(ctx->d_n.p, 0, E1a * 4, st));
+    CU(cudaMemsetAsync(ctx->d_nvalid.p, 0, E1a * 4, st)); CU(cudaMemsetAsync(ctx->d_nsel.p, 0, E1a * 4, st));
+    CU(cudaMemsetAsync(ctx->d_ctr.p, 0, sizeof(DevCounters), st));
+    cudaEventRecord(ctx->ev[0], st);
+    // ---- hypothesis formation
+    launch_form_count(pc, x1, y1, h1_begin, h1_end, ctx->d_wedge_h1.p, x2, y2, th2, ctx->d_ang2.p, E2, ctx->d_m.p, ctx->d_n.p, st);
+    launch_scan_i32_i64(ctx->d_n.p, ctx->d_row_off.p, E1, st);
+    ctx->tm.kernel_launches += 2;
+    ctx->h_row_off.resize(size_t(E1) + 1);
+    CU(cudaMemcpyAsync(ctx->h_row_off.data(), ctx->d_row_off.p, (size_t(E1) + 1) * 8, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    const int64_t H = ctx->h_row_off[E1];
+    ctx->H = H;
+    const size_t Ha = size_t(std::max<int64_t>(H, 1));
+    DevBuf<int32_t>* ib[] = {&ctx->r_h1, &ctx->r_h2orig, &ctx->r_local, &ctx->r_rawat, &ctx->r_label, &ctx->r_h2rep, &ctx->r_count, &ctx->r_flags};
+    for (auto* b : ib) CU(b->reserve(Ha));
+    DevBuf<double>* db[] = {&ctx->r_xc, &ctx->r_yc, &ctx->r_th, &ctx->r_xbar, &ctx->r_ybar, &ctx->r_thbar, &ctx->r_thn, &ctx->r_orient};
+    for (auto* b : db) CU(b->reserve(Ha));
+    RowTable rt = row_table(ctx);
+    launch_form_fill(pc, x1, y1, h1_begin, h1_end, ctx->d_wedge_h1.p, x2, y2, th2, ctx->d_ang2.p, E2, ctx->d_n.p, ctx->d_row_off.p, rt, st);
+    ctx->tm.kernel_launches++;
+    cudaEventRecord(ctx->ev[1], st);
+    // ---- validation
+    CU(ctx->d_w31.reserve(size_t(std::max(V, 1)) * E1a));
+    CU(ctx->d_support.reserve(size_t(std::max(V, 1)) * Ha));
+    launch_wedge31(pc, ctx->d_vc.p, x1, y1, ctx->d_n.p, h1_begin, h1_end, E1, ctx->d_w31.p, ctx->d_ctr.p, st);
+    ctx->tm.kernel_launches++;
+    // chunk the hypothesis rows so that the per-validation intermediates (32 B each) stay under the budget
+    int64_t max_rows = int64_t(ctx->inter_budget_bytes / (size_t(std::max(V, 1)) * 32));
+    if (max_rows < 1024) max_rows = 1024;
+    float rep_ms = 0, sup_ms = 0;
+    int ha = h1_begin;
+    bool chunked = false;
+    while (ha < h1_end) {
+        int hb = ha;
+        const int64_t rbeg = ctx->h_row_off[ha];
+        while (hb < h1_end && ctx->h_row_off[hb + 1] - rbeg <= max_rows) hb++;
+        if (hb == ha) hb = ha + 1;   // a single edge larger than the budget: take it alone
+        const int64_t rend = ctx->h_row_off[hb];
+        const int64_t rows = rend - rbeg;
+        if (hb < h1_end || ha > h1_begin) chunked = true;
+        if (rows > 0) {
+            CU(ctx->d_w32.reserve(size_t(V) * rows)); CU(ctx->d_tgt.reserve(size_t(V) * rows));
+            cudaEventRecord(ctx->ev[4], st);
+            launch_reproject(pc, ctx->d_vc.p, x1, y1, th1, rt, rbeg, rend, ctx->d_w32.p, ctx->d_tgt.p, ctx->d_ctr.p, st);
+            cudaEventRecord(ctx->ev[5], st);
+            SupportArgs a;
+            a.group_off = ctx->d_row_off.p; a.g_begin = ha; a.g_end = hb; a.row_base = rbeg; a.chunk_rows = rows;
+            a.w31 = ctx->d_w31.p; a.w31_stride = E1; a.w32 = ctx->d_w32.p; a.tgt = ctx->d_tgt.p;
+            a.vali_view = ctx->d_vali.p; a.edge_off = ctx->d_edge_off.p; a.bg = ctx->bg;
+            a.s_a31 = ctx->ea.s_a31; a.s_a32 = ctx->ea.s_a32; a.s_cs = ctx->ea.s_cs; a.s_sn = ctx->ea.s_sn; a.s_idx = ctx->ea.s_idx;
+            a.cos_thresh = pc.cos_thresh; a.parallel_deg = pc.parallel_deg;
+            a.support = ctx->d_support.p; a.sup_stride = int64_t(Ha); a.ctr = ctx->d_ctr.p; a.n_vali = V;
+            launch_support(a, st);
+            cudaEventRecord(ctx->ev[6], st);
+            ctx->tm.kernel_launches += 2;
+            if (chunked) {   // per-chunk timing needs a sync; the unchunked path stays asynchronous
+                CU(cudaStreamSynchronize(st));
+                float t1 = 0, t2 = 0;
+                cudaEventElapsedTime(&t1, ctx->ev[4], ctx->ev[5]); cudaEventElapsedTime(&t2, ctx->ev[5], ctx->ev[6]);
+                rep_ms += t1; sup_ms += t2;
+            }
+            ctx->inter_rows = rows;
+        }
+        ha = hb;
+    }
+    cudaEventRecord(ctx->ev[2], st);
+    // ---- vote + ratio test
+    launch_select(pc, ctx->d_row_off.p, h1_begin, h1_end, ctx->d_support.p, int64_t(Ha), rt, ctx->d_nvalid.p, ctx->d_nsel.p, st);
+    launch_scan_i32_i64(ctx->d_nvalid.p, ctx->d_valid_off.p, E1, st);
+    launch_scan_i32_i64(ctx->d_nsel.p, ctx->d_pair_off.p, E1, st);
+    ctx->tm.kernel_launches += 3;
+    int64_t tot[2] = {0, 0};
+    CU(cudaMemcpyAsync(&tot[0], ctx->d_valid_off.p + E1, 8, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(&tot[1], ctx->d_pair_off.p + E1, 8, cudaMemcpyDeviceToHost, st));
+    DevCounters hc;
+    CU(cudaMemcpyAsync(&hc, ctx->d_ctr.p, sizeof(hc), cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    ctx->n_valid = tot[0]; ctx->P = tot[1];
+    const size_t NVa = size_t(std::max<int64_t>(ctx->n_valid, 1)), Pa = size_t(std::max<int64_t>(ctx->P, 1));
+    CU(ctx->v_h1.reserve(NVa)); CU(ctx->v_row.reserve(NVa)); CU(ctx->v_count.reserve(NVa)); CU(ctx->v_sel.reserve(NVa));
+    CU(ctx->p_h1.reserve(Pa)); CU(ctx->p_h2rep.reserve(Pa)); CU(ctx->p_row.reserve(Pa)); CU(ctx->p_count.reserve(Pa));
+    CU(ctx->p_sup.reserve(Pa * std::max(V, 1)));
+    launch_select_fill(ctx->d_row_off.p, h1_begin, h1_end, rt, ctx->d_valid_off.p, ctx->d_pair_off.p, ctx->v_h1.p, ctx->v_row.p, ctx->v_count.p,
+                       ctx->v_sel.p, ctx->p_h1.p, ctx->p_h2rep.p, ctx->p_row.p, ctx->p_count.p, st);
+    launch_gather_supports(ctx->p_row.p, ctx->P, V, ctx->d_support.p, int64_t(Ha), ctx->p_sup.p, st);
+    ctx->tm.kernel_launches += 2;
+    cudaEventRecord(ctx->ev[3], st);
+    CU(cudaStreamSynchronize(st));
+    CU(cudaGetLastError());
+    cudaEventElapsedTime(&ctx->tm.run_ms, ctx->ev[0], ctx->ev[3]);
+    cudaEventElapsedTime(&ctx->tm.form_ms, ctx->ev[0], ctx->ev[1]);
+    cudaEventElapsedTime(&ctx->tm.select_ms, ctx->ev[2], ctx->ev[3]);
+    if (!chunked && H > 0) {
+        cudaEventElapsedTime(&rep_ms, ctx->ev[4], ctx->ev[5]); cudaEventElapsedTime(&sup_ms, ctx->ev[5], ctx->ev[6]);
+    }
+    ctx->tm.reproject_ms = rep_ms; ctx->tm.support_ms = sup_ms;
+    if (chunked) ctx->inter_rows = -1;
+    // ---- counts
+    cvx_counts& c = ctx->counts;
+    std::memset(&c, 0, sizeof(c));
+    c.n_h1_total = E1; c.n_hypotheses = H; c.n_validations = H * V; c.n_valid_rows = ctx->n_valid; c.n_pairs = ctx->P;
+    c.n_degenerate_wedges = int64_t(hc.n_degenerate); c.n_supported = int64_t(hc.n_supported); c.n_parallel = int64_t(hc.n_parallel);
+    for (int i = h1_begin; i < h1_end; i++) if (ctx->h_row_off[i + 1] > ctx->h_row_off[i]) c.n_h1_processed++;
+    c.n_candidates = -1;   // filled lazily by cvx_get_counts (needs m[])
+    ctx->have_run = true; ctx->have_final = false;
+    return CVX_OK;
+}
+
+int cvx_get_counts(cvx_ctx* ctx, cvx_counts* out) {
+    if (!ctx || !out || !ctx->have_run) return fail(ctx, CVX_ERR_INVALID, "cvx_get_counts: no run");
+    if (ctx->counts.n_candidates < 0) {
+        CU(cudaSetDevice(ctx->device));
+        const int E1 = ctx->edge_n[ctx->h1];
+        std::vector<int32_t> m(std::max(E1, 1));
+        CU(cudaMemcpy(m.data(), ctx->d_m.p, size_t(E1) * 4, cudaMemcpyDeviceToHost));
+        int64_t s = 0;
+        for (int i = 0; i < E1; i++) s += m[i];
+        ctx->counts.n_candidates = s;
+    }
+    *out = ctx->counts;
+    return CVX_OK;
+}
+
+#define D2H(dst, src, n, T)                                                                                       \
+    do { if ((dst) && (n) > 0) CU(cudaMemcpy((dst), (src), size_t(n) * sizeof(T), cudaMemcpyDeviceToHost)); } while (0)
+
+int cvx_get_h2_angles(cvx_ctx* ctx, double* out) {
+    if (!ctx || ctx->h2 < 0) return fail(ctx, CVX_ERR_INVALID, "no pair");
+    CU(cudaSetDevice(ctx->device));
+    D2H(out, ctx->d_ang2.p, ctx->edge_n[ctx->h2], double);
+    return CVX_OK;
+}
+int cvx_get_h1_wedges(cvx_ctx* ctx, double* out, int32_t* flag) {
+    if (!ctx || ctx->h1 < 0) return fail(ctx, CVX_ERR_INVALID, "no pair");
+    CU(cudaSetDevice(ctx->device));
+    D2H(out, ctx->d_wedge_h1.p, ctx->edge_n[ctx->h1], double2);
+    D2H(flag, ctx->d_wflag_h1.p, ctx->edge_n[ctx->h1], int32_t);
+    return CVX_OK;
+}
+int cvx_get_h1_table(cvx_ctx* ctx, int32_t* m, int32_t* n, int64_t* row_off) {
+    if (!ctx || !ctx->have_run) return fail(ctx, CVX_ERR_INVALID, "no run");
+    CU(cudaSetDevice(ctx->device));
+    const int E1 = ctx->edge_n[ctx->h1];
+    D2H(m, ctx->d_m.p, E1, int32_t);
+    D2H(n, ctx->d_n.p, E1, int32_t);
+    if (row_off)
+        for (int i = 0; i < E1; i++) row_off[i] = (ctx->h_row_off[i + 1] > ctx->h_row_off[i]) ? ctx->h_row_off[i] : -1;
+    return CVX_OK;
+}
+int cvx_get_rows(cvx_ctx* ctx, int32_t* h1, int32_t* h2_orig, int32_t* local_idx, int32_t* raw_at_local, double* xc, double* yc,
+                 double* theta_orig, double* xbar, double* ybar, double* thbar, int32_t* label, int32_t* h2_rep, int32_t* count) {
+    if (!ctx || !ctx->have_run) return fail(ctx, CVX_ERR_INVALID, "no run");
+    CU(cudaSetDevice(ctx->device));
+    const int64_t H = ctx->H;
+    D2H(h1, ctx->r_h1.p, H, int32_t); D2H(h2_orig, ctx->r_h2orig.p, H, int32_t); D2H(local_idx, ctx->r_local.p, H, int32_t);
+    D2H(raw_at_local, ctx->r_rawat.p, H, int32_t); D2H(xc, ctx->r_xc.p, H, double); D2H(yc, ctx->r_yc.p, H, double);
+    D2H(theta_orig, ctx->r_th.p, H, double); D2H(xbar, ctx->r_xbar.p, H, double); D2H(ybar, ctx->r_ybar.p, H, double);
+    D2H(thbar, ctx->r_thbar.p, H, double); D2H(label, ctx->r_label.p, H, int32_t); D2H(h2_rep, ctx->r_h2rep.p, H, int32_t);
+    D2H(count, ctx->r_count.p, H, int32_t);
+    return CVX_OK;
+}
+int cvx_get_support_matrix(cvx_ctx* ctx, int32_t* out) {
+    if (!ctx || !ctx->have_run || !out) return fail(ctx, CVX_ERR_INVALID, "no run");
+    CU(cudaSetDevice(ctx->device));
+    const int64_t H = ctx->H;
+    const int V = ctx->n_vali;
+    if (H == 0 || V == 0) return CVX_OK;
+    CU(ctx->d_support_t.reserve(size_t(H) * V));
+    launch_transpose_support(ctx->d_support.p, std::max<int64_t>(H, 1), H, V, ctx->d_support_t.p, ctx->stream);
+    ctx->tm.kernel_launches++;
+    CU(cudaStreamSynchronize(ctx->stream));
+    D2H(out, ctx->d_support_t.p, H * V, int32_t);
+    return CVX_OK;
+}
+int cvx_get_intermediates(cvx_ctx* ctx, double* wedge31, double* wedge32, double* tgt) {
+    if (!ctx || !ctx->have_run) return fail(ctx, CVX_ERR_INVALID, "no run");
+    if (ctx->inter_rows != ctx->H && ctx->H > 0) return fail(ctx, CVX_ERR_INVALID, "intermediates unavailable: the run was chunked");
+    CU(cudaSetDevice(ctx->device));
+    const int E1 = ctx->edge_n[ctx->h1], V = ctx->n_vali;
+    const int64_t H = ctx->H;
+    // device layout is view-major; the ABI returns [E1][V][2] and [H][V][2]
+    if (wedge31) {
+        std::vector<double> t(size_t(V) * E1 * 2);
+        CU(cudaMemcpy(t.data(), ctx->d_w31.p, t.size() * 8, cudaMemcpyDeviceToHost));
+        for (int v = 0; v < V; v++) for (int i = 0; i < E1; i++) for (int k = 0; k < 2; k++)
+            wedge31[(size_t(i) * V + v) * 2 + k] = t[(size_t(v) * E1 + i) * 2 + k];
+    }
+    for (int which = 0; which < 2; which++) {
+        double* dst = which ? tgt : wedge32;
+        if (!dst || H == 0) continue;
+        std::vector<double> t(size_t(V) * H * 2);
+        CU(cudaMemcpy(t.data(), which ? (void*)ctx->d_tgt.p : (void*)ctx->d_w32.p, t.size() * 8, cudaMemcpyDeviceToHost));
+        for (int v = 0; v < V; v++) for (int64_t r = 0; r < H; r++) for (int k = 0; k < 2; k++)
+            dst[(size_t(r) * V + v) * 2 + k] = t[(size_t(v) * H + r) * 2 + k];
+    }
+    return CVX_OK;
+}
+int cvx_get_valid_rows(cvx_ctx* ctx, int32_t* h1, int32_t* row, int32_t* count, int32_t* selected) {
+    if (!ctx || !ctx->have_run) return fail(ctx, CVX_ERR_INVALID, "no run");
+    CU(cudaSetDevice(ctx->device));
+    const int64_t n = ctx->n_valid;
+    D2H(h1, ctx->v_h1.p, n, int32_t); D2H(row, ctx->v_row.p, n, int32_t); D2H(count, ctx->v_count.p, n, int32_t); D2H(selected, ctx->v_sel.p, n, int32_t);
+    return CVX_OK;
+}
+int cvx_get_pairs(cvx_ctx* ctx, int32_t* h1, int32_t* h2rep, int32_t* row, int32_t* count, int32_t* supports) {
+    if (!ctx || !ctx->have_run) return fail(ctx, CVX_ERR_INVALID, "no run");
+    CU(cudaSetDevice(ctx->device));
+    const int64_t P = ctx->P;
+    D2H(h1, ctx->p_h1.p, P, int32_t); D2H(h2rep, ctx->p_h2rep.p, P, int32_t); D2H(row, ctx->p_row.p, P, int32_t);
+    D2H(count, ctx->p_count.p, P, int32_t); D2H(supports, ctx->p_sup.p, P * ctx->n_vali, int32_t);
+    return CVX_OK;
+}
+
+int cvx_get_reference_order(cvx_ctx* ctx, int64_t* idx, int64_t* n_out) {
+    if (!ctx || !ctx->have_run || !idx || !n_out) return fail(ctx, CVX_ERR_INVALID, "cvx_get_reference_order: bad arguments");
+    CU(cudaSetDevice(ctx->device));
+    const int64_t nv = ctx->n_valid;
+    std::vector<int32_t> h1(nv), cnt(nv), sel(nv);
+    D2H(h1.data(), ctx->v_h1.p, nv, int32_t); D2H(cnt.data(), ctx->v_count.p, nv, int32_t); D2H(sel.data(), ctx->v_sel.p, nv, int32_t);
+    int64_t out = 0, pair_base = 0;
+    for (int64_t i = 0; i < nv;) {
+        int64_t j = i;
+        while (j < nv && h1[j] == h1[i]) j++;
+        // valid_pairs_with_counts in ascending row order, EdgeSketch_Core.cpp:480-485
+        std::vector<std::pair<int, int>> vp;
+        std::vector<int64_t> pair_of(j - i, -1);
+        int64_t q = pair_base;
+        for (int64_t k = i; k < j; k++) { vp.push_back({int(k - i), cnt[k]}); if (sel[k]) pair_of[k - i] = q++; }
+        std::sort(vp.begin(), vp.end(), [](const std::pair<int, int>& a, const std::pair<int, int>& b) { return a.second > b.second; });   // :488-491
+        int taken = 0;
+        for (const auto& pr : vp)
+            if (pair_of[pr.first] >= 0 && taken < ctx->cfg.n_views) { idx[out++] = pair_of[pr.first]; taken++; }   // :500-526
+        pair_base = q;
+        i = j;
+    }
+    *n_out = out;
+    return CVX_OK;
+}
+
+static int run_finalize(cvx_ctx* ctx) {
+    if (ctx->have_final) return CVX_OK;
+    const int64_t P = ctx->P;
+    const size_t Pa = size_t(std::max<int64_t>(P, 1));
+    CU(ctx->f_gc.reserve(Pa * 3)); CU(ctx->f_gw.reserve(Pa * 3)); CU(ctx->f_tw.reserve(Pa * 3)); CU(ctx->f_h2c.reserve(Pa * 2)); CU(ctx->f_nan.reserve(Pa));
+    const double *x1 = ctx->ea.x + ctx->edge_off[ctx->h1], *y1 = ctx->ea.y + ctx->edge_off[ctx->h1], *th1 = ctx->ea.th + ctx->edge_off[ctx->h1];
+    const double *x2 = ctx->ea.x + ctx->edge_off[ctx->h2], *y2 = ctx->ea.y + ctx->edge_off[ctx->h2], *th2 = ctx->ea.th + ctx->edge_off[ctx->h2];
+    cudaEventRecord(ctx->ev[0], ctx->stream);
+    launch_finalize(ctx->pc, x1, y1, th1, x2, y2, th2, ctx->p_h1.p, ctx->p_h2rep.p, P, ctx->f_gc.p, ctx->f_gw.p, ctx->f_tw.p, ctx->f_h2c.p,
+                    ctx->f_nan.p, ctx->stream);
+    ctx->tm.kernel_launches++;
+    cudaEventRecord(ctx->ev[1], ctx->stream);
+    CU(cudaStreamSynchronize(ctx->stream));
+    CU(cudaGetLastError());
+    cudaEventElapsedTime(&ctx->tm.finalize_ms, ctx->ev[0], ctx->ev[1]);
+    ctx->have_final = true;
+    return CVX_OK;
+}
+
+int cvx_finalize(cvx_ctx* ctx, double* gamma_cam, double* gamma_world, double* tangent_world, double* h2_corrected_xy, int32_t* nan_flag) {
+    if (!ctx || !ctx->have_run) return fail(ctx, CVX_ERR_INVALID, "cvx_finalize: no run");
+    CU(cudaSetDevice(ctx->device));
+    const int rc = run_finalize(ctx);
+    if (rc) return rc;
+    const int64_t P = ctx->P;
+    D2H(gamma_cam, ctx->f_gc.p, P * 3, double); D2H(gamma_world, ctx->f_gw.p, P * 3, double); D2H(tangent_world, ctx->f_tw.p, P * 3, double);
+    D2H(h2_corrected_xy, ctx->f_h2c.p, P * 2, double); D2H(nan_flag, ctx->f_nan.p, P, int32_t);
+    return CVX_OK;
+}
+
+int cvx_get_device_results(cvx_ctx* ctx, cvx_device_results* out) {
+    if (!ctx || !out || !ctx->have_run) return fail(ctx, CVX_ERR_INVALID, "no run");
+    CU(cudaSetDevice(ctx->device));
+    const int rc = run_finalize(ctx);
+    if (rc) return rc;
+    out->n_pairs = ctx->P; out->n_vali_views = ctx->n_vali; out->pad = 0;
+    out->pair_h1 = ctx->p_h1.p; out->pair_h2rep = ctx->p_h2rep.p; out->pair_count = ctx->p_count.p; out->pair_supports = ctx->p_sup.p;
+    out->gamma_cam = ctx->f_gc.p; out->gamma_world = ctx->f_gw.p; out->tangent_world = ctx->f_tw.p;
+    return CVX_OK;
+}
+
+int cvx_get_timings(cvx_ctx* ctx, cvx_timings* out) {
+    if (!ctx || !out) return CVX_ERR_INVALID;
+    *out = ctx->tm;
+    return CVX_OK;
+}
+int cvx_synchronize(cvx_ctx* ctx) {
+    if (!ctx) return CVX_ERR_INVALID;
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return CVX_OK;
+}
+
+// ------------------------------------------------------------------------------------------------------------------
+// stand-alone support test (BASELINE.json config 5)
+// ------------------------------------------------------------------------------------------------------------------
+int cvx_support_problem_create(cvx_ctx* ctx, int G, const int64_t* group_off, int V, const int64_t* view_off, const double* ang31,
+                               const double* ang32, const double* cos_t, const double* sin_t, const double* wedge31, const double* wedge32,
+                               const double* tgt, double cos_thresh, double parallel_deg, cvx_support_problem** out) {
+    if (!ctx || !out || G <= 0 || V <= 0 || !group_off || !view_off) return fail(ctx, CVX_ERR_INVALID, "cvx_support_problem_create: bad arguments");
+    CU(cudaSetDevice(ctx->device));
+    cvx_support_problem* p = new cvx_support_problem();
+    p->ctx = ctx; p->G = G; p->V = V; p->H = group_off[G]; p->n_edges = view_off[V]; p->thr = cos_thresh; p->par = parallel_deg;
+    cudaStream_t st = ctx->stream;
+    const size_t NE = size_t(std::max<int64_t>(p->n_edges, 1)), H = size_t(std::max<int64_t>(p->H, 1));
+    int64_t max_edges = 1;
+    for (int v = 0; v < V; v++) max_edges = std::max(max_edges, view_off[v + 1] - view_off[v]);
+    p->bg.B = pick_bins(int(max_edges)); p->bg.BS = p->bg.B + 1; p->bg.scale = p->bg.B / 180.0;
+    CU(p->group_off.reserve(G + 1)); CU(p->view_off.reserve(V + 1)); CU(p->vali.reserve(V)); CU(p->bins.reserve(size_t(V) * p->bg.BS));
+    CU(p->support.reserve(size_t(V) * H)); CU(p->bin_tmp.reserve(NE)); CU(p->s_idx.reserve(NE));
+    CU(p->a31.reserve(NE)); CU(p->a32.reserve(NE)); CU(p->cs.reserve(NE)); CU(p->sn.reserve(NE));
+    CU(p->s_a31.reserve(NE)); CU(p->s_a32.reserve(NE)); CU(p->s_cs.reserve(NE)); CU(p->s_sn.reserve(NE));
+    CU(p->w31.reserve(size_t(V) * G)); CU(p->w32.reserve(size_t(V) * H)); CU(p->tgt.reserve(size_t(V) * H));
+    p->bg.bins = p->bins.p;
+    CU(cudaMemcpyAsync(p->group_off.p, group_off, (G + 1) * 8, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(p->view_off.p, view_off, (V + 1) * 8, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(p->a31.p, ang31, p->n_edges * 8, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(p->a32.p, ang32, p->n_edges * 8, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(p->cs.p, cos_t, p->n_edges * 8, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(p->sn.p, sin_t, p->n_edges * 8, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(p->w31.p, wedge31, size_t(V) * G * 16, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(p->w32.p, wedge32, size_t(V) * p->H * 16, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(p->tgt.p, tgt, size_t(V) * p->H * 16, cudaMemcpyHostToDevice, st));
+    CU(cudaMemsetAsync(p->bins.p, 0, size_t(V) * p->bg.BS * 4, st));
+    launch_stage_given(p->a31.p, p->a32.p, p->cs.p, p->sn.p, p->view_off.p, V, max_edges, p->bin_tmp.p, p->bg, p->s_a31.p, p->s_a32.p, p->s_cs.p,
+                       p->s_sn.p, p->s_idx.p, p->vali.p, st);
+    ctx->tm.kernel_launches += 4;
+    cudaEventCreate(&p->e0); cudaEventCreate(&p->e1);
+    CU(cudaStreamSynchronize(st));
+    CU(cudaGetLastError());
+    *out = p;
+    return CVX_OK;
+}
+
+int cvx_support_problem_run(cvx_support_problem* p, float* kernel_ms) {
+    if (!p) return CVX_ERR_INVALID;
+    cvx_ctx* ctx = p->ctx;
+    CU(cudaSetDevice(ctx->device));
+    SupportArgs a;
+    a.group_off = p->group_off.p; a.g_begin = 0; a.g_end = p->G; a.row_base = 0; a.chunk_rows = p->H;
+    a.w31 = p->w31.p; a.w31_stride = p->G; a.w32 = p->w32.p; a.tgt = p->tgt.p;
+    a.vali_view = p->vali.p; a.edge_off = p->view_off.p; a.bg = p->bg;
+    a.s_a31 = p->s_a31.p; a.s_a32 = p->s_a32.p; a.s_cs = p->s_cs.p; a.s_sn = p->s_sn.p; a.s_idx = p->s_idx.p;
+    a.cos_thresh = p->thr; a.parallel_deg = p->par; a.support = p->support.p; a.sup_stride = std::max<int64_t>(p->H, 1); a.ctr = nullptr; a.n_vali = p->V;
+    cudaEventRecord(p->e0, ctx->stream);
+    launch_support(a, ctx->stream);
+    cudaEventRecord(p->e1, ctx->stream);
+    ctx->tm.kernel_launches++;
+    CU(cudaStreamSynchronize(ctx->stream));
+    CU(cudaGetLastError());
+    float ms = 0;
+    cudaEventElapsedTime(&ms, p->e0, p->e1);
+    if (kernel_ms) *kernel_ms = ms;
+    return CVX_OK;
+}
+int cvx_support_problem_result(cvx_support_problem* p, int32_t* support) {
+    if (!p || !support) return CVX_ERR_INVALID;
+    cvx_ctx* ctx = p->ctx;
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaMemcpy(support, p->support.p, size_t(p->V) * p->H * 4, cudaMemcpyDeviceToHost));
+    return CVX_OK;
+}
+int cvx_support_problem_destroy(cvx_support_problem* p) {
+    if (!p) return CVX_ERR_INVALID;
+    cudaSetDevice(p->ctx->device);
+    p->group_off.release(); p->view_off.release(); p->vali.release(); p->bins.release(); p->support.release(); p->bin_tmp.release();
+    p->s_idx.release(); p->edge_n.release(); p->a31.release(); p->a32.release(); p->cs.release(); p->sn.release(); p->s_a31.release();
+    p->s_a32.release(); p->s_cs.release(); p->s_sn.release(); p->w31.release(); p->w32.release(); p->tgt.release();
+    cudaEventDestroy(p->e0); cudaEventDestroy(p->e1);
+    delete p;
+    return CVX_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,70 @@
+"""Multi-GPU layer of the edge-sketch path: one process per GPU, torch.distributed for the plumbing.
+
+The path shards with NO data-path collective: inside a pass every view-1 edge is independent
+(EdgeSketch_Core.cpp:209, disjoint output rows :515-523), so rank r processes a contiguous range of view-1 edges against
+its own resident copy of all views; with a fixed schedule of hypothesis view pairs the pairs themselves are dealt
+round-robin.  The only exchange is the final variable-length gather of accepted pairs + 3-D edges + tangents to rank 0,
+concatenated in rank order = ascending view-1 index, i.e. the single-GPU / CPU row order that EdgeMapping insertion and
+the output files expect.
+"""
+import numpy as np
+import torch
+import torch.distributed as dist
+
+
+def shard_range(n_items, rank, world):
+    """Contiguous, balanced [begin, end) of rank `rank` among `world` ranks (first n_items % world ranks get one more)."""
+    base, rem = divmod(int(n_items), int(world))
+    begin = rank * base + min(rank, rem)
+    return begin, begin + base + (1 if rank < rem else 0)
+
+
+def shard_pairs(pairs, rank, world):
+    """Fixed hypothesis-pair schedule dealt round-robin (configs 3/4: the schedule is known up front)."""
+    return [p for i, p in enumerate(pairs) if i % world == rank]
+
+
+class _DevArray:
+    """Exposes a raw device pointer of the C-ABI (cvx_get_device_results) through __cuda_array_interface__."""
+
+    def __init__(self, ptr, shape, typestr):
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": typestr, "data": (int(ptr), True), "version": 3, "strides": None}
+
+
+def device_tensor(ptr, shape, dtype):
+    """Zero-copy torch view of device memory owned by a cvx context (valid until its next run)."""
+    n = int(np.prod(shape))
+    if n == 0 or not ptr:
+        return torch.empty(tuple(shape), dtype=dtype, device="cuda")
+    ts = {torch.int32: "<i4", torch.float64: "<f8", torch.int64: "<i8"}[dtype]
+    return torch.as_tensor(_DevArray(ptr, shape, ts), device="cuda")
+
+
+def gather_varlen(t, group=None, dst=0):
+    """Gather first-dimension-ragged tensors to rank `dst` (concatenated in rank order).  Works on gloo (CPU tensors)
+    and nccl (CUDA tensors): all_gather of the row counts, then one padded all_gather (payload is KB-MB: latency-bound,
+    not bandwidth-bound, so one fused collective beats per-rank send/recv)."""
+    world = dist.get_world_size(group)
+    rank = dist.get_rank(group)
+    n = torch.tensor([t.shape[0]], dtype=torch.int64, device=t.device)
+    counts = [torch.zeros_like(n) for _ in range(world)]
+    dist.all_gather(counts, n, group=group)
+    counts = [int(c.item()) for c in counts]
+    mx = max(max(counts), 1)
+    pad = torch.zeros((mx,) + tuple(t.shape[1:]), dtype=t.dtype, device=t.device)
+    pad[: t.shape[0]] = t
+    bufs = [torch.empty_like(pad) for _ in range(world)]
+    dist.all_gather(bufs, pad, group=group)
+    if rank != dst:
+        return None, counts
+    return torch.cat([b[:c] for b, c in zip(bufs, counts)], 0), counts
+
+
+def gather_results(local, group=None, dst=0):
+    """local: dict name -> tensor with a common ragged first dimension (pairs).  Returns the concatenated dict on dst."""
+    out = {}
+    counts = None
+    for k in sorted(local):
+        g, counts = gather_varlen(local[k], group, dst)
+        out[k] = g
+    return (out if dist.get_rank(group) == dst else None), counts

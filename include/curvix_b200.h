@@ -1,0 +1,178 @@
+/* =====================================================================================
+ * curvix_b200.h -- C-ABI of the B200-native 3D Curvix edge-sketch hot path.
+ *
+ * The reference (C-H-Chien/3D_Curvix) has no FFI/plugin layer: its boundary is the C++ class
+ * EdgeSketch_Core as driven by cmd/main.cpp:114-170.  This header is what a re-implementation of that
+ * class binds instead of the in-process Eigen/OpenMP code; each entry point cites the reference
+ * interface it replaces (paths relative to the reference root).  Plain pointers and sizes only; the
+ * caller owns every host buffer, the context owns all device memory and its stream; variable-length
+ * outputs use a size-then-fill pattern (cvx_get_counts first).  Every function returns 0 on success
+ * or a negative cvx_status; the message is available through cvx_last_error().  Nothing here ever
+ * calls exit() or throws, and there is no CPU fallback: without a CUDA device cvx_create fails.
+ *
+ * One context per GPU, used from one host thread at a time.  Multi-GPU = one context per device, each
+ * given a disjoint [h1_begin, h1_end) range (or a disjoint set of hypothesis view pairs).
+ * ===================================================================================== */
+#ifndef CURVIX_B200_H
+#define CURVIX_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum cvx_status {
+    CVX_OK = 0,
+    CVX_ERR_INVALID = -1,    /* bad argument / call order */
+    CVX_ERR_CUDA = -2,       /* CUDA runtime error (message has the cudaError string) */
+    CVX_ERR_NO_DEVICE = -3,  /* no CUDA device: there is deliberately no CPU path */
+    CVX_ERR_NOMEM = -4
+} cvx_status;
+
+/* Run-time YAML knobs (EdgeSketch_Core.cpp:37-59) and compile-time macros (Edge_Reconst/definitions.h:14-26,54)
+ * of the reference, passed as one POD so the thresholds travel with the call. */
+typedef struct cvx_config {
+    double delta;                      /* YAML delta: edge location perturbation      EdgeSketch_Core.cpp:40 */
+    double delta_theta_deg;            /* YAML delta_theta                            EdgeSketch_Core.cpp:41 */
+    double parallel_angle_deg;         /* YAML Parallel_Epipolar_Line_Angle           EdgeSketch_Core.cpp:44 */
+    double lowes_ratio;                /* LOWES_RATIO_THRESHOLD (0.6)                 definitions.h:14 */
+    double epip_tangency_displ_thresh; /* EPIP_TANGENCY_DISPL_THRESH (3)              definitions.h:20 */
+    double location_perturbation;      /* LOCATION_PERTURBATION (0.4)                 definitions.h:21 */
+    double orient_perturbation;        /* ORIENT_PERTURBATION (0.174533)              definitions.h:22 */
+    double cluster_dist_thresh;        /* CLUSTER_DIST_THRESH (1)                     definitions.h:23 */
+    double cluster_orient_thresh_deg;  /* CLUSTER_ORIENT_THRESH (20.0)                definitions.h:24 */
+    double cluster_gauss_sigma;        /* CLUSTER_ORIENT_GAUSS_SIGMA (2.0)            definitions.h:26 */
+    double pi_truncated;               /* PI (3.1415926, truncated on purpose)        definitions.h:54 */
+    int32_t n_views;                   /* YAML Total_Num_Of_Images */
+    int32_t img_rows;                  /* YAML Image_Rows */
+    int32_t img_cols;                  /* YAML Image_Cols */
+    int32_t max_support_views;         /* YAML Max_Num_Of_Support_Views (must be >= 1) */
+    int32_t max_cluster_size;          /* MAX_CLUSTER_SIZE (10)                       definitions.h:25 */
+    int32_t reserved;
+} cvx_config;
+
+/* Sizes of the variable-length outputs of the last cvx_run_edge_sketch + run statistics. */
+typedef struct cvx_counts {
+    int64_t n_h1_total;          /* edges in hypothesis view 1 */
+    int64_t n_h1_processed;      /* H1 edges that reached validation (n >= 1) */
+    int64_t n_candidates;        /* sum of m: raw epipolar-wedge candidates        PairEdgeHypo.cpp:88-102 */
+    int64_t n_hypotheses;        /* sum of n: rows surviving epipolar correction   PairEdgeHypo.cpp:225-293 */
+    int64_t n_validations;       /* sum of n * V: the metric's unit                EdgeSketch_Core.cpp:355 */
+    int64_t n_valid_rows;        /* rows with >= max_support_views supports        EdgeSketch_Core.cpp:430-435 */
+    int64_t n_pairs;             /* accepted rows after the ratio test             EdgeSketch_Core.cpp:510-526 */
+    int64_t n_degenerate_wedges; /* wedges with != 2 border crossings or NaN (reference reads stale memory there) */
+    int64_t n_supported;         /* validations that returned a support index != -2 */
+    int64_t n_parallel;          /* validations short-circuited by is_Epipolar_Wedges_in_Parallel */
+} cvx_counts;
+
+typedef struct cvx_ctx cvx_ctx;
+
+/* Fills *c with the values of configs/3D_Curvix_ABC_NEF.yaml:4-27 and definitions.h. */
+void cvx_default_config(cvx_config* c);
+
+/* replaces EdgeSketch_Core::EdgeSketch_Core(YAML::Node)             EdgeSketch_Core.cpp:32-93 (device side) */
+int cvx_create(const cvx_config* cfg, int device, cvx_ctx** out);
+int cvx_destroy(cvx_ctx* ctx);
+const char* cvx_last_error(const cvx_ctx* ctx);
+
+/* replaces Read_Camera_Data                                         EdgeSketch_Core.cpp:95-113
+ * R: n x 9 row-major world->camera rotations; T: n x 3; K: 9 doubles (k_per_view = 0) or n x 9 (k_per_view = 1) */
+int cvx_set_cameras(cvx_ctx* ctx, int n, const double* R, const double* T, const double* K, int k_per_view);
+
+/* replaces Read_Edgels_Data / file_reader::read_All_Edgels           EdgeSketch_Core.hpp:87-90
+ * Host SoA columns of Edges/Edge_<view>_t<thr>.txt; copied to the device once and kept resident across passes.
+ * strength may be NULL (it is carried through, never computed on). */
+int cvx_set_view_edges(cvx_ctx* ctx, int view, int n, const double* x, const double* y, const double* theta,
+                       const double* strength);
+
+/* replaces Set_Hypothesis_Views_Camera + Set_Hypothesis_Views_Edgels EdgeSketch_Core.cpp:115-166
+ * Computes the per-pass constants (R21,T21,F21, per-view F/epipoles), the epipolar angles of the view-2 edges
+ * (getOreList), the wedges of the view-1 edges (getOreListBar) and stages every validation view
+ * (two epipolar angles, cos/sin of the orientation) into its angular bin grid. */
+int cvx_set_hypothesis_pair(cvx_ctx* ctx, int h1, int h2);
+
+/* replaces Run_3D_Edge_Sketch for view-1 edges [h1_begin, h1_end)    EdgeSketch_Core.cpp:168-573
+ * (h1_end < 0 means "to the last edge").  Asynchronous on the context stream until a getter is called. */
+int cvx_run_edge_sketch(cvx_ctx* ctx, int h1_begin, int h1_end);
+
+int cvx_get_counts(cvx_ctx* ctx, cvx_counts* out);
+
+/* Pass-level arrays, for parity checks: OreListdegree (E2) and OreListBardegree (E1 x 2, NaN when flagged). */
+int cvx_get_h2_angles(cvx_ctx* ctx, double* out);
+int cvx_get_h1_wedges(cvx_ctx* ctx, double* out, int32_t* flag);
+
+/* Per view-1 edge (E1 entries): m, n and the first row of the edge in the hypothesis table (-1 when n == 0). */
+int cvx_get_h1_table(cvx_ctx* ctx, int32_t* m, int32_t* n, int64_t* row_off);
+
+/* The hypothesis table (n_hypotheses rows, grouped by view-1 edge, ascending view-2 index inside a group):
+ * h2_orig = corrected(:,8), local_idx = corrected(:,9), raw_at_local = HYPO2_idx_raw(local row) (the reference's
+ * cluster-map key quirk, EdgeClusterer.cpp:216-221), (xc,yc) epipolar-corrected location, (xbar,ybar,thbar)
+ * cluster average written back to every member, label = cluster label, h2_rep = HYPO2_idx (EdgeClusterer.cpp:282),
+ * count = number of supporting validation views.  Any pointer may be NULL.   replaces hypo2_clusters (hpp:47-48) */
+int cvx_get_rows(cvx_ctx* ctx, int32_t* h1, int32_t* h2_orig, int32_t* local_idx, int32_t* raw_at_local, double* xc,
+                 double* yc, double* theta_orig, double* xbar, double* ybar, double* thbar, int32_t* label,
+                 int32_t* h2_rep, int32_t* count);
+
+/* replaces all_supported_indices (EdgeSketch_Core.hpp:160): H x V int32 row-major, -2 = no support */
+int cvx_get_support_matrix(cvx_ctx* ctx, int32_t* out);
+/* Intermediates of the validation stage (debug/parity): wedge31 (E1 x V x 2), wedge32 and tgt (H x V x 2). */
+int cvx_get_intermediates(cvx_ctx* ctx, double* wedge31, double* wedge32, double* tgt);
+
+/* Rows with count >= max_support_views, ascending (h1,row): the input of the reference's std::sort + ratio test
+ * (EdgeSketch_Core.cpp:480-508); selected = passes count > lowes_ratio * max. */
+int cvx_get_valid_rows(cvx_ctx* ctx, int32_t* h1, int32_t* row, int32_t* count, int32_t* selected);
+
+/* replaces paired_edge / paired_edge_final (EdgeSketch_Core.cpp:510-526,582-601): accepted rows in ascending
+ * (h1, row) order; supports is P x V.  The reference's within-edge order (std::sort by count) and its per-edge
+ * capacity of n_views rows are applied by the host shim from cvx_get_valid_rows. */
+int cvx_get_pairs(cvx_ctx* ctx, int32_t* h1, int32_t* h2rep, int32_t* row, int32_t* count, int32_t* supports);
+
+/* The reference's host-side ordering of the accepted rows of each view-1 edge (EdgeSketch_Core.cpp:480-526): std::sort of
+ * the valid rows by support count (descending; literally std::sort, so libstdc++'s unstable order above 16 elements is
+ * reproduced), ratio-test filter, capacity of n_views rows per edge.  Writes indices into the arrays of cvx_get_pairs /
+ * cvx_finalize in paired_edge order; idx must hold n_pairs entries; *n_out <= n_pairs (smaller only if the capacity cut). */
+int cvx_get_reference_order(cvx_ctx* ctx, int64_t* idx, int64_t* n_out);
+
+/* replaces Finalize_Edge_Pairs_and_Reconstruct_3D_Edges (geometry) + the transform of Stack_3D_Edges
+ * EdgeSketch_Core.cpp:625-676,742-748.  P x 3 each, h2_corrected_xy P x 2, nan_flag P (bit0 NaN point -> zero row,
+ * bit1 representative dropped by the correction).  Any pointer may be NULL. */
+int cvx_finalize(cvx_ctx* ctx, double* gamma_cam, double* gamma_world, double* tangent_world,
+                 double* h2_corrected_xy, int32_t* nan_flag);
+
+/* Device-resident results of the last run/finalize for a device-to-device gather (NCCL): pointers stay valid
+ * until the next cvx_run_edge_sketch on this context. */
+typedef struct cvx_device_results {
+    int64_t n_pairs; int32_t n_vali_views; int32_t pad;
+    const int32_t* pair_h1; const int32_t* pair_h2rep; const int32_t* pair_count; const int32_t* pair_supports;
+    const double* gamma_cam; const double* gamma_world; const double* tangent_world;
+} cvx_device_results;
+int cvx_get_device_results(cvx_ctx* ctx, cvx_device_results* out);
+
+/* Timing of the last phases on the context stream (CUDA events, milliseconds). */
+typedef struct cvx_timings {
+    float set_pair_ms; float run_ms; float finalize_ms;
+    float form_ms; float reproject_ms; float support_ms; float select_ms;
+    int32_t kernel_launches; int32_t pad;
+} cvx_timings;
+int cvx_get_timings(cvx_ctx* ctx, cvx_timings* out);
+int cvx_synchronize(cvx_ctx* ctx);
+
+/* ---- stand-alone support test on pre-formed hypotheses (BASELINE.json config 5) -------------------------
+ * replaces the inner body of LOOP 2/3: getHYPO2_idx_Ore x2 + set_intersection + getSupportIdx
+ * (EdgeSketch_Core.cpp:348-384, getSupportedEdgels.cpp:32-47).  Hypotheses are grouped (one group = one
+ * view-1 edge, sharing wedge31).  Per-view edge arrays are concatenated with offsets view_off[V+1].
+ * wedge31: V x G x 2, wedge32 and tgt: V x H x 2 (view-major), support out: V x H. */
+typedef struct cvx_support_problem cvx_support_problem;
+int cvx_support_problem_create(cvx_ctx* ctx, int n_groups, const int64_t* group_off, int n_vali, const int64_t* view_off,
+                               const double* ang31, const double* ang32, const double* cos_t, const double* sin_t,
+                               const double* wedge31, const double* wedge32, const double* tgt, double cos_thresh,
+                               double parallel_deg, cvx_support_problem** out);
+int cvx_support_problem_run(cvx_support_problem* p, float* kernel_ms);
+int cvx_support_problem_result(cvx_support_problem* p, int32_t* support);
+int cvx_support_problem_destroy(cvx_support_problem* p);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CURVIX_B200_H */

@@ -1003,6 +1003,22 @@ void orc_tangent3d(const double* e1, const double* e2, const double* K1, const d
     std::memcpy(out3, w.v, 24);
 }
 
+int orc_correct_one(const orc_config* cfg, const double* F21, double x1, double y1, double x2, double y2, double th2, double* cx, double* cy) {
+    M3 F; std::memcpy(F.m, F21, 72);
+    double c[3];
+    epip_line_coeffs(F, x1, y1, c);
+    return correct_one(c, x2, y2, th2, *cfg, cx, cy, nullptr) ? 1 : 0;
+}
+void orc_reproject_tangent(double x1, double y1, double th1, double x2, double y2, double th2, const double* K1, const double* K2,
+                           const double* R21, const double* T21, const double* R31, const double* T31, double* t3) {
+    M3 k1, k2, r21, r31; V3 t21, t31;
+    std::memcpy(k1.m, K1, 72); std::memcpy(k2.m, K2, 72); std::memcpy(r21.m, R21, 72); std::memcpy(r31.m, R31, 72);
+    std::memcpy(t21.v, T21, 24); std::memcpy(t31.v, T31, 24);
+    reproject_tangent(x1, y1, th1, x2, y2, th2, inverse3(k1), inverse3(k2), r21, t21, r31, t31, &t3[0], &t3[1]);
+}
+double orc_ore_angle(double x, double y, double ex, double ey) { V3 e = {{ex, ey, 1.0}}; return ore_angle(x, y, e); }
+void orc_inverse3(const double* A, double* out) { M3 a; std::memcpy(a.m, A, 72); M3 r = inverse3(a); std::memcpy(out, r.m, 72); }
+
 // Stand-alone support test over pre-formed hypotheses (BASELINE.json config 5).  Follows
 // EdgeSketch_Core.cpp:348-384 + getSupportedEdgels.cpp:32-47 with the per-view lists given.
 int orc_support_test(int n_groups, const int64_t* group_off, int V, const int64_t* view_off, const double* ang31,

@@ -101,6 +101,13 @@ void  orc_triangulate(const double* p1, const double* p2, const double* R21, con
                       double* out3);
 void  orc_tangent3d(const double* e1 /*x y th*/, const double* e2, const double* K1, const double* K2,
                     const double* R1, const double* T1, const double* R2, const double* T2, double* out3);
+int   orc_correct_one(const orc_config* cfg, const double* F21, double x1, double y1, double x2, double y2, double th2,
+                      double* cx, double* cy);
+void  orc_reproject_tangent(double x1, double y1, double th1, double x2, double y2, double th2, const double* K1,
+                            const double* K2, const double* R21, const double* T21, const double* R31, const double* T31,
+                            double* t3);
+double orc_ore_angle(double x, double y, double ex, double ey);
+void  orc_inverse3(const double* A, double* out);
 // stand-alone support test on pre-formed hypotheses (cfg5): group CSR, per-view staged edges
 // ang31/ang32/cs/sn: per view concatenated arrays with offsets view_off[V+1]
 int   orc_support_test(int n_groups, const int64_t* group_off, int V, const int64_t* view_off, const double* ang31,
