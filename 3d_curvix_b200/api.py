@@ -15,7 +15,7 @@ SYMBOLS = [
     "cvx_default_config", "cvx_create", "cvx_destroy", "cvx_last_error", "cvx_set_cameras", "cvx_set_view_edges",
     "cvx_set_hypothesis_pair", "cvx_run_edge_sketch", "cvx_get_counts", "cvx_get_h2_angles", "cvx_get_h1_wedges",
     "cvx_get_h1_table", "cvx_get_rows", "cvx_get_support_matrix", "cvx_get_intermediates", "cvx_get_valid_rows",
-    "cvx_get_pairs", "cvx_get_reference_order", "cvx_finalize", "cvx_get_device_results", "cvx_get_timings", "cvx_synchronize",
+    "cvx_get_pairs", "cvx_get_reference_order", "cvx_finalize", "cvx_get_device_results", "cvx_get_timings", "cvx_synchronize", "cvx_get_stream",
     "cvx_support_problem_create", "cvx_support_problem_run", "cvx_support_problem_result", "cvx_support_problem_destroy",
 ]
 
@@ -35,7 +35,7 @@ class CvxConfig(C.Structure):
 class CvxCounts(C.Structure):
     _fields_ = [(n, C.c_int64) for n in (
         "n_h1_total", "n_h1_processed", "n_candidates", "n_hypotheses", "n_validations", "n_valid_rows",
-        "n_pairs", "n_degenerate_wedges", "n_supported", "n_parallel")]
+        "n_pairs", "n_degenerate_wedges", "n_supported", "n_parallel", "n_inliers")]
 
     def as_dict(self):
         return {n: int(getattr(self, n)) for n, _ in self._fields_}
@@ -164,6 +164,12 @@ class EdgeSketch:
 
     def synchronize(self):
         self._ck(self.lib.cvx_synchronize(self.h))
+
+    def stream_ptr(self):
+        """cudaStream_t of the context as an integer (for torch.cuda.ExternalStream)."""
+        s = C.c_void_p()
+        self._ck(self.lib.cvx_get_stream(self.h, C.byref(s)))
+        return int(s.value or 0)
 
     def h2_angles(self):
         out = np.empty(self.n_edges[self.h2])

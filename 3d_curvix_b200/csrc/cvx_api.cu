@@ -505,7 +505,7 @@ int cvx_run_edge_sketch(cvx_ctx* ctx, int h1_begin, int h1_end) {
     cvx_counts& c = ctx->counts;
     std::memset(&c, 0, sizeof(c));
     c.n_h1_total = E1; c.n_hypotheses = H; c.n_validations = H * V; c.n_valid_rows = ctx->n_valid; c.n_pairs = ctx->P;
-    c.n_degenerate_wedges = int64_t(hc.n_degenerate); c.n_supported = int64_t(hc.n_supported); c.n_parallel = int64_t(hc.n_parallel);
+    c.n_degenerate_wedges = int64_t(hc.n_degenerate); c.n_supported = int64_t(hc.n_supported); c.n_parallel = int64_t(hc.n_parallel); c.n_inliers = int64_t(hc.n_inliers);
     for (int i = h1_begin; i < h1_end; i++) if (ctx->h_row_off[i + 1] > ctx->h_row_off[i]) c.n_h1_processed++;
     c.n_candidates = -1;   // filled lazily by cvx_get_counts (needs m[])
     ctx->have_run = true; ctx->have_final = false;
@@ -687,6 +687,11 @@ int cvx_get_device_results(cvx_ctx* ctx, cvx_device_results* out) {
 int cvx_get_timings(cvx_ctx* ctx, cvx_timings* out) {
     if (!ctx || !out) return CVX_ERR_INVALID;
     *out = ctx->tm;
+    return CVX_OK;
+}
+int cvx_get_stream(cvx_ctx* ctx, void** stream) {
+    if (!ctx || !stream) return CVX_ERR_INVALID;
+    *stream = (void*)ctx->stream;
     return CVX_OK;
 }
 int cvx_synchronize(cvx_ctx* ctx) {

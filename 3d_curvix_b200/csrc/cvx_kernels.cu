@@ -456,7 +456,7 @@ __global__ void __launch_bounds__(SUP_WARPS * 32) k_support(const __grid_constan
         end = bins[b1];
     }
     const unsigned lt = lanemask_lt();
-    unsigned long long n_sup = 0, n_par = 0, n_deg = 0;
+    unsigned long long n_sup = 0, n_par = 0, n_deg = 0, n_inl = 0;
     for (int64_t rc = r_beg; rc < r_end; rc += 32) {
         const int64_t r = rc + lane;
         const bool valid = r < r_end;
@@ -498,6 +498,7 @@ __global__ void __launch_bounds__(SUP_WARPS * 32) k_support(const __grid_constan
                     for (int k = 0; k < cnt; k++) {
                         const double a32 = sm_a32[wid][k];
                         if (a32 > w2.x && a32 < w2.y) {
+                            n_inl++;
                             const double d = fabs(tg.x * sm_cs[wid][k] + tg.y * sm_sn[wid][k]);
                             const int idx = sm_idx[wid][k];
                             if (d >= a.cos_thresh && (d > best || (d == best && bidx != -2 && idx < bidx))) { best = d; bidx = idx; }
@@ -516,10 +517,12 @@ __global__ void __launch_bounds__(SUP_WARPS * 32) k_support(const __grid_constan
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
         n_sup += __shfl_xor_sync(FULL, n_sup, o); n_par += __shfl_xor_sync(FULL, n_par, o); n_deg += __shfl_xor_sync(FULL, n_deg, o);
+        n_inl += __shfl_xor_sync(FULL, n_inl, o);
     }
     if (lane == 0 && a.ctr) {
         if (n_sup) atomicAdd(&a.ctr->n_supported, n_sup);
         if (n_par) atomicAdd(&a.ctr->n_parallel, n_par);
+        if (n_inl) atomicAdd(&a.ctr->n_inliers, n_inl);
         (void)n_deg;
     }
 }

@@ -23,7 +23,7 @@ struct EdgeArena {
 };
 
 struct DevCounters {
-    unsigned long long n_degenerate, n_supported, n_parallel, pad;
+    unsigned long long n_degenerate, n_supported, n_parallel, n_inliers;
 };
 
 // Hypothesis table (one row per epipolar-corrected candidate), grouped by view-1 edge.

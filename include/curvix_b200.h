@@ -64,6 +64,7 @@ typedef struct cvx_counts {
     int64_t n_degenerate_wedges; /* wedges with != 2 border crossings or NaN (reference reads stale memory there) */
     int64_t n_supported;         /* validations that returned a support index != -2 */
     int64_t n_parallel;          /* validations short-circuited by is_Epipolar_Wedges_in_Parallel */
+    int64_t n_inliers;           /* sum over validations of |wedge31 ∩ wedge32| (edges that reached getSupportIdx) */
 } cvx_counts;
 
 typedef struct cvx_ctx cvx_ctx;
@@ -157,6 +158,9 @@ typedef struct cvx_timings {
 } cvx_timings;
 int cvx_get_timings(cvx_ctx* ctx, cvx_timings* out);
 int cvx_synchronize(cvx_ctx* ctx);
+/* The cudaStream_t every call of this context is ordered on (lets the caller record its own CUDA events / order its own
+ * copies against the context's work).  No reference counterpart: the reference is single-process host code. */
+int cvx_get_stream(cvx_ctx* ctx, void** stream);
 
 /* ---- stand-alone support test on pre-formed hypotheses (BASELINE.json config 5) -------------------------
  * replaces the inner body of LOOP 2/3: getHYPO2_idx_Ore x2 + set_intersection + getSupportIdx
