@@ -14,7 +14,7 @@ LIB_PATH = os.path.join(_HERE, "libcurvix_b200.so")
 SYMBOLS = [
     "cvx_default_config", "cvx_create", "cvx_destroy", "cvx_last_error", "cvx_set_cameras", "cvx_set_view_edges",
     "cvx_set_hypothesis_pair", "cvx_run_edge_sketch", "cvx_get_counts", "cvx_get_h2_angles", "cvx_get_h1_wedges",
-    "cvx_get_h1_table", "cvx_get_rows", "cvx_get_support_matrix", "cvx_get_intermediates", "cvx_get_valid_rows",
+    "cvx_get_h1_table", "cvx_get_rows", "cvx_get_support_matrix", "cvx_set_keep_intermediates", "cvx_get_intermediates", "cvx_get_valid_rows",
     "cvx_get_pairs", "cvx_get_reference_order", "cvx_finalize", "cvx_get_device_results", "cvx_get_timings", "cvx_synchronize", "cvx_get_stream",
     "cvx_support_problem_create", "cvx_support_problem_run", "cvx_support_problem_result", "cvx_support_problem_destroy",
 ]
@@ -35,7 +35,7 @@ class CvxConfig(C.Structure):
 class CvxCounts(C.Structure):
     _fields_ = [(n, C.c_int64) for n in (
         "n_h1_total", "n_h1_processed", "n_candidates", "n_hypotheses", "n_validations", "n_valid_rows",
-        "n_pairs", "n_degenerate_wedges", "n_supported", "n_parallel", "n_inliers")]
+        "n_pairs", "n_degenerate_wedges", "n_supported", "n_parallel", "n_inliers", "n_unique_hypotheses")]
 
     def as_dict(self):
         return {n: int(getattr(self, n)) for n, _ in self._fields_}
@@ -43,7 +43,7 @@ class CvxCounts(C.Structure):
 
 class CvxTimings(C.Structure):
     _fields_ = [("set_pair_ms", C.c_float), ("run_ms", C.c_float), ("finalize_ms", C.c_float), ("form_ms", C.c_float),
-                ("reproject_ms", C.c_float), ("support_ms", C.c_float), ("select_ms", C.c_float),
+                ("prep_ms", C.c_float), ("validate_ms", C.c_float), ("select_ms", C.c_float),
                 ("kernel_launches", C.c_int32), ("pad", C.c_int32)]
 
     def as_dict(self):
@@ -203,6 +203,9 @@ class EdgeSketch:
         out = np.empty((H, self.V), np.int32)
         self._ck(self.lib.cvx_get_support_matrix(self.h, _vp(out)))
         return out
+
+    def keep_intermediates(self, on=True):
+        self._ck(self.lib.cvx_set_keep_intermediates(self.h, 1 if on else 0))
 
     def intermediates(self):
         H = self.counts()["n_hypotheses"]

@@ -114,7 +114,7 @@ struct cvx_ctx {
     PassConst pc;
     std::vector<int32_t> vali_views;
     DevBuf<ViewConst> d_vc;
-    DevBuf<int32_t> d_vali, d_bins;
+    DevBuf<int32_t> d_vali, d_bins1, d_bins2;
     BinGrid bg = {};
     DevBuf<double> d_ang2;
     DevBuf<double2> d_wedge_h1;
@@ -122,14 +122,18 @@ struct cvx_ctx {
     // run
     bool have_run = false, have_final = false;
     int run_begin = 0, run_end = 0;
-    DevBuf<int32_t> d_m, d_n, d_nvalid, d_nsel;
-    DevBuf<int64_t> d_row_off, d_valid_off, d_pair_off;
-    int64_t H = 0, n_valid = 0, P = 0;
+    DevBuf<int32_t> d_m, d_n, d_ncl, d_nvalid, d_nsel;
+    DevBuf<int64_t> d_row_off, d_u_off, d_valid_off, d_pair_off;
+    int64_t H = 0, U = 0, n_valid = 0, P = 0;
     // row table storage
-    DevBuf<int32_t> r_h1, r_h2orig, r_local, r_rawat, r_label, r_h2rep, r_count, r_flags;
+    DevBuf<int32_t> r_h1, r_h2orig, r_local, r_rawat, r_label, r_h2rep, r_count, r_flags, r_urank, r_row_u;
     DevBuf<double> r_xc, r_yc, r_th, r_xbar, r_ybar, r_thbar, r_thn, r_orient;
+    // unique-hypothesis table (one entry per cluster)
+    DevBuf<int32_t> u_h1, u_row, u_mult, u_count;
+    DevBuf<double2> u_xy;
+    DevBuf<double4> u_geom;
     DevBuf<double2> d_w31, d_w32, d_tgt;
-    int64_t inter_rows = 0;   // rows covered by d_w32/d_tgt (== H when the run was not chunked)
+    bool keep_inter = false, have_inter = false;   // wedge32 / tangent of every (unique hypothesis, view): parity debugging only
     DevBuf<int32_t> d_support, d_support_t;
     DevBuf<DevCounters> d_ctr;
     DevBuf<int32_t> v_h1, v_row, v_count, v_sel, p_h1, p_h2rep, p_row, p_count, p_sup, f_nan;
@@ -138,17 +142,16 @@ struct cvx_ctx {
     cvx_counts counts;
     cvx_timings tm;
     cudaEvent_t ev[8];
-    size_t inter_budget_bytes = size_t(12) << 30;
 };
 
 struct cvx_support_problem {
     cvx_ctx* ctx;
     int G, V;
     int64_t H, n_edges;
-    DevBuf<int64_t> group_off, view_off;
-    DevBuf<int32_t> vali, bins, support, bin_tmp, s_idx, edge_n;
-    DevBuf<double> a31, a32, cs, sn, s_a31, s_a32, s_cs, s_sn;
-    DevBuf<double2> w31, w32, tgt;
+    DevBuf<int64_t> view_off;
+    DevBuf<int32_t> bins1, bins2, support, bin1, bin2, idx1, idx2, row_group;
+    DevBuf<double> a31, a32, cs, sn;
+    DevBuf<double2> ang1, tan1, ang2, tan2, w31, w32, tgt;
     BinGrid bg;
     double thr, par;
     cudaEvent_t e0, e1;
@@ -170,31 +173,42 @@ int fail(cvx_ctx* c, int code, const std::string& msg) {
 RowTable row_table(cvx_ctx* c) {
     RowTable rt;
     rt.h1 = c->r_h1.p; rt.h2orig = c->r_h2orig.p; rt.local = c->r_local.p; rt.rawat = c->r_rawat.p; rt.label = c->r_label.p;
-    rt.h2rep = c->r_h2rep.p; rt.count = c->r_count.p; rt.flags = c->r_flags.p;
+    rt.h2rep = c->r_h2rep.p; rt.count = c->r_count.p; rt.flags = c->r_flags.p; rt.urank = c->r_urank.p; rt.row_u = c->r_row_u.p;
     rt.xc = c->r_xc.p; rt.yc = c->r_yc.p; rt.th = c->r_th.p; rt.xbar = c->r_xbar.p; rt.ybar = c->r_ybar.p; rt.thbar = c->r_thbar.p;
     rt.thn = c->r_thn.p; rt.orient = c->r_orient.p;
     return rt;
 }
 
+template <typename T>
+cudaError_t regrow(T*& p, size_t keep, size_t cap, cudaStream_t st) {   // new allocation of cap elements, first `keep` copied over
+    T* q = nullptr;
+    cudaError_t e = cudaMalloc(&q, cap * sizeof(T));
+    if (e != cudaSuccess) return e;
+    if (p && keep) e = cudaMemcpyAsync(q, p, keep * sizeof(T), cudaMemcpyDeviceToDevice, st);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    if (p) cudaFree(p);
+    p = q;
+    return e;
+}
+void free_arena(EdgeArena& ea) {
+    void* ps[] = {ea.x, ea.y, ea.th, ea.cs, ea.sn, ea.ang, ea.bin1, ea.bin2, ea.ix1.ang, ea.ix1.tan, ea.ix1.idx, ea.ix2.ang, ea.ix2.tan, ea.ix2.idx};
+    for (void* p : ps) if (p) cudaFree(p);
+    int32_t *b1 = ea.ix1.bins, *b2 = ea.ix2.bins;   // owned by DevBufs
+    ea = EdgeArena{};
+    ea.ix1.bins = b1; ea.ix2.bins = b2;
+}
 int grow_arena(cvx_ctx* ctx, size_t need) {
     if (need <= ctx->arena_cap) return CVX_OK;
     size_t cap = std::max(need, ctx->arena_cap * 2);
     cap = (cap + 1023) & ~size_t(1023);
-    EdgeArena n = {};
-    double** dp_new[] = {&n.x, &n.y, &n.th, &n.cs, &n.sn, &n.a31, &n.a32, &n.s_a31, &n.s_a32, &n.s_cs, &n.s_sn};
-    double** dp_old[] = {&ctx->ea.x, &ctx->ea.y, &ctx->ea.th, &ctx->ea.cs, &ctx->ea.sn, &ctx->ea.a31, &ctx->ea.a32, &ctx->ea.s_a31,
-                         &ctx->ea.s_a32, &ctx->ea.s_cs, &ctx->ea.s_sn};
-    for (int k = 0; k < 11; k++) {
-        CU(cudaMalloc(dp_new[k], cap * sizeof(double)));
-        if (k < 5 && ctx->arena_used) CU(cudaMemcpyAsync(*dp_new[k], *dp_old[k], ctx->arena_used * sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream));
-    }
-    CU(cudaMalloc(&n.bin, cap * sizeof(int32_t)));
-    CU(cudaMalloc(&n.s_idx, cap * sizeof(int32_t)));
-    CU(cudaStreamSynchronize(ctx->stream));
-    for (int k = 0; k < 11; k++) if (*dp_old[k]) cudaFree(*dp_old[k]);
-    if (ctx->ea.bin) cudaFree(ctx->ea.bin);
-    if (ctx->ea.s_idx) cudaFree(ctx->ea.s_idx);
-    ctx->ea = n;
+    EdgeArena& ea = ctx->ea;
+    const size_t used = ctx->arena_used;
+    cudaStream_t st = ctx->stream;
+    CU(regrow(ea.x, used, cap, st)); CU(regrow(ea.y, used, cap, st)); CU(regrow(ea.th, used, cap, st));
+    CU(regrow(ea.cs, used, cap, st)); CU(regrow(ea.sn, used, cap, st));
+    CU(regrow(ea.ang, 0, cap, st)); CU(regrow(ea.bin1, 0, cap, st)); CU(regrow(ea.bin2, 0, cap, st));
+    CU(regrow(ea.ix1.ang, 0, cap, st)); CU(regrow(ea.ix1.tan, 0, cap, st)); CU(regrow(ea.ix1.idx, 0, cap, st));
+    CU(regrow(ea.ix2.ang, 0, cap, st)); CU(regrow(ea.ix2.tan, 0, cap, st)); CU(regrow(ea.ix2.idx, 0, cap, st));
     ctx->arena_cap = cap;
     return CVX_OK;
 }
@@ -243,7 +257,7 @@ int cvx_create(const cvx_config* cfg, int device, cvx_ctx** out) {
     ctx->edge_off.assign(cfg->n_views, 0); ctx->edge_n.assign(cfg->n_views, 0); ctx->edge_cap.assign(cfg->n_views, 0);
     std::memset(&ctx->counts, 0, sizeof(ctx->counts));
     std::memset(&ctx->tm, 0, sizeof(ctx->tm));
-    if (const char* b = getenv("CVX_INTER_BUDGET_MB")) ctx->inter_budget_bytes = size_t(atoll(b)) << 20;
+    if (const char* b = getenv("CVX_KEEP_INTERMEDIATES")) ctx->keep_inter = atoi(b) != 0;
     if (cudaSetDevice(device) != cudaSuccess || cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) {
         delete ctx;
         return CVX_ERR_CUDA;
@@ -258,21 +272,21 @@ int cvx_destroy(cvx_ctx* ctx) {
     if (!ctx) return CVX_ERR_INVALID;
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
-    double* dp[] = {ctx->ea.x, ctx->ea.y, ctx->ea.th, ctx->ea.cs, ctx->ea.sn, ctx->ea.a31, ctx->ea.a32, ctx->ea.s_a31, ctx->ea.s_a32, ctx->ea.s_cs, ctx->ea.s_sn};
-    for (double* p : dp) if (p) cudaFree(p);
-    if (ctx->ea.bin) cudaFree(ctx->ea.bin);
-    if (ctx->ea.s_idx) cudaFree(ctx->ea.s_idx);
-    ctx->d_edge_off.release(); ctx->d_edge_n.release(); ctx->d_vc.release(); ctx->d_vali.release(); ctx->d_bins.release();
-    ctx->d_ang2.release(); ctx->d_wedge_h1.release(); ctx->d_wflag_h1.release(); ctx->d_m.release(); ctx->d_n.release();
-    ctx->d_nvalid.release(); ctx->d_nsel.release(); ctx->d_row_off.release(); ctx->d_valid_off.release(); ctx->d_pair_off.release();
-    DevBuf<int32_t>* ib[] = {&ctx->r_h1, &ctx->r_h2orig, &ctx->r_local, &ctx->r_rawat, &ctx->r_label, &ctx->r_h2rep, &ctx->r_count, &ctx->r_flags,
+    free_arena(ctx->ea);
+    DevBuf<int32_t>* ib[] = {&ctx->d_edge_n, &ctx->d_vali, &ctx->d_bins1, &ctx->d_bins2, &ctx->d_wflag_h1, &ctx->d_m, &ctx->d_n, &ctx->d_ncl,
+                             &ctx->d_nvalid, &ctx->d_nsel, &ctx->r_h1, &ctx->r_h2orig, &ctx->r_local, &ctx->r_rawat, &ctx->r_label, &ctx->r_h2rep,
+                             &ctx->r_count, &ctx->r_flags, &ctx->r_urank, &ctx->r_row_u, &ctx->u_h1, &ctx->u_row, &ctx->u_mult, &ctx->u_count,
                              &ctx->d_support, &ctx->d_support_t, &ctx->v_h1, &ctx->v_row, &ctx->v_count, &ctx->v_sel, &ctx->p_h1, &ctx->p_h2rep,
                              &ctx->p_row, &ctx->p_count, &ctx->p_sup, &ctx->f_nan};
     for (auto* b : ib) b->release();
-    DevBuf<double>* db[] = {&ctx->r_xc, &ctx->r_yc, &ctx->r_th, &ctx->r_xbar, &ctx->r_ybar, &ctx->r_thbar, &ctx->r_thn, &ctx->r_orient,
+    DevBuf<int64_t>* lb[] = {&ctx->d_edge_off, &ctx->d_row_off, &ctx->d_u_off, &ctx->d_valid_off, &ctx->d_pair_off};
+    for (auto* b : lb) b->release();
+    DevBuf<double>* db[] = {&ctx->d_ang2, &ctx->r_xc, &ctx->r_yc, &ctx->r_th, &ctx->r_xbar, &ctx->r_ybar, &ctx->r_thbar, &ctx->r_thn, &ctx->r_orient,
                             &ctx->f_gc, &ctx->f_gw, &ctx->f_tw, &ctx->f_h2c};
     for (auto* b : db) b->release();
-    ctx->d_w31.release(); ctx->d_w32.release(); ctx->d_tgt.release(); ctx->d_ctr.release();
+    DevBuf<double2>* d2[] = {&ctx->d_wedge_h1, &ctx->u_xy, &ctx->d_w31, &ctx->d_w32, &ctx->d_tgt};
+    for (auto* b : d2) b->release();
+    ctx->u_geom.release(); ctx->d_vc.release(); ctx->d_ctr.release();
     for (auto& e : ctx->ev) cudaEventDestroy(e);
     cudaStreamDestroy(ctx->stream);
     delete ctx;
@@ -370,8 +384,8 @@ int cvx_set_hypothesis_pair(cvx_ctx* ctx, int h1, int h2) {
     CU(cudaMemcpyAsync(ctx->d_vali.p, ctx->vali_views.data(), V * sizeof(int32_t), cudaMemcpyHostToDevice, ctx->stream));
     // ---- stage every validation view into its bin grid (hoisted getOreListVali + cos/sin, EdgeSketch_Core.cpp:315-342)
     ctx->bg.B = pick_bins(max_edges); ctx->bg.BS = ctx->bg.B + 1; ctx->bg.scale = ctx->bg.B / 180.0;
-    CU(ctx->d_bins.reserve(size_t(V) * ctx->bg.BS));
-    ctx->bg.bins = ctx->d_bins.p;
+    CU(ctx->d_bins1.reserve(size_t(std::max(V, 1)) * ctx->bg.BS)); CU(ctx->d_bins2.reserve(size_t(std::max(V, 1)) * ctx->bg.BS));
+    ctx->ea.ix1.bins = ctx->d_bins1.p; ctx->ea.ix2.bins = ctx->d_bins2.p;
     launch_stage_views(ctx->ea, ctx->d_edge_off.p, ctx->d_edge_n.p, ctx->d_vali.p, V, max_edges, ctx->d_vc.p, ctx->bg, ctx->stream,
                        &ctx->tm.kernel_launches);
     // ---- Set_Hypothesis_Views_Edgels, EdgeSketch_Core.cpp:145-166
@@ -388,6 +402,12 @@ int cvx_set_hypothesis_pair(cvx_ctx* ctx, int h1, int h2) {
     return CVX_OK;
 }
 
+static UniqTable uniq_table(cvx_ctx* c) {
+    UniqTable ut;
+    ut.h1 = c->u_h1.p; ut.row = c->u_row.p; ut.mult = c->u_mult.p; ut.count = c->u_count.p; ut.xy = c->u_xy.p; ut.geom = c->u_geom.p;
+    return ut;
+}
+
 int cvx_run_edge_sketch(cvx_ctx* ctx, int h1_begin, int h1_end) {
     if (!ctx || ctx->h1 < 0) return fail(ctx, CVX_ERR_INVALID, "cvx_run_edge_sketch: no hypothesis pair set");
     CU(cudaSetDevice(ctx->device));
@@ -400,10 +420,10 @@ int cvx_run_edge_sketch(cvx_ctx* ctx, int h1_begin, int h1_end) {
     const PassConst& pc = ctx->pc;
     const double *x1 = ctx->ea.x + ctx->edge_off[ctx->h1], *y1 = ctx->ea.y + ctx->edge_off[ctx->h1], *th1 = ctx->ea.th + ctx->edge_off[ctx->h1];
     const double *x2 = ctx->ea.x + ctx->edge_off[ctx->h2], *y2 = ctx->ea.y + ctx->edge_off[ctx->h2], *th2 = ctx->ea.th + ctx->edge_off[ctx->h2];
-    const int E1a = std::max(E1, 1);
-    CU(ctx->d_m.reserve(E1a)); CU(ctx->d_n.reserve(E1a)); CU(ctx->d_nvalid.reserve(E1a)); CU(ctx->d_nsel.reserve(E1a));
-    CU(ctx->d_row_off.reserve(E1a + 1)); CU(ctx->d_valid_off.reserve(E1a + 1)); CU(ctx->d_pair_off.reserve(E1a + 1));
-    CU(cudaMemsetAsync(ctx->d_m.p, 0, E1a * 4, st)); CU(cudaMemsetAsync(ctx->d_n.p, 0, E1a * 4, st));
+    const int E1a = std::max(E1, 1), Va = std::max(V, 1);
+    CU(ctx->d_m.reserve(E1a)); CU(ctx->d_n.reserve(E1a)); CU(ctx->d_ncl.reserve(E1a)); CU(ctx->d_nvalid.reserve(E1a)); CU(ctx->d_nsel.reserve(E1a));
+    CU(ctx->d_row_off.reserve(E1a + 1)); CU(ctx->d_u_off.reserve(E1a + 1)); CU(ctx->d_valid_off.reserve(E1a + 1)); CU(ctx->d_pair_off.reserve(E1a + 1));
+    CU(cudaMemsetAsync(ctx->d_m.p, 0, E1a * 4, st)); CU(cudaMemsetAsync(ctx->d_n.p, 0, E1a * 4, st)); CU(cudaMemsetAsync(ctx->d_ncl.p, 0, E1a * 4, st));
     CU(cudaMemsetAsync(ctx->d_nvalid.p, 0, E1a * 4, st)); CU(cudaMemsetAsync(ctx->d_nsel.p, 0, E1a * 4, st));
     CU(cudaMemsetAsync(ctx->d_ctr.p, 0, sizeof(DevCounters), st));
     cudaEventRecord(ctx->ev[0], st);
@@ -417,67 +437,56 @@ int cvx_run_edge_sketch(cvx_ctx* ctx, int h1_begin, int h1_end) {
     const int64_t H = ctx->h_row_off[E1];
     ctx->H = H;
     const size_t Ha = size_t(std::max<int64_t>(H, 1));
-    DevBuf<int32_t>* ib[] = {&ctx->r_h1, &ctx->r_h2orig, &ctx->r_local, &ctx->r_rawat, &ctx->r_label, &ctx->r_h2rep, &ctx->r_count, &ctx->r_flags};
+    DevBuf<int32_t>* ib[] = {&ctx->r_h1, &ctx->r_h2orig, &ctx->r_local, &ctx->r_rawat, &ctx->r_label, &ctx->r_h2rep, &ctx->r_count, &ctx->r_flags,
+                             &ctx->r_urank, &ctx->r_row_u};
     for (auto* b : ib) CU(b->reserve(Ha));
     DevBuf<double>* db[] = {&ctx->r_xc, &ctx->r_yc, &ctx->r_th, &ctx->r_xbar, &ctx->r_ybar, &ctx->r_thbar, &ctx->r_thn, &ctx->r_orient};
     for (auto* b : db) CU(b->reserve(Ha));
     RowTable rt = row_table(ctx);
-    launch_form_fill(pc, x1, y1, h1_begin, h1_end, ctx->d_wedge_h1.p, x2, y2, th2, ctx->d_ang2.p, E2, ctx->d_n.p, ctx->d_row_off.p, rt, st);
-    ctx->tm.kernel_launches++;
+    launch_form_fill(pc, x1, y1, h1_begin, h1_end, ctx->d_wedge_h1.p, x2, y2, th2, ctx->d_ang2.p, E2, ctx->d_n.p, ctx->d_row_off.p, rt,
+                     ctx->d_ncl.p, st);
+    launch_scan_i32_i64(ctx->d_ncl.p, ctx->d_u_off.p, E1, st);
+    ctx->tm.kernel_launches += 2;
     cudaEventRecord(ctx->ev[1], st);
-    // ---- validation
-    CU(ctx->d_w31.reserve(size_t(std::max(V, 1)) * E1a));
-    CU(ctx->d_support.reserve(size_t(std::max(V, 1)) * Ha));
+    int64_t U = 0;
+    CU(cudaMemcpyAsync(&U, ctx->d_u_off.p + E1, 8, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    ctx->U = U;
+    // ---- unique hypotheses (one per cluster) + wedge of the view-1 edge in every validation view
+    const size_t Ua = size_t(std::max<int64_t>(U, 1));
+    CU(ctx->u_h1.reserve(Ua)); CU(ctx->u_row.reserve(Ua)); CU(ctx->u_mult.reserve(Ua)); CU(ctx->u_count.reserve(Ua));
+    CU(ctx->u_xy.reserve(Ua)); CU(ctx->u_geom.reserve(Ua));
+    CU(ctx->d_w31.reserve(size_t(Va) * E1a));
+    CU(ctx->d_support.reserve(size_t(Va) * Ua));
+    ctx->have_inter = false;
+    if (ctx->keep_inter) { CU(ctx->d_w32.reserve(size_t(Va) * Ua)); CU(ctx->d_tgt.reserve(size_t(Va) * Ua)); ctx->have_inter = true; }
+    CU(cudaMemsetAsync(ctx->u_mult.p, 0, Ua * 4, st));
+    UniqTable ut = uniq_table(ctx);
+    launch_uniq_fill(pc, x1, y1, th1, rt, H, ctx->d_row_off.p, ctx->d_u_off.p, ut, st);
     launch_wedge31(pc, ctx->d_vc.p, x1, y1, ctx->d_n.p, h1_begin, h1_end, E1, ctx->d_w31.p, ctx->d_ctr.p, st);
+    ctx->tm.kernel_launches += 2;
+    cudaEventRecord(ctx->ev[4], st);
+    // ---- validation: reprojection + wedge + parallel test + support test, one thread per (unique hypothesis, view)
+    ValidateArgs a;
+    std::memset(&a, 0, sizeof(a));
+    a.ut = ut; a.U = U; a.x1 = x1; a.y1 = y1; a.w31 = ctx->d_w31.p; a.w31_stride = E1; a.vc = ctx->d_vc.p;
+    a.vali_view = ctx->d_vali.p; a.edge_off = ctx->d_edge_off.p; a.bg = ctx->bg; a.ix1 = ctx->ea.ix1; a.ix2 = ctx->ea.ix2;
+    a.cos_thresh = pc.cos_thresh; a.parallel_deg = pc.parallel_deg; a.delta = pc.delta; a.rows = pc.rows; a.cols = pc.cols; a.n_vali = V;
+    a.support = ctx->d_support.p; a.sup_stride = int64_t(Ua); a.ctr = ctx->d_ctr.p;
+    if (ctx->keep_inter) { a.w32_out = ctx->d_w32.p; a.tgt_out = ctx->d_tgt.p; }
+    launch_validate(pc, a, false, st);
     ctx->tm.kernel_launches++;
-    // chunk the hypothesis rows so that the per-validation intermediates (32 B each) stay under the budget
-    int64_t max_rows = int64_t(ctx->inter_budget_bytes / (size_t(std::max(V, 1)) * 32));
-    if (max_rows < 1024) max_rows = 1024;
-    float rep_ms = 0, sup_ms = 0;
-    int ha = h1_begin;
-    bool chunked = false;
-    while (ha < h1_end) {
-        int hb = ha;
-        const int64_t rbeg = ctx->h_row_off[ha];
-        while (hb < h1_end && ctx->h_row_off[hb + 1] - rbeg <= max_rows) hb++;
-        if (hb == ha) hb = ha + 1;   // a single edge larger than the budget: take it alone
-        const int64_t rend = ctx->h_row_off[hb];
-        const int64_t rows = rend - rbeg;
-        if (hb < h1_end || ha > h1_begin) chunked = true;
-        if (rows > 0) {
-            CU(ctx->d_w32.reserve(size_t(V) * rows)); CU(ctx->d_tgt.reserve(size_t(V) * rows));
-            cudaEventRecord(ctx->ev[4], st);
-            launch_reproject(pc, ctx->d_vc.p, x1, y1, th1, rt, rbeg, rend, ctx->d_w32.p, ctx->d_tgt.p, ctx->d_ctr.p, st);
-            cudaEventRecord(ctx->ev[5], st);
-            SupportArgs a;
-            a.group_off = ctx->d_row_off.p; a.g_begin = ha; a.g_end = hb; a.row_base = rbeg; a.chunk_rows = rows;
-            a.w31 = ctx->d_w31.p; a.w31_stride = E1; a.w32 = ctx->d_w32.p; a.tgt = ctx->d_tgt.p;
-            a.vali_view = ctx->d_vali.p; a.edge_off = ctx->d_edge_off.p; a.bg = ctx->bg;
-            a.s_a31 = ctx->ea.s_a31; a.s_a32 = ctx->ea.s_a32; a.s_cs = ctx->ea.s_cs; a.s_sn = ctx->ea.s_sn; a.s_idx = ctx->ea.s_idx;
-            a.cos_thresh = pc.cos_thresh; a.parallel_deg = pc.parallel_deg;
-            a.support = ctx->d_support.p; a.sup_stride = int64_t(Ha); a.ctr = ctx->d_ctr.p; a.n_vali = V;
-            launch_support(a, st);
-            cudaEventRecord(ctx->ev[6], st);
-            ctx->tm.kernel_launches += 2;
-            if (chunked) {   // per-chunk timing needs a sync; the unchunked path stays asynchronous
-                CU(cudaStreamSynchronize(st));
-                float t1 = 0, t2 = 0;
-                cudaEventElapsedTime(&t1, ctx->ev[4], ctx->ev[5]); cudaEventElapsedTime(&t2, ctx->ev[5], ctx->ev[6]);
-                rep_ms += t1; sup_ms += t2;
-            }
-            ctx->inter_rows = rows;
-        }
-        ha = hb;
-    }
-    cudaEventRecord(ctx->ev[2], st);
+    cudaEventRecord(ctx->ev[5], st);
     // ---- vote + ratio test
-    launch_select(pc, ctx->d_row_off.p, h1_begin, h1_end, ctx->d_support.p, int64_t(Ha), rt, ctx->d_nvalid.p, ctx->d_nsel.p, st);
+    launch_count_u(ctx->d_support.p, int64_t(Ua), U, V, ctx->u_count.p, st);
+    launch_select(pc, ctx->d_row_off.p, h1_begin, h1_end, ctx->u_count.p, rt, ctx->d_nvalid.p, ctx->d_nsel.p, st);
     launch_scan_i32_i64(ctx->d_nvalid.p, ctx->d_valid_off.p, E1, st);
     launch_scan_i32_i64(ctx->d_nsel.p, ctx->d_pair_off.p, E1, st);
-    ctx->tm.kernel_launches += 3;
+    ctx->tm.kernel_launches += 4;
     int64_t tot[2] = {0, 0};
     CU(cudaMemcpyAsync(&tot[0], ctx->d_valid_off.p + E1, 8, cudaMemcpyDeviceToHost, st));
     CU(cudaMemcpyAsync(&tot[1], ctx->d_pair_off.p + E1, 8, cudaMemcpyDeviceToHost, st));
+    static_assert(sizeof(DevCounters) == 4 * CVX_CTR_SLOTS * 8, "DevCounters layout");
     DevCounters hc;
     CU(cudaMemcpyAsync(&hc, ctx->d_ctr.p, sizeof(hc), cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
@@ -485,27 +494,28 @@ int cvx_run_edge_sketch(cvx_ctx* ctx, int h1_begin, int h1_end) {
     const size_t NVa = size_t(std::max<int64_t>(ctx->n_valid, 1)), Pa = size_t(std::max<int64_t>(ctx->P, 1));
     CU(ctx->v_h1.reserve(NVa)); CU(ctx->v_row.reserve(NVa)); CU(ctx->v_count.reserve(NVa)); CU(ctx->v_sel.reserve(NVa));
     CU(ctx->p_h1.reserve(Pa)); CU(ctx->p_h2rep.reserve(Pa)); CU(ctx->p_row.reserve(Pa)); CU(ctx->p_count.reserve(Pa));
-    CU(ctx->p_sup.reserve(Pa * std::max(V, 1)));
+    CU(ctx->p_sup.reserve(Pa * Va));
     launch_select_fill(ctx->d_row_off.p, h1_begin, h1_end, rt, ctx->d_valid_off.p, ctx->d_pair_off.p, ctx->v_h1.p, ctx->v_row.p, ctx->v_count.p,
                        ctx->v_sel.p, ctx->p_h1.p, ctx->p_h2rep.p, ctx->p_row.p, ctx->p_count.p, st);
-    launch_gather_supports(ctx->p_row.p, ctx->P, V, ctx->d_support.p, int64_t(Ha), ctx->p_sup.p, st);
+    launch_gather_supports(ctx->p_row.p, ctx->r_row_u.p, ctx->P, V, ctx->d_support.p, int64_t(Ua), ctx->p_sup.p, st);
     ctx->tm.kernel_launches += 2;
     cudaEventRecord(ctx->ev[3], st);
     CU(cudaStreamSynchronize(st));
     CU(cudaGetLastError());
     cudaEventElapsedTime(&ctx->tm.run_ms, ctx->ev[0], ctx->ev[3]);
     cudaEventElapsedTime(&ctx->tm.form_ms, ctx->ev[0], ctx->ev[1]);
-    cudaEventElapsedTime(&ctx->tm.select_ms, ctx->ev[2], ctx->ev[3]);
-    if (!chunked && H > 0) {
-        cudaEventElapsedTime(&rep_ms, ctx->ev[4], ctx->ev[5]); cudaEventElapsedTime(&sup_ms, ctx->ev[5], ctx->ev[6]);
-    }
-    ctx->tm.reproject_ms = rep_ms; ctx->tm.support_ms = sup_ms;
-    if (chunked) ctx->inter_rows = -1;
+    cudaEventElapsedTime(&ctx->tm.prep_ms, ctx->ev[1], ctx->ev[4]);
+    cudaEventElapsedTime(&ctx->tm.validate_ms, ctx->ev[4], ctx->ev[5]);
+    cudaEventElapsedTime(&ctx->tm.select_ms, ctx->ev[5], ctx->ev[3]);
     // ---- counts
     cvx_counts& c = ctx->counts;
     std::memset(&c, 0, sizeof(c));
     c.n_h1_total = E1; c.n_hypotheses = H; c.n_validations = H * V; c.n_valid_rows = ctx->n_valid; c.n_pairs = ctx->P;
-    c.n_degenerate_wedges = int64_t(hc.n_degenerate); c.n_supported = int64_t(hc.n_supported); c.n_parallel = int64_t(hc.n_parallel); c.n_inliers = int64_t(hc.n_inliers);
+    c.n_unique_hypotheses = U;
+    for (int k = 0; k < CVX_CTR_SLOTS; k++) {
+        c.n_degenerate_wedges += int64_t(hc.n_degenerate[k]); c.n_supported += int64_t(hc.n_supported[k]);
+        c.n_parallel += int64_t(hc.n_parallel[k]); c.n_inliers += int64_t(hc.n_inliers[k]);
+    }
     for (int i = h1_begin; i < h1_end; i++) if (ctx->h_row_off[i + 1] > ctx->h_row_off[i]) c.n_h1_processed++;
     c.n_candidates = -1;   // filled lazily by cvx_get_counts (needs m[])
     ctx->have_run = true; ctx->have_final = false;
@@ -572,32 +582,42 @@ int cvx_get_support_matrix(cvx_ctx* ctx, int32_t* out) {
     const int V = ctx->n_vali;
     if (H == 0 || V == 0) return CVX_OK;
     CU(ctx->d_support_t.reserve(size_t(H) * V));
-    launch_transpose_support(ctx->d_support.p, std::max<int64_t>(H, 1), H, V, ctx->d_support_t.p, ctx->stream);
+    launch_expand_support(ctx->d_support.p, std::max<int64_t>(ctx->U, 1), ctx->r_row_u.p, H, V, ctx->d_support_t.p, ctx->stream);
     ctx->tm.kernel_launches++;
     CU(cudaStreamSynchronize(ctx->stream));
     D2H(out, ctx->d_support_t.p, H * V, int32_t);
     return CVX_OK;
 }
+int cvx_set_keep_intermediates(cvx_ctx* ctx, int on) {
+    if (!ctx) return CVX_ERR_INVALID;
+    ctx->keep_inter = on != 0;
+    return CVX_OK;
+}
 int cvx_get_intermediates(cvx_ctx* ctx, double* wedge31, double* wedge32, double* tgt) {
     if (!ctx || !ctx->have_run) return fail(ctx, CVX_ERR_INVALID, "no run");
-    if (ctx->inter_rows != ctx->H && ctx->H > 0) return fail(ctx, CVX_ERR_INVALID, "intermediates unavailable: the run was chunked");
+    if ((wedge32 || tgt) && !ctx->have_inter && ctx->H > 0)
+        return fail(ctx, CVX_ERR_INVALID, "intermediates were not kept: call cvx_set_keep_intermediates(ctx, 1) before the run");
     CU(cudaSetDevice(ctx->device));
     const int E1 = ctx->edge_n[ctx->h1], V = ctx->n_vali;
-    const int64_t H = ctx->H;
-    // device layout is view-major; the ABI returns [E1][V][2] and [H][V][2]
+    const int64_t H = ctx->H, U = ctx->U;
+    // device layout is view-major over unique hypotheses; the ABI returns [E1][V][2] and [H][V][2]
     if (wedge31) {
         std::vector<double> t(size_t(V) * E1 * 2);
         CU(cudaMemcpy(t.data(), ctx->d_w31.p, t.size() * 8, cudaMemcpyDeviceToHost));
         for (int v = 0; v < V; v++) for (int i = 0; i < E1; i++) for (int k = 0; k < 2; k++)
             wedge31[(size_t(i) * V + v) * 2 + k] = t[(size_t(v) * E1 + i) * 2 + k];
     }
-    for (int which = 0; which < 2; which++) {
-        double* dst = which ? tgt : wedge32;
-        if (!dst || H == 0) continue;
-        std::vector<double> t(size_t(V) * H * 2);
-        CU(cudaMemcpy(t.data(), which ? (void*)ctx->d_tgt.p : (void*)ctx->d_w32.p, t.size() * 8, cudaMemcpyDeviceToHost));
-        for (int v = 0; v < V; v++) for (int64_t r = 0; r < H; r++) for (int k = 0; k < 2; k++)
-            dst[(size_t(r) * V + v) * 2 + k] = t[(size_t(v) * H + r) * 2 + k];
+    if ((wedge32 || tgt) && H > 0) {
+        std::vector<int32_t> row_u(H);
+        CU(cudaMemcpy(row_u.data(), ctx->r_row_u.p, size_t(H) * 4, cudaMemcpyDeviceToHost));
+        for (int which = 0; which < 2; which++) {
+            double* dst = which ? tgt : wedge32;
+            if (!dst) continue;
+            std::vector<double> t(size_t(V) * U * 2);
+            CU(cudaMemcpy(t.data(), which ? (void*)ctx->d_tgt.p : (void*)ctx->d_w32.p, t.size() * 8, cudaMemcpyDeviceToHost));
+            for (int v = 0; v < V; v++) for (int64_t r = 0; r < H; r++) for (int k = 0; k < 2; k++)
+                dst[(size_t(r) * V + v) * 2 + k] = t[(size_t(v) * U + row_u[r]) * 2 + k];
+        }
     }
     return CVX_OK;
 }
@@ -716,13 +736,15 @@ int cvx_support_problem_create(cvx_ctx* ctx, int G, const int64_t* group_off, in
     int64_t max_edges = 1;
     for (int v = 0; v < V; v++) max_edges = std::max(max_edges, view_off[v + 1] - view_off[v]);
     p->bg.B = pick_bins(int(max_edges)); p->bg.BS = p->bg.B + 1; p->bg.scale = p->bg.B / 180.0;
-    CU(p->group_off.reserve(G + 1)); CU(p->view_off.reserve(V + 1)); CU(p->vali.reserve(V)); CU(p->bins.reserve(size_t(V) * p->bg.BS));
-    CU(p->support.reserve(size_t(V) * H)); CU(p->bin_tmp.reserve(NE)); CU(p->s_idx.reserve(NE));
+    CU(p->view_off.reserve(V + 1)); CU(p->bins1.reserve(size_t(V) * p->bg.BS)); CU(p->bins2.reserve(size_t(V) * p->bg.BS));
+    CU(p->support.reserve(size_t(V) * H)); CU(p->bin1.reserve(NE)); CU(p->bin2.reserve(NE)); CU(p->idx1.reserve(NE)); CU(p->idx2.reserve(NE));
+    CU(p->row_group.reserve(H));
     CU(p->a31.reserve(NE)); CU(p->a32.reserve(NE)); CU(p->cs.reserve(NE)); CU(p->sn.reserve(NE));
-    CU(p->s_a31.reserve(NE)); CU(p->s_a32.reserve(NE)); CU(p->s_cs.reserve(NE)); CU(p->s_sn.reserve(NE));
+    CU(p->ang1.reserve(NE)); CU(p->tan1.reserve(NE)); CU(p->ang2.reserve(NE)); CU(p->tan2.reserve(NE));
     CU(p->w31.reserve(size_t(V) * G)); CU(p->w32.reserve(size_t(V) * H)); CU(p->tgt.reserve(size_t(V) * H));
-    p->bg.bins = p->bins.p;
-    CU(cudaMemcpyAsync(p->group_off.p, group_off, (G + 1) * 8, cudaMemcpyHostToDevice, st));
+    std::vector<int32_t> rg(H, 0);
+    for (int g = 0; g < G; g++) for (int64_t r = group_off[g]; r < group_off[g + 1]; r++) rg[size_t(r)] = g;
+    CU(cudaMemcpyAsync(p->row_group.p, rg.data(), size_t(p->H) * 4, cudaMemcpyHostToDevice, st));
     CU(cudaMemcpyAsync(p->view_off.p, view_off, (V + 1) * 8, cudaMemcpyHostToDevice, st));
     CU(cudaMemcpyAsync(p->a31.p, ang31, p->n_edges * 8, cudaMemcpyHostToDevice, st));
     CU(cudaMemcpyAsync(p->a32.p, ang32, p->n_edges * 8, cudaMemcpyHostToDevice, st));
@@ -731,12 +753,11 @@ int cvx_support_problem_create(cvx_ctx* ctx, int G, const int64_t* group_off, in
     CU(cudaMemcpyAsync(p->w31.p, wedge31, size_t(V) * G * 16, cudaMemcpyHostToDevice, st));
     CU(cudaMemcpyAsync(p->w32.p, wedge32, size_t(V) * p->H * 16, cudaMemcpyHostToDevice, st));
     CU(cudaMemcpyAsync(p->tgt.p, tgt, size_t(V) * p->H * 16, cudaMemcpyHostToDevice, st));
-    CU(cudaMemsetAsync(p->bins.p, 0, size_t(V) * p->bg.BS * 4, st));
-    launch_stage_given(p->a31.p, p->a32.p, p->cs.p, p->sn.p, p->view_off.p, V, max_edges, p->bin_tmp.p, p->bg, p->s_a31.p, p->s_a32.p, p->s_cs.p,
-                       p->s_sn.p, p->s_idx.p, p->vali.p, st);
-    ctx->tm.kernel_launches += 4;
+    ViewIndex ix1 = {p->ang1.p, p->tan1.p, p->idx1.p, p->bins1.p}, ix2 = {p->ang2.p, p->tan2.p, p->idx2.p, p->bins2.p};
+    launch_stage_given(p->a31.p, p->a32.p, p->cs.p, p->sn.p, p->view_off.p, V, max_edges, p->bin1.p, p->bin2.p, p->bg, ix1, ix2, st);
+    ctx->tm.kernel_launches += 3;
     cudaEventCreate(&p->e0); cudaEventCreate(&p->e1);
-    CU(cudaStreamSynchronize(st));
+    CU(cudaStreamSynchronize(st));   // rg (host vector) must outlive the copy
     CU(cudaGetLastError());
     *out = p;
     return CVX_OK;
@@ -746,14 +767,15 @@ int cvx_support_problem_run(cvx_support_problem* p, float* kernel_ms) {
     if (!p) return CVX_ERR_INVALID;
     cvx_ctx* ctx = p->ctx;
     CU(cudaSetDevice(ctx->device));
-    SupportArgs a;
-    a.group_off = p->group_off.p; a.g_begin = 0; a.g_end = p->G; a.row_base = 0; a.chunk_rows = p->H;
-    a.w31 = p->w31.p; a.w31_stride = p->G; a.w32 = p->w32.p; a.tgt = p->tgt.p;
-    a.vali_view = p->vali.p; a.edge_off = p->view_off.p; a.bg = p->bg;
-    a.s_a31 = p->s_a31.p; a.s_a32 = p->s_a32.p; a.s_cs = p->s_cs.p; a.s_sn = p->s_sn.p; a.s_idx = p->s_idx.p;
-    a.cos_thresh = p->thr; a.parallel_deg = p->par; a.support = p->support.p; a.sup_stride = std::max<int64_t>(p->H, 1); a.ctr = nullptr; a.n_vali = p->V;
+    ValidateArgs a;
+    std::memset(&a, 0, sizeof(a));
+    a.ut.h1 = p->row_group.p; a.U = p->H; a.w31 = p->w31.p; a.w31_stride = p->G; a.w32_in = p->w32.p; a.tgt_in = p->tgt.p;
+    a.vali_view = nullptr; a.edge_off = p->view_off.p; a.bg = p->bg;
+    a.ix1 = ViewIndex{p->ang1.p, p->tan1.p, p->idx1.p, p->bins1.p}; a.ix2 = ViewIndex{p->ang2.p, p->tan2.p, p->idx2.p, p->bins2.p};
+    a.cos_thresh = p->thr; a.parallel_deg = p->par; a.n_vali = p->V;
+    a.support = p->support.p; a.sup_stride = std::max<int64_t>(p->H, 1); a.ctr = nullptr;
     cudaEventRecord(p->e0, ctx->stream);
-    launch_support(a, ctx->stream);
+    launch_validate(ctx->pc, a, true, ctx->stream);
     cudaEventRecord(p->e1, ctx->stream);
     ctx->tm.kernel_launches++;
     CU(cudaStreamSynchronize(ctx->stream));
@@ -773,9 +795,9 @@ int cvx_support_problem_result(cvx_support_problem* p, int32_t* support) {
 int cvx_support_problem_destroy(cvx_support_problem* p) {
     if (!p) return CVX_ERR_INVALID;
     cudaSetDevice(p->ctx->device);
-    p->group_off.release(); p->view_off.release(); p->vali.release(); p->bins.release(); p->support.release(); p->bin_tmp.release();
-    p->s_idx.release(); p->edge_n.release(); p->a31.release(); p->a32.release(); p->cs.release(); p->sn.release(); p->s_a31.release();
-    p->s_a32.release(); p->s_cs.release(); p->s_sn.release(); p->w31.release(); p->w32.release(); p->tgt.release();
+    p->view_off.release(); p->bins1.release(); p->bins2.release(); p->support.release(); p->bin1.release(); p->bin2.release();
+    p->idx1.release(); p->idx2.release(); p->row_group.release(); p->a31.release(); p->a32.release(); p->cs.release(); p->sn.release();
+    p->ang1.release(); p->tan1.release(); p->ang2.release(); p->tan2.release(); p->w31.release(); p->w32.release(); p->tgt.release();
     cudaEventDestroy(p->e0); cudaEventDestroy(p->e1);
     delete p;
     return CVX_OK;

@@ -5,15 +5,16 @@
 // (-fmad=false keeps every a*b+c un-fused so accept/reject decisions match an un-fused CPU build).
 //
 // Pipeline of one hypothesis view pair (Run_3D_Edge_Sketch, EdgeSketch_Core.cpp:168-573):
-//   stage_views   per validation view: two epipolar angles per edge (a2), binned by the first one
+//   stage_views   per validation view: two epipolar angles per edge (a2); two counting-sorted angular indexes
 //   h2_angles     epipolar angle of every view-2 edge (a2)          h1_wedges: wedge of every view-1 edge (a3)
 //   form_count / form_fill   one warp per view-1 edge: wedge scan of view 2 (a5), epipolar correction (a6),
-//                 greedy clustering (a7) -> hypothesis table
+//                 greedy clustering in shared memory (a7) -> hypothesis table + per-edge cluster ranks
+//   uniq_fill     one entry per cluster (members of a cluster carry the same averaged edge) + hoisted reprojection terms
 //   wedge31       wedge of the view-1 edge in each validation view (a3, row 0 only)
-//   reproject     per hypothesis x view: reprojected tangent (a8) + wedge of the view-2 edge (a3)
-//   support       one warp per (view-1 edge, view): walks the bins covered by wedge31, intersects with
-//                 wedge32, orientation arg-max (a10, a11, a12)  <- the HBM-bound support test
-//   select        vote + ratio test (a13), finalize: correction + 2-view DLT + tangent (a15)
+//   validate      per (unique hypothesis, view): reprojected tangent (a8), wedge of the view-2 edge (a3), parallel-wedge
+//                 test (a10), wedge31 n wedge32 enumeration from the narrower of the two angular indexes (a5, a11),
+//                 orientation arg-max (a12) -> support index
+//   count_u / select / select_fill   vote + ratio test (a13);  finalize: correction + 2-view DLT + tangent (a15)
 // No tensor cores: there is no dense contraction anywhere on this path.
 // =====================================================================================
 #include "cvx_kernels.cuh"
@@ -34,7 +35,6 @@ __device__ __forceinline__ int bin_of(double a, double scale, int B) {
     int b = int(a * scale);
     return b < 0 ? 0 : (b >= B ? B - 1 : b);
 }
-__device__ __forceinline__ double2 ldg2(const double2* p) { return __ldg(p); }
 
 // ----------------------------------------------------------------------------- upload-time
 __global__ void k_edge_trig(const double* __restrict__ th, double* __restrict__ cs, double* __restrict__ sn, int64_t n) {
@@ -59,17 +59,18 @@ __global__ void k_stage_angles(EdgeArena ea, const int64_t* __restrict__ edge_of
         const double x = ea.x[off + i], y = ea.y[off + i];
         const double a31 = ore_angle(x, y, e31x, e31y);
         const double a32 = ore_angle(x, y, e32x, e32y);
-        const int b = bin_of(a31, bg.scale, bg.B);
-        ea.a31[off + i] = a31; ea.a32[off + i] = a32; ea.bin[off + i] = b;
-        atomicAdd(&bg.bins[int64_t(v) * bg.BS + b], 1);
+        const int b1 = bin_of(a31, bg.scale, bg.B), b2 = bin_of(a32, bg.scale, bg.B);
+        ea.ang[off + i] = make_double2(a31, a32); ea.bin1[off + i] = b1; ea.bin2[off + i] = b2;
+        atomicAdd(&ea.ix1.bins[int64_t(v) * bg.BS + b1], 1);
+        atomicAdd(&ea.ix2.bins[int64_t(v) * bg.BS + b2], 1);
     }
 }
-// in-place exclusive scan of one view's bin histogram (one block per view)
-__global__ void __launch_bounds__(1024) k_scan_bins(BinGrid bg) {
+// in-place exclusive scan of one bin histogram (one block per histogram; hists = [ix1 views..., ix2 views...])
+__global__ void __launch_bounds__(1024) k_scan_bins(int32_t* bins1, int32_t* bins2, int n_vali, int BS) {
     __shared__ int part[1024];
-    int32_t* b = bg.bins + int64_t(blockIdx.x) * bg.BS;
-    const int per = (bg.BS + 1023) / 1024;
-    const int lo = threadIdx.x * per, hi = min(lo + per, bg.BS);
+    int32_t* b = (blockIdx.x < n_vali ? bins1 + int64_t(blockIdx.x) * BS : bins2 + int64_t(blockIdx.x - n_vali) * BS);
+    const int per = (BS + 1023) / 1024;
+    const int lo = min(int(threadIdx.x) * per, BS), hi = min(lo + per, BS);
     int s = 0;
     for (int i = lo; i < hi; i++) s += b[i];
     part[threadIdx.x] = s;
@@ -91,60 +92,66 @@ __global__ void k_stage_scatter(EdgeArena ea, const int64_t* __restrict__ edge_o
     const int n = edge_n[view];
     const int64_t off = edge_off[view];
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-        const int b = ea.bin[off + i];
-        const int pos = atomicAdd(&bg.bins[int64_t(v) * bg.BS + b], 1);
-        const int64_t d = off + pos;
-        ea.s_a31[d] = ea.a31[off + i]; ea.s_a32[d] = ea.a32[off + i];
-        ea.s_cs[d] = ea.cs[off + i]; ea.s_sn[d] = ea.sn[off + i]; ea.s_idx[d] = i;
+        const double2 a = ea.ang[off + i];
+        const double2 t = make_double2(ea.cs[off + i], ea.sn[off + i]);
+        const int p1 = atomicAdd(&ea.ix1.bins[int64_t(v) * bg.BS + ea.bin1[off + i]], 1);
+        const int p2 = atomicAdd(&ea.ix2.bins[int64_t(v) * bg.BS + ea.bin2[off + i]], 1);
+        ea.ix1.ang[off + p1] = a; ea.ix1.tan[off + p1] = t; ea.ix1.idx[off + p1] = i;
+        ea.ix2.ang[off + p2] = a; ea.ix2.tan[off + p2] = t; ea.ix2.idx[off + p2] = i;
     }
 }
 void launch_stage_views(const EdgeArena& ea, const int64_t* edge_off, const int32_t* edge_n, const int32_t* vali_view, int n_vali,
                         int max_edges, const ViewConst* vc, const BinGrid& bg, cudaStream_t st, int* launches) {
     if (n_vali <= 0) return;
-    cudaMemsetAsync(bg.bins, 0, size_t(n_vali) * bg.BS * sizeof(int32_t), st);
+    cudaMemsetAsync(ea.ix1.bins, 0, size_t(n_vali) * bg.BS * sizeof(int32_t), st);
+    cudaMemsetAsync(ea.ix2.bins, 0, size_t(n_vali) * bg.BS * sizeof(int32_t), st);
     int bx = (max_edges + 255) / 256;
     if (bx < 1) bx = 1;
     if (bx > 1024) bx = 1024;
     dim3 grid(bx, n_vali);
     k_stage_angles<<<grid, 256, 0, st>>>(ea, edge_off, edge_n, vali_view, vc, bg);
-    k_scan_bins<<<n_vali, 1024, 0, st>>>(bg);
+    k_scan_bins<<<2 * n_vali, 1024, 0, st>>>(ea.ix1.bins, ea.ix2.bins, n_vali, bg.BS);
     k_stage_scatter<<<grid, 256, 0, st>>>(ea, edge_off, edge_n, vali_view, bg);
     if (launches) *launches += 3;
 }
 
-// stand-alone support test: the per-view angle / tangent arrays are given; only the bin grid is built here
-__global__ void k_given_hist(const double* __restrict__ a31, const int64_t* __restrict__ view_off, int32_t* __restrict__ bin, BinGrid bg) {
+// stand-alone support test: the per-view angle / tangent arrays are given; only the two indexes are built here
+__global__ void k_given_hist(const double* __restrict__ a31, const double* __restrict__ a32, const int64_t* __restrict__ view_off,
+                             int32_t* __restrict__ bin1, int32_t* __restrict__ bin2, BinGrid bg, int32_t* bins1, int32_t* bins2) {
     const int v = blockIdx.y;
     const int64_t b0 = view_off[v], n = view_off[v + 1] - b0;
     for (int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; i < n; i += int64_t(gridDim.x) * blockDim.x) {
-        const int b = bin_of(a31[b0 + i], bg.scale, bg.B);
-        bin[b0 + i] = b;
-        atomicAdd(&bg.bins[int64_t(v) * bg.BS + b], 1);
+        const int b1 = bin_of(a31[b0 + i], bg.scale, bg.B), b2 = bin_of(a32[b0 + i], bg.scale, bg.B);
+        bin1[b0 + i] = b1; bin2[b0 + i] = b2;
+        atomicAdd(&bins1[int64_t(v) * bg.BS + b1], 1);
+        atomicAdd(&bins2[int64_t(v) * bg.BS + b2], 1);
     }
 }
 __global__ void k_given_scatter(const double* __restrict__ a31, const double* __restrict__ a32, const double* __restrict__ cs,
-                                const double* __restrict__ sn, const int64_t* __restrict__ view_off, const int32_t* __restrict__ bin, BinGrid bg,
-                                double* s_a31, double* s_a32, double* s_cs, double* s_sn, int32_t* s_idx) {
+                                const double* __restrict__ sn, const int64_t* __restrict__ view_off, const int32_t* __restrict__ bin1,
+                                const int32_t* __restrict__ bin2, BinGrid bg, ViewIndex ix1, ViewIndex ix2) {
     const int v = blockIdx.y;
     const int64_t b0 = view_off[v], n = view_off[v + 1] - b0;
     for (int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; i < n; i += int64_t(gridDim.x) * blockDim.x) {
-        const int pos = atomicAdd(&bg.bins[int64_t(v) * bg.BS + bin[b0 + i]], 1);
-        const int64_t d = b0 + pos;
-        s_a31[d] = a31[b0 + i]; s_a32[d] = a32[b0 + i]; s_cs[d] = cs[b0 + i]; s_sn[d] = sn[b0 + i]; s_idx[d] = int32_t(i);
+        const double2 a = make_double2(a31[b0 + i], a32[b0 + i]);
+        const double2 t = make_double2(cs[b0 + i], sn[b0 + i]);
+        const int p1 = atomicAdd(&ix1.bins[int64_t(v) * bg.BS + bin1[b0 + i]], 1);
+        const int p2 = atomicAdd(&ix2.bins[int64_t(v) * bg.BS + bin2[b0 + i]], 1);
+        ix1.ang[b0 + p1] = a; ix1.tan[b0 + p1] = t; ix1.idx[b0 + p1] = int32_t(i);
+        ix2.ang[b0 + p2] = a; ix2.tan[b0 + p2] = t; ix2.idx[b0 + p2] = int32_t(i);
     }
 }
-__global__ void k_iota(int32_t* p, int n) { int i = blockIdx.x * blockDim.x + threadIdx.x; if (i < n) p[i] = i; }
 void launch_stage_given(const double* a31, const double* a32, const double* cs, const double* sn, const int64_t* view_off, int n_vali,
-                        int64_t max_edges, int32_t* bin_tmp, const BinGrid& bg, double* s_a31, double* s_a32, double* s_cs, double* s_sn,
-                        int32_t* s_idx, int32_t* vali_iota, cudaStream_t st) {
-    k_iota<<<(n_vali + 255) / 256, 256, 0, st>>>(vali_iota, n_vali);
+                        int64_t max_edges, int32_t* bin1, int32_t* bin2, const BinGrid& bg, ViewIndex ix1, ViewIndex ix2, cudaStream_t st) {
+    cudaMemsetAsync(ix1.bins, 0, size_t(n_vali) * bg.BS * sizeof(int32_t), st);
+    cudaMemsetAsync(ix2.bins, 0, size_t(n_vali) * bg.BS * sizeof(int32_t), st);
     int64_t bx = (max_edges + 255) / 256;
     if (bx < 1) bx = 1;
     if (bx > 2048) bx = 2048;
     dim3 grid((unsigned)bx, n_vali);
-    k_given_hist<<<grid, 256, 0, st>>>(a31, view_off, bin_tmp, bg);
-    k_scan_bins<<<n_vali, 1024, 0, st>>>(bg);
-    k_given_scatter<<<grid, 256, 0, st>>>(a31, a32, cs, sn, view_off, bin_tmp, bg, s_a31, s_a32, s_cs, s_sn, s_idx);
+    k_given_hist<<<grid, 256, 0, st>>>(a31, a32, view_off, bin1, bin2, bg, ix1.bins, ix2.bins);
+    k_scan_bins<<<2 * n_vali, 1024, 0, st>>>(ix1.bins, ix2.bins, n_vali, bg.BS);
+    k_given_scatter<<<grid, 256, 0, st>>>(a31, a32, cs, sn, view_off, bin1, bin2, bg, ix1, ix2);
 }
 
 // ----------------------------------------------------------------------------- pass-level tables
@@ -172,7 +179,7 @@ void launch_h1_wedges(const PassConst& pc, const double* x1, const double* y1, i
 __global__ void __launch_bounds__(1024) k_scan_i32_i64(const int32_t* __restrict__ in, int64_t* __restrict__ out, int n) {
     __shared__ long long part[1024];
     const int per = (n + 1023) / 1024;
-    const int lo = min(threadIdx.x * per, n), hi = min(lo + per, n);
+    const int lo = min(int(threadIdx.x) * per, n), hi = min(lo + per, n);
     long long s = 0;
     for (int i = lo; i < hi; i++) s += in[i];
     part[threadIdx.x] = s;
@@ -189,8 +196,177 @@ __global__ void __launch_bounds__(1024) k_scan_i32_i64(const int32_t* __restrict
 }
 void launch_scan_i32_i64(const int32_t* in, int64_t* out, int n, cudaStream_t st) { k_scan_i32_i64<<<1, 1024, 0, st>>>(in, out, n); }
 
-// ----------------------------------------------------------------------------- clustering (one warp)
-// EdgeClusterer.cpp:60-125; every lane runs the same sequential sums (ascending member index, as the reference).
+// ----------------------------------------------------------------------------- clustering (one warp per view-1 edge)
+// EdgeClusterer.cpp:127-293.  The reference is a sequential greedy merge with restart: scan i ascending, take the nearest
+// j of another cluster (dist < 1 px, cluster orientations within 20 deg, first minimum), merge if the sizes allow, restart.
+// Distances never change, so the warp keeps an adjacency bit matrix (dist < threshold) in shared memory and evaluates
+// "would edge i merge?" for 32 edges at a time; the first such i (ballot + ffs) is the reference's next merge.
+template <int N>
+struct ClusterSm {
+    double x[N], y[N], thn[N], orient[N];   // corrected location, normalised orientation, per-label average orientation
+    double tmpd[32], tmpw[32];
+    uint32_t adj[N * (N / 32)];
+    int16_t label[N], size[N], rank[N], mem[32];
+};
+#define CL_N 128          // rows handled by the shared-memory path; larger groups take the global-memory fallback
+#define FORM_WARPS 4
+
+// Gaussian-weighted average over the members s.mem[0..cnt) (ascending index): EdgeClusterer.cpp:60-125.  All sums run
+// in member order on every lane (bit-identical to the sequential code); sqrt / exp of the members are lane-parallel.
+template <int N>
+__device__ __forceinline__ void gauss_avg_list(ClusterSm<N>& s, int cnt, double sigma, int lane, double* gx, double* gy, double* gth) {
+    double sx = 0, sy = 0;
+    for (int k = 0; k < cnt; k++) { const int i = s.mem[k]; sx += s.x[i]; sy += s.y[i]; }
+    const double cx = sx / cnt, cy = sy / cnt;
+    if (lane < cnt) {
+        const int i = s.mem[lane];
+        const double dx = s.x[i] - cx, dy = s.y[i] - cy;
+        s.tmpd[lane] = sqrt(dx * dx + dy * dy);
+    }
+    __syncwarp();
+    double tot = 0.0;
+    for (int k = 0; k < cnt; k++) tot += s.tmpd[k];
+    const double mean_shift = tot / cnt;
+    if (lane < cnt) {
+        const double q = (s.tmpd[lane] - mean_shift) / sigma;
+        s.tmpw[lane] = exp(-0.5 * (q * q));
+    }
+    __syncwarp();
+    double swx = 0, swy = 0, swo = 0, tw = 0;
+    for (int k = 0; k < cnt; k++) {
+        const int i = s.mem[k];
+        const double w = s.tmpw[k];
+        swx += w * s.x[i]; swy += w * s.y[i]; swo += w * s.thn[i]; tw += w;
+    }
+    *gx = swx / tw; *gy = swy / tw; *gth = swo / tw;
+    __syncwarp();
+}
+// members with label la or lb, ascending, into s.mem; returns the count (<= 32 by construction)
+template <int N>
+__device__ __forceinline__ int member_list(ClusterSm<N>& s, int n, int la, int lb, int lane, unsigned lt) {
+    int cnt = 0;
+    for (int base = 0; base < n; base += 32) {
+        const int k = base + lane;
+        const bool in = k < n && (s.label[k] == la || s.label[k] == lb);
+        const unsigned m = __ballot_sync(FULL, in);
+        if (in) { const int p = cnt + __popc(m & lt); if (p < 32) s.mem[p] = int16_t(k); }
+        cnt += __popc(m);
+    }
+    __syncwarp();
+    return cnt < 32 ? cnt : 32;
+}
+
+template <int N>
+__device__ void cluster_warp_sm(int n, const PassConst& pc, ClusterSm<N>& s, const double* __restrict__ xc, const double* __restrict__ yc,
+                                const double* __restrict__ th, const int32_t* __restrict__ h2orig, double* xbar, double* ybar, double* thbar,
+                                int32_t* label_out, int32_t* h2rep, int32_t* urank, int32_t* n_clusters, int lane) {
+    constexpr int NW = N / 32;
+    const unsigned lt = lanemask_lt();
+    const int nw = (n + 31) >> 5;
+    for (int k = lane; k < n; k += 32) {
+        const double t = normalize_orientation(th[k], pc.cl_wrap_deg);   // :131-135
+        s.x[k] = xc[k]; s.y[k] = yc[k]; s.thn[k] = t; s.orient[k] = t; s.label[k] = int16_t(k); s.size[k] = 1;
+    }
+    __syncwarp();
+    for (int i = lane; i < n; i += 32) {                                  // adjacency: dist(i, j) < CLUSTER_DIST_THRESH
+        const double xi = s.x[i], yi = s.y[i];
+        for (int w = 0; w < nw; w++) {
+            uint32_t bits = 0;
+            const int jend = min(32, n - w * 32);
+            for (int b = 0; b < jend; b++) {
+                const int j = w * 32 + b;
+                const double ddx = xi - s.x[j], ddy = yi - s.y[j];
+                if (sqrt(ddx * ddx + ddy * ddy) < pc.cl_dist && j != i) bits |= (1u << b);
+            }
+            s.adj[i * NW + w] = bits;
+        }
+    }
+    __syncwarp();
+    while (true) {                                                        // :139-189
+        int mi = -1, mj = -1;
+        for (int base = 0; base < n; base += 32) {
+            const int i = base + lane;
+            bool found = false;
+            int bj = -1;
+            if (i < n) {
+                const int li = s.label[i];
+                const double oi = s.orient[li], xi = s.x[i], yi = s.y[i];
+                double bd = DBL_MAX;
+                for (int w = 0; w < nw; w++) {
+                    uint32_t bits = s.adj[i * NW + w];
+                    while (bits) {
+                        const int b = __ffs(bits) - 1;
+                        bits &= bits - 1;
+                        const int j = w * 32 + b;
+                        const int lj = s.label[j];
+                        if (lj != li && fabs(oi - s.orient[lj]) < pc.cl_orient_rad) {          // :147-154
+                            const double ddx = xi - s.x[j], ddy = yi - s.y[j];
+                            const double d = sqrt(ddx * ddx + ddy * ddy);
+                            if (d < bd) { bd = d; bj = j; }                                     // first minimum (j ascending)
+                        }
+                    }
+                }
+                if (bj >= 0 && int(s.size[s.label[bj]]) + int(s.size[li]) <= pc.max_cluster) found = true;   // :166
+            }
+            const unsigned m = __ballot_sync(FULL, found);
+            if (m) {
+                const int src = __ffs(m) - 1;
+                mi = base + src;
+                mj = __shfl_sync(FULL, bj, src);
+                break;
+            }
+        }
+        if (mi < 0) break;
+        const int old_l = s.label[mj], new_l = s.label[mi];
+        const int cnt = member_list(s, n, old_l, new_l, lane, lt);
+        double gx, gy, gth;
+        gauss_avg_list(s, cnt, pc.cl_sigma, lane, &gx, &gy, &gth);       // :168
+        if (lane == 0) { s.orient[new_l] = normalize_orientation(gth, pc.cl_wrap_deg); s.size[new_l] = int16_t(cnt); }   // :175-176
+        for (int k = lane; k < n; k += 32) if (s.label[k] == old_l) s.label[k] = int16_t(new_l);   // :179-183
+        __syncwarp();
+    }
+    // cluster ranks (clusters in ascending label order = the reference's std::map order); a label in use is the index
+    // of one of its members, so the cluster roots are the rows with label[k] == k
+    int nroots = 0;
+    for (int base = 0; base < n; base += 32) {
+        const int k = base + lane;
+        const bool root = k < n && s.label[k] == k;
+        const unsigned m = __ballot_sync(FULL, root);
+        if (root) s.rank[k] = int16_t(nroots + __popc(m & lt));
+        nroots += __popc(m);
+    }
+    __syncwarp();
+    // :250-290 per cluster: Gaussian-weighted average written to every member, representative = member closest to it
+    for (int i = 0; i < n; i++) {
+        if (s.label[i] != i) continue;
+        const int cnt = member_list(s, n, i, i, lane, lt);
+        double gx, gy, gth;
+        gauss_avg_list(s, cnt, pc.cl_sigma, lane, &gx, &gy, &gth);
+        double d = DBL_MAX;
+        int pos = lane;
+        if (lane < cnt) {
+            const int j = s.mem[lane];
+            const double ddx = s.x[j] - gx, ddy = s.y[j] - gy;
+            d = sqrt(ddx * ddx + ddy * ddy);
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {                                // first minimum in member order (:270)
+            const double od = __shfl_xor_sync(FULL, d, o);
+            const int op = __shfl_xor_sync(FULL, pos, o);
+            if (od < d || (od == d && op < pos)) { d = od; pos = op; }
+        }
+        const int rep = h2orig[s.mem[pos]];                               // corrected(closest, 8), :282
+        if (lane < cnt) {
+            const int j = s.mem[lane];
+            xbar[j] = gx; ybar[j] = gy; thbar[j] = gth; h2rep[j] = rep;
+        }
+        __syncwarp();
+    }
+    for (int k = lane; k < n; k += 32) { const int l = s.label[k]; label_out[k] = l; urank[k] = s.rank[l]; }
+    if (lane == 0) *n_clusters = nroots;
+}
+
+// ---- global-memory fallback for groups larger than CL_N rows (same semantics, the plain sequential scan order)
 __device__ void gauss_avg_warp(int n, const double* xc, const double* yc, const double* thn, const int32_t* label, int l1, int l2,
                                double sigma, double* gx, double* gy, double* gth) {
     double sx = 0, sy = 0;
@@ -219,17 +395,17 @@ __device__ void gauss_avg_warp(int n, const double* xc, const double* yc, const 
     }
     *gx = swx / tw; *gy = swy / tw; *gth = swo / tw;
 }
-
-// EdgeClusterer.cpp:127-293 for the n rows of one view-1 edge.
-__device__ void cluster_warp(int n, const PassConst& pc, const double* xc, const double* yc, const double* th, double* thn, double* orient,
-                             int32_t* label, const int32_t* h2orig, double* xbar, double* ybar, double* thbar, int32_t* h2rep, int lane) {
+__device__ void cluster_warp_global(int n, const PassConst& pc, const double* xc, const double* yc, const double* th, double* thn, double* orient,
+                                    int32_t* label, const int32_t* h2orig, double* xbar, double* ybar, double* thbar, int32_t* h2rep,
+                                    int32_t* urank, int32_t* n_clusters, int lane) {
+    const unsigned lt = lanemask_lt();
     for (int k = lane; k < n; k += 32) {
-        const double t = normalize_orientation(th[k], pc.cl_wrap_deg);   // :131-135
+        const double t = normalize_orientation(th[k], pc.cl_wrap_deg);
         thn[k] = t; orient[k] = t; label[k] = k;
     }
     __syncwarp();
     bool merged = true;
-    while (merged) {                                                       // :139-189
+    while (merged) {
         merged = false;
         for (int i = 0; i < n; i++) {
             const int li = label[i];
@@ -241,11 +417,11 @@ __device__ void cluster_warp(int n, const PassConst& pc, const double* xc, const
                 if (lj != li) {
                     const double ddx = xi - xc[j], ddy = yi - yc[j];
                     const double dist = sqrt(ddx * ddx + ddy * ddy);
-                    if (dist < bd && dist < pc.cl_dist && fabs(oi - orient[lj]) < pc.cl_orient_rad) { bd = dist; bj = j; }   // :154
+                    if (dist < bd && dist < pc.cl_dist && fabs(oi - orient[lj]) < pc.cl_orient_rad) { bd = dist; bj = j; }
                 }
             }
 #pragma unroll
-            for (int o = 16; o > 0; o >>= 1) {   // arg-min, ties -> lowest j (the sequential scan keeps the first minimum)
+            for (int o = 16; o > 0; o >>= 1) {
                 const double od = __shfl_xor_sync(FULL, bd, o);
                 const int oj = __shfl_xor_sync(FULL, bj, o);
                 if (oj >= 0 && (bj < 0 || od < bd || (od == bd && oj < bj))) { bd = od; bj = oj; }
@@ -256,12 +432,12 @@ __device__ void cluster_warp(int n, const PassConst& pc, const double* xc, const
                 for (int j = lane; j < n; j += 32) { const int l = label[j]; so += (l == old_l); sn += (l == new_l); }
 #pragma unroll
                 for (int o = 16; o > 0; o >>= 1) { so += __shfl_xor_sync(FULL, so, o); sn += __shfl_xor_sync(FULL, sn, o); }
-                if (so + sn <= pc.max_cluster) {                           // :166
+                if (so + sn <= pc.max_cluster) {
                     double gx, gy, gth;
                     gauss_avg_warp(n, xc, yc, thn, label, old_l, new_l, pc.cl_sigma, &gx, &gy, &gth);
                     __syncwarp();
-                    if (lane == 0) orient[new_l] = normalize_orientation(gth, pc.cl_wrap_deg);   // :175-176
-                    for (int j = lane; j < n; j += 32) if (label[j] == old_l) label[j] = new_l;   // :179-183
+                    if (lane == 0) orient[new_l] = normalize_orientation(gth, pc.cl_wrap_deg);
+                    for (int j = lane; j < n; j += 32) if (label[j] == old_l) label[j] = new_l;
                     __syncwarp();
                     merged = true;
                     break;
@@ -269,27 +445,35 @@ __device__ void cluster_warp(int n, const PassConst& pc, const double* xc, const
             }
         }
     }
-    // :250-290 per cluster: Gaussian-weighted average written to every member, representative = member closest to it
+    int nroots = 0;
+    for (int base = 0; base < n; base += 32) {
+        const int k = base + lane;
+        const bool root = k < n && label[k] == k;
+        const unsigned m = __ballot_sync(FULL, root);
+        if (root) urank[k] = nroots + __popc(m & lt);
+        nroots += __popc(m);
+    }
+    __syncwarp();
     for (int i = 0; i < n; i++) {
-        const int li = label[i];
-        bool first = true;
-        for (int j = lane; j < i; j += 32) if (label[j] == li) first = false;
-        if (!__all_sync(FULL, first)) continue;
+        if (label[i] != i) continue;
         double gx, gy, gth;
-        gauss_avg_warp(n, xc, yc, thn, label, li, li, pc.cl_sigma, &gx, &gy, &gth);
+        gauss_avg_warp(n, xc, yc, thn, label, i, i, pc.cl_sigma, &gx, &gy, &gth);
         double md = DBL_MAX;
         int closest = -1;
         for (int j = i; j < n; j++) {
-            if (label[j] == li) {
+            if (label[j] == i) {
                 const double ddx = xc[j] - gx, ddy = yc[j] - gy;
                 const double dist = sqrt(ddx * ddx + ddy * ddy);
-                if (dist < md) { md = dist; closest = j; }                 // :270
+                if (dist < md) { md = dist; closest = j; }
             }
         }
-        const int rep = h2orig[closest];                                   // corrected(closest, 8), :282
+        const int rep = h2orig[closest];
         for (int j = i + lane; j < n; j += 32)
-            if (label[j] == li) { xbar[j] = gx; ybar[j] = gy; thbar[j] = gth; h2rep[j] = rep; }
+            if (label[j] == i) { xbar[j] = gx; ybar[j] = gy; thbar[j] = gth; h2rep[j] = rep; }
     }
+    __syncwarp();
+    for (int k = lane; k < n; k += 32) { const int l = label[k]; if (l != k) urank[k] = urank[l]; }
+    if (lane == 0) *n_clusters = nroots;
 }
 
 // ----------------------------------------------------------------------------- formation
@@ -297,10 +481,13 @@ __device__ void cluster_warp(int n, const PassConst& pc, const double* xc, const
 // ballot-compacted scan over the view-2 angle list (keeps the reference's ascending-index order for free),
 // edgelsHYPO2_epipolar_correction (PairEdgeHypo.cpp:225-293), then clustering.
 template <bool FILL>
-__global__ void __launch_bounds__(128) k_form(const __grid_constant__ PassConst pc, const double* __restrict__ x1, const double* __restrict__ y1,
-                                              int h1_begin, int h1_end, const double2* __restrict__ wedge_h1, const double* __restrict__ x2,
-                                              const double* __restrict__ y2, const double* __restrict__ th2, const double* __restrict__ ang2,
-                                              int E2, int32_t* m_out, int32_t* n_out, const int64_t* __restrict__ row_off, RowTable rt) {
+__global__ void __launch_bounds__(FORM_WARPS * 32) k_form(const __grid_constant__ PassConst pc, const double* __restrict__ x1,
+                                                          const double* __restrict__ y1, int h1_begin, int h1_end,
+                                                          const double2* __restrict__ wedge_h1, const double* __restrict__ x2,
+                                                          const double* __restrict__ y2, const double* __restrict__ th2,
+                                                          const double* __restrict__ ang2, int E2, int32_t* m_out, int32_t* n_out,
+                                                          const int64_t* __restrict__ row_off, RowTable rt, int32_t* n_clusters) {
+    extern __shared__ __align__(16) unsigned char form_smem[];
     const int lane = threadIdx.x & 31;
     const int h1 = h1_begin + blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (h1 >= h1_end) return;
@@ -311,7 +498,7 @@ __global__ void __launch_bounds__(128) k_form(const __grid_constant__ PassConst 
     int64_t row0 = 0;
     if (FILL) {
         n_total = n_out[h1];
-        if (n_total == 0) return;
+        if (n_total == 0) { if (lane == 0) n_clusters[h1] = 0; return; }
         row0 = row_off[h1];
     } else if (skip || w.x != w.x) {
         if (lane == 0) { m_out[h1] = 0; n_out[h1] = 0; }
@@ -329,11 +516,13 @@ __global__ void __launch_bounds__(128) k_form(const __grid_constant__ PassConst 
             const double a = ang2[i];
             in = (a > w.x && a < w.y);                                       // PairEdgeHypo.cpp:94 (strict both sides)
         }
+        const unsigned mm = __ballot_sync(FULL, in);
+        if (mm == 0) continue;
         if (in) {
             t2 = th2[i];
             ok = correct_one(coef, x2[i], y2[i], t2, pc.loc_pert, pc.tang_thresh, pc.orient_pert, &cx, &cy);
         }
-        const unsigned mm = __ballot_sync(FULL, in), mo = __ballot_sync(FULL, ok);
+        const unsigned mo = __ballot_sync(FULL, ok);
         if (FILL) {
             if (in) {
                 const int k = mbase + __popc(mm & lt);                       // pre-correction position (col 9)
@@ -352,8 +541,15 @@ __global__ void __launch_bounds__(128) k_form(const __grid_constant__ PassConst 
         return;
     }
     __syncwarp();
-    cluster_warp(n_total, pc, rt.xc + row0, rt.yc + row0, rt.th + row0, rt.thn + row0, rt.orient + row0, rt.label + row0, rt.h2orig + row0,
-                 rt.xbar + row0, rt.ybar + row0, rt.thbar + row0, rt.h2rep + row0, lane);
+    if (n_total <= CL_N && pc.max_cluster <= 32) {
+        ClusterSm<CL_N>& s = reinterpret_cast<ClusterSm<CL_N>*>(form_smem)[threadIdx.x >> 5];
+        cluster_warp_sm<CL_N>(n_total, pc, s, rt.xc + row0, rt.yc + row0, rt.th + row0, rt.h2orig + row0, rt.xbar + row0, rt.ybar + row0,
+                              rt.thbar + row0, rt.label + row0, rt.h2rep + row0, rt.urank + row0, n_clusters + h1, lane);
+    } else {
+        cluster_warp_global(n_total, pc, rt.xc + row0, rt.yc + row0, rt.th + row0, rt.thn + row0, rt.orient + row0, rt.label + row0,
+                            rt.h2orig + row0, rt.xbar + row0, rt.ybar + row0, rt.thbar + row0, rt.h2rep + row0, rt.urank + row0,
+                            n_clusters + h1, lane);
+    }
 }
 void launch_form_count(const PassConst& pc, const double* x1, const double* y1, int h1_begin, int h1_end, const double2* wedge_h1,
                        const double* x2, const double* y2, const double* th2, const double* ang2, int E2, int32_t* m_out, int32_t* n_out,
@@ -361,18 +557,49 @@ void launch_form_count(const PassConst& pc, const double* x1, const double* y1, 
     const int n = h1_end - h1_begin;
     if (n <= 0) return;
     RowTable rt = {};
-    k_form<false><<<(n + 3) / 4, 128, 0, st>>>(pc, x1, y1, h1_begin, h1_end, wedge_h1, x2, y2, th2, ang2, E2, m_out, n_out, nullptr, rt);
+    k_form<false><<<(n + FORM_WARPS - 1) / FORM_WARPS, FORM_WARPS * 32, 0, st>>>(pc, x1, y1, h1_begin, h1_end, wedge_h1, x2, y2, th2, ang2, E2,
+                                                                                m_out, n_out, nullptr, rt, nullptr);
 }
 void launch_form_fill(const PassConst& pc, const double* x1, const double* y1, int h1_begin, int h1_end, const double2* wedge_h1,
                       const double* x2, const double* y2, const double* th2, const double* ang2, int E2, const int32_t* n_of,
-                      const int64_t* row_off, RowTable rt, cudaStream_t st) {
+                      const int64_t* row_off, RowTable rt, int32_t* n_clusters, cudaStream_t st) {
     const int n = h1_end - h1_begin;
     if (n <= 0) return;
-    k_form<true><<<(n + 3) / 4, 128, 0, st>>>(pc, x1, y1, h1_begin, h1_end, wedge_h1, x2, y2, th2, ang2, E2, nullptr, const_cast<int32_t*>(n_of),
-                                             row_off, rt);
+    const size_t smem = FORM_WARPS * sizeof(ClusterSm<CL_N>);
+    cudaFuncSetAttribute(k_form<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));   // per device, cheap
+    k_form<true><<<(n + FORM_WARPS - 1) / FORM_WARPS, FORM_WARPS * 32, smem, st>>>(pc, x1, y1, h1_begin, h1_end, wedge_h1, x2, y2, th2, ang2, E2,
+                                                                                  nullptr, const_cast<int32_t*>(n_of), row_off, rt, n_clusters);
 }
 
-// ----------------------------------------------------------------------------- validation: geometry
+// ----------------------------------------------------------------------------- unique-hypothesis table
+// Every member row of a cluster was overwritten with the same (xbar, ybar, thbar) (EdgeClusterer.cpp:273-276), so
+// getGamma3LocationAndTangent / getOreListBar / getSupportIdx give identical results for all of them: they are evaluated
+// once per cluster ("unique hypothesis") and the member rows read the result through row_u.
+__global__ void __launch_bounds__(256) k_uniq_fill(const __grid_constant__ PassConst pc, const double* __restrict__ x1, const double* __restrict__ y1,
+                                                   const double* __restrict__ th1, RowTable rt, int64_t H, const int64_t* __restrict__ row_off,
+                                                   const int64_t* __restrict__ u_off, UniqTable ut) {
+    const int64_t r = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+    if (r >= H) return;
+    const int h1 = rt.h1[r];
+    const int k = int(r - row_off[h1]);
+    const int u = int(u_off[h1]) + rt.urank[r];
+    rt.row_u[r] = u;
+    atomicAdd(&ut.mult[u], 1);
+    if (rt.label[r] != k) return;
+    const double xb = rt.xbar[r], yb = rt.ybar[r];
+    RowGeom g;
+    row_geometry(x1[h1], y1[h1], th1[h1], xb, yb, rt.thbar[r], pc, &g);   // view-independent part of getGamma3LocationAndTangent
+    ut.h1[u] = h1; ut.row[u] = int32_t(r);
+    ut.xy[u] = make_double2(xb, yb);
+    ut.geom[u] = make_double4(g.rho1, g.Tv1[0], g.Tv1[1], g.Tv1[2]);
+}
+void launch_uniq_fill(const PassConst& pc, const double* x1, const double* y1, const double* th1, RowTable rt, int64_t H,
+                      const int64_t* row_off, const int64_t* u_off, UniqTable ut, cudaStream_t st) {
+    if (H <= 0) return;
+    k_uniq_fill<<<unsigned((H + 255) / 256), 256, 0, st>>>(pc, x1, y1, th1, rt, H, row_off, u_off, ut);
+}
+
+// ----------------------------------------------------------------------------- validation
 // wedge of the view-1 edge in every validation view (getOreListBar row 0, EdgeSketch_Core.cpp:334,345)
 __global__ void __launch_bounds__(128) k_wedge31(const __grid_constant__ PassConst pc, const ViewConst* __restrict__ vc, const double* __restrict__ x1,
                                                  const double* __restrict__ y1, const int32_t* __restrict__ n_of, int h1_begin, int h1_end, int E1,
@@ -384,7 +611,7 @@ __global__ void __launch_bounds__(128) k_wedge31(const __grid_constant__ PassCon
     double lo, hi;
     const int f = wedge_row(x1[h1], y1[h1], c.F31, c.e1_31[0], c.e1_31[1], c.e2_31[0], c.e2_31[1], pc.delta, pc.rows, pc.cols, &lo, &hi);
     w31[int64_t(v) * E1 + h1] = make_double2(lo, hi);
-    if (f) atomicAdd(&ctr->n_degenerate, 1ULL);
+    if (f) atomicAdd(&ctr->n_degenerate[(blockIdx.x + blockIdx.y) & (CVX_CTR_SLOTS - 1)], 1ULL);
 }
 void launch_wedge31(const PassConst& pc, const ViewConst* vc, const double* x1, const double* y1, const int32_t* n_of, int h1_begin, int h1_end,
                     int E1, double2* w31, DevCounters* ctr, cudaStream_t st) {
@@ -394,157 +621,131 @@ void launch_wedge31(const PassConst& pc, const ViewConst* vc, const double* x1, 
     k_wedge31<<<grid, 128, 0, st>>>(pc, vc, x1, y1, n_of, h1_begin, h1_end, E1, w31, ctr);
 }
 
-// per hypothesis row x validation view: reprojected tangent (getGamma3LocationAndTangent, EdgeSketch_Core.cpp:330)
-// and wedge of the clustered view-2 edge (getOreListBar, :340).  FP64-transcendental bound (7 atan, asin, 6 sin/cos, ~24 div).
-__global__ void __launch_bounds__(128) k_reproject(const __grid_constant__ PassConst pc, const ViewConst* __restrict__ vc, const double* __restrict__ x1,
-                                                   const double* __restrict__ y1, const double* __restrict__ th1, RowTable rt, int64_t row_begin,
-                                                   int64_t row_end, double2* __restrict__ w32, double2* __restrict__ tgt, DevCounters* ctr) {
-    const int64_t r = row_begin + blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+// One thread per (unique hypothesis, validation view):
+//   getGamma3LocationAndTangent (EdgeSketch_Core.cpp:330, view-dependent part), getOreListBar of the clustered view-2 edge
+//   (:340), is_Epipolar_Wedges_in_Parallel (hpp:112-128), getHYPO2_idx_Ore x2 + set_intersection (:348-374) as a walk over
+//   the narrower of the two angular indexes with the exact strict tests of PairEdgeHypo.cpp:94 on both angles, and
+//   getSupportIdx (getSupportedEdgels.cpp:32-47: d >= thr && d > prev in ascending index order == maximum, ties to the
+//   lowest index).  Threads of a warp are consecutive hypotheses of (mostly) one view-1 edge: they share wedge31, the bin
+//   lookups and -- when the a31-keyed index is the narrower one -- the whole walk (broadcast loads).
+#define VAL_THREADS 128
+template <bool GIVEN>
+__global__ void __launch_bounds__(VAL_THREADS) k_validate(const __grid_constant__ PassConst pc, const __grid_constant__ ValidateArgs a) {
+    const int64_t u = blockIdx.x * int64_t(VAL_THREADS) + threadIdx.x;
     const int v = blockIdx.y;
-    if (r >= row_end) return;
-    const int h1 = rt.h1[r];
-    const double xb = rt.xbar[r], yb = rt.ybar[r], tb = rt.thbar[r];
-    RowGeom g;
-    row_geometry(x1[h1], y1[h1], th1[h1], xb, yb, tb, pc, &g);
-    const ViewConst& c = vc[v];
-    double t3x, t3y;
-    reproject_tangent(g, c.R31, c.T31, &t3x, &t3y);
-    double lo, hi;
-    const int f = wedge_row(xb, yb, c.F32, c.e1_32[0], c.e1_32[1], c.e2_32[0], c.e2_32[1], pc.delta, pc.rows, pc.cols, &lo, &hi);
-    const int64_t o = int64_t(v) * (row_end - row_begin) + (r - row_begin);
-    w32[o] = make_double2(lo, hi);
-    tgt[o] = make_double2(t3x, t3y);
-    if (f) atomicAdd(&ctr->n_degenerate, 1ULL);
-}
-void launch_reproject(const PassConst& pc, const ViewConst* vc, const double* x1, const double* y1, const double* th1, RowTable rt, int64_t row_begin,
-                      int64_t row_end, double2* w32, double2* tgt, DevCounters* ctr, cudaStream_t st) {
-    const int64_t n = row_end - row_begin;
-    if (n <= 0 || pc.n_vali <= 0) return;
-    dim3 grid(unsigned((n + 127) / 128), pc.n_vali);
-    k_reproject<<<grid, 128, 0, st>>>(pc, vc, x1, y1, th1, rt, row_begin, row_end, w32, tgt, ctr);
-}
-
-// ----------------------------------------------------------------------------- validation: the support test
-// One warp per (group = view-1 edge, validation view).  The members of wedge31 are enumerated from the view's
-// angular bin grid (bins covered by [lo31, hi31], exact test on the staged angle), compacted into shared memory,
-// and every lane owns one hypothesis row: wedge32 membership (PairEdgeHypo.cpp:94), parallel-wedge test
-// (EdgeSketch_Core.hpp:112-128), orientation arg-max with the reference's first-maximum rule
-// (getSupportedEdgels.cpp:32-47: d >= thr && d > prev, ascending index -> ties go to the lowest index).
-#define SUP_WARPS 4
-#define SUP_TILE 64
-__global__ void __launch_bounds__(SUP_WARPS * 32) k_support(const __grid_constant__ SupportArgs a) {
-    __shared__ double sm_a32[SUP_WARPS][SUP_TILE];
-    __shared__ double sm_cs[SUP_WARPS][SUP_TILE];
-    __shared__ double sm_sn[SUP_WARPS][SUP_TILE];
-    __shared__ int32_t sm_idx[SUP_WARPS][SUP_TILE];
-    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    const int g = a.g_begin + blockIdx.x * SUP_WARPS + wid;
-    const int v = blockIdx.y;
-    if (g >= a.g_end) return;
-    const int64_t r_beg = a.group_off[g], r_end = a.group_off[g + 1];
-    if (r_end <= r_beg) return;
-    const double2 w1 = a.w31[int64_t(v) * a.w31_stride + g];
-    const bool w1_bad = (w1.x != w1.x);
-    int beg = 0, end = 0;
-    int64_t off = 0;
-    if (!w1_bad) {
-        const int view = a.vali_view[v];
-        off = a.edge_off[view];
-        const int32_t* bins = a.bg.bins + int64_t(v) * a.bg.BS;
-        const int b0 = bin_of(w1.x, a.bg.scale, a.bg.B), b1 = bin_of(w1.y, a.bg.scale, a.bg.B);
-        beg = (b0 == 0) ? 0 : bins[b0 - 1];
-        end = bins[b1];
-    }
-    const unsigned lt = lanemask_lt();
-    unsigned long long n_sup = 0, n_par = 0, n_deg = 0, n_inl = 0;
-    for (int64_t rc = r_beg; rc < r_end; rc += 32) {
-        const int64_t r = rc + lane;
-        const bool valid = r < r_end;
-        double2 w2 = make_double2(0, 0), tg = make_double2(0, 0);
+    unsigned long long c_sup = 0, c_par = 0, c_inl = 0, c_deg = 0;
+    if (u < a.U) {
+        const int h1 = a.ut.h1[u];
+        const unsigned long long mult = GIVEN ? 1ULL : (unsigned long long)a.ut.mult[u];
+        const double2 w1 = a.w31[int64_t(v) * a.w31_stride + h1];
+        double2 w2, tg;
+        if (GIVEN) {
+            w2 = a.w32_in[int64_t(v) * a.U + u];
+            tg = a.tgt_in[int64_t(v) * a.U + u];
+        } else {
+            const ViewConst& c = a.vc[v];
+            const double2 xy = a.ut.xy[u];
+            const double4 ge = a.ut.geom[u];
+            RowGeom g;
+            mat_vec(pc.K1inv, a.x1[h1], a.y1[h1], 1.0, g.G1);
+            g.rho1 = ge.x; g.Tv1[0] = ge.y; g.Tv1[1] = ge.z; g.Tv1[2] = ge.w;
+            reproject_tangent(g, c.R31, c.T31, &tg.x, &tg.y);
+            wedge_row(xy.x, xy.y, c.F32, c.e1_32[0], c.e1_32[1], c.e2_32[0], c.e2_32[1], a.delta, a.rows, a.cols, &w2.x, &w2.y);
+            if (a.w32_out) { a.w32_out[int64_t(v) * a.U + u] = w2; a.tgt_out[int64_t(v) * a.U + u] = tg; }
+        }
+        const bool w1_bad = (w1.x != w1.x), w2_bad = (w2.x != w2.x);
+        if (w2_bad) c_deg = mult;
         bool active = false;
-        if (valid) {
-            const int64_t o = int64_t(v) * a.chunk_rows + (r - a.row_base);
-            w2 = ldg2(a.w32 + o);
-            tg = ldg2(a.tgt + o);
-            const bool w2_bad = (w2.x != w2.x);
-            if (w2_bad) n_deg++;
-            if (!w1_bad && !w2_bad) {
-                const double d0 = fabs(w1.x - w2.x), d1 = fabs(w1.x - w2.y), d2 = fabs(w1.y - w2.x), d3 = fabs(w1.y - w2.y);
-                const double dmax = fmax(fmax(d0, d1), fmax(d2, d3));
-                if (dmax <= a.parallel_deg) n_par++;                        // hpp:120 (inclusive)
-                else active = true;
-            }
+        if (!w1_bad && !w2_bad) {
+            const double d0 = fabs(w1.x - w2.x), d1 = fabs(w1.x - w2.y), d2 = fabs(w1.y - w2.x), d3 = fabs(w1.y - w2.y);
+            const double dmax = fmax(fmax(d0, d1), fmax(d2, d3));
+            if (dmax <= a.parallel_deg) c_par = mult;                       // hpp:120 (inclusive)
+            else active = true;
         }
         double best = 0.0;   // prev_prod, getSupportedEdgels.cpp:33
         int bidx = -2;
-        if (__any_sync(FULL, active)) {
-            for (int tb = beg; tb < end; tb += SUP_TILE) {
-                int cnt = 0;
-#pragma unroll
-                for (int s = 0; s < SUP_TILE / 32; s++) {
-                    const int j = tb + s * 32 + lane;
-                    bool in = false;
-                    if (j < end) { const double a31 = a.s_a31[off + j]; in = (a31 > w1.x && a31 < w1.y); }
-                    const unsigned m = __ballot_sync(FULL, in);
-                    if (in) {
-                        const int p = cnt + __popc(m & lt);
-                        sm_a32[wid][p] = a.s_a32[off + j]; sm_cs[wid][p] = a.s_cs[off + j]; sm_sn[wid][p] = a.s_sn[off + j];
-                        sm_idx[wid][p] = a.s_idx[off + j];
-                    }
-                    cnt += __popc(m);
+        if (active) {
+            const int64_t off = a.edge_off[a.vali_view ? a.vali_view[v] : v];
+            const int32_t* bins1 = a.ix1.bins + int64_t(v) * a.bg.BS;
+            const int32_t* bins2 = a.ix2.bins + int64_t(v) * a.bg.BS;
+            const int p0 = bin_of(w1.x, a.bg.scale, a.bg.B), p1 = bin_of(w1.y, a.bg.scale, a.bg.B);
+            const int q0 = bin_of(w2.x, a.bg.scale, a.bg.B), q1 = bin_of(w2.y, a.bg.scale, a.bg.B);
+            const int beg1 = p0 ? bins1[p0 - 1] : 0, end1 = bins1[p1];
+            const int beg2 = q0 ? bins2[q0 - 1] : 0, end2 = bins2[q1];
+            const bool use1 = (end1 - beg1) <= (end2 - beg2);
+            const ViewIndex& ix = use1 ? a.ix1 : a.ix2;
+            const int beg = use1 ? beg1 : beg2, end = use1 ? end1 : end2;
+            const double2* __restrict__ ang = ix.ang + off;
+            const double2* __restrict__ tan_ = ix.tan + off;
+            const int32_t* __restrict__ idx_ = ix.idx + off;
+            unsigned n_in = 0;
+            for (int j = beg; j < end; j++) {
+                const double2 e = ang[j];
+                if (e.x > w1.x && e.x < w1.y && e.y > w2.x && e.y < w2.y) {          // PairEdgeHypo.cpp:94, both wedges
+                    n_in++;
+                    const double2 t = tan_[j];
+                    const double d = fabs(tg.x * t.x + tg.y * t.y);                   // getSupportedEdgels.cpp:38
+                    const int idx = idx_[j];
+                    if (d >= a.cos_thresh && (d > best || (d == best && bidx != -2 && idx < bidx))) { best = d; bidx = idx; }
                 }
-                __syncwarp();
-                if (active) {
-                    for (int k = 0; k < cnt; k++) {
-                        const double a32 = sm_a32[wid][k];
-                        if (a32 > w2.x && a32 < w2.y) {
-                            n_inl++;
-                            const double d = fabs(tg.x * sm_cs[wid][k] + tg.y * sm_sn[wid][k]);
-                            const int idx = sm_idx[wid][k];
-                            if (d >= a.cos_thresh && (d > best || (d == best && bidx != -2 && idx < bidx))) { best = d; bidx = idx; }
-                        }
-                    }
-                }
-                __syncwarp();
             }
+            c_inl = mult * n_in;
+            if (bidx != -2) c_sup = mult;
         }
-        if (valid) {
-            a.support[int64_t(v) * a.sup_stride + r] = bidx;
-            if (bidx != -2) n_sup++;
-        }
+        a.support[int64_t(v) * a.sup_stride + u] = bidx;
     }
-    // warp-aggregated statistics
+    if (a.ctr == nullptr) return;
+    // block-aggregated statistics -> one slot per block
+    __shared__ unsigned long long red[4][VAL_THREADS / 32];
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
-        n_sup += __shfl_xor_sync(FULL, n_sup, o); n_par += __shfl_xor_sync(FULL, n_par, o); n_deg += __shfl_xor_sync(FULL, n_deg, o);
-        n_inl += __shfl_xor_sync(FULL, n_inl, o);
+        c_sup += __shfl_xor_sync(FULL, c_sup, o); c_par += __shfl_xor_sync(FULL, c_par, o);
+        c_inl += __shfl_xor_sync(FULL, c_inl, o); c_deg += __shfl_xor_sync(FULL, c_deg, o);
     }
-    if (lane == 0 && a.ctr) {
-        if (n_sup) atomicAdd(&a.ctr->n_supported, n_sup);
-        if (n_par) atomicAdd(&a.ctr->n_parallel, n_par);
-        if (n_inl) atomicAdd(&a.ctr->n_inliers, n_inl);
-        (void)n_deg;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    if (lane == 0) { red[0][wid] = c_sup; red[1][wid] = c_par; red[2][wid] = c_inl; red[3][wid] = c_deg; }
+    __syncthreads();
+    if (threadIdx.x < 4) {
+        unsigned long long s = 0;
+        for (int w = 0; w < VAL_THREADS / 32; w++) s += red[threadIdx.x][w];
+        if (s) {
+            const int slot = (blockIdx.x + blockIdx.y) & (CVX_CTR_SLOTS - 1);
+            unsigned long long* dst = threadIdx.x == 0 ? a.ctr->n_supported : threadIdx.x == 1 ? a.ctr->n_parallel
+                                      : threadIdx.x == 2 ? a.ctr->n_inliers : a.ctr->n_degenerate;
+            atomicAdd(&dst[slot], s);
+        }
     }
 }
-void launch_support(const SupportArgs& a, cudaStream_t st) {
-    const int n = a.g_end - a.g_begin;
-    if (n <= 0 || a.n_vali <= 0) return;
-    dim3 grid((n + SUP_WARPS - 1) / SUP_WARPS, a.n_vali);
-    k_support<<<grid, SUP_WARPS * 32, 0, st>>>(a);
+void launch_validate(const PassConst& pc, const ValidateArgs& a, bool given, cudaStream_t st) {
+    if (a.U <= 0 || a.n_vali <= 0) return;
+    dim3 grid(unsigned((a.U + VAL_THREADS - 1) / VAL_THREADS), a.n_vali);
+    if (given) k_validate<true><<<grid, VAL_THREADS, 0, st>>>(pc, a);
+    else k_validate<false><<<grid, VAL_THREADS, 0, st>>>(pc, a);
 }
 
 // ----------------------------------------------------------------------------- vote + ratio test
-// EdgeSketch_Core.cpp:414-508.  One warp per view-1 edge.  flags bit0 = valid (count >= N), bit1 = passes count > ratio * max.
+// EdgeSketch_Core.cpp:414-427: number of validation views that support a hypothesis (per unique hypothesis).
+__global__ void __launch_bounds__(256) k_count_u(const int32_t* __restrict__ support, int64_t sup_stride, int64_t U, int n_vali,
+                                                 int32_t* __restrict__ count_u) {
+    const int64_t u = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+    if (u >= U) return;
+    int c = 0;
+    for (int v = 0; v < n_vali; v++) c += (support[int64_t(v) * sup_stride + u] != -2);
+    count_u[u] = c;
+}
+void launch_count_u(const int32_t* support, int64_t sup_stride, int64_t U, int n_vali, int32_t* count_u, cudaStream_t st) {
+    if (U > 0) k_count_u<<<unsigned((U + 255) / 256), 256, 0, st>>>(support, sup_stride, U, n_vali, count_u);
+}
+// EdgeSketch_Core.cpp:430-508.  One warp per view-1 edge.  flags bit0 = valid (count >= N), bit1 = passes count > ratio * max.
 __global__ void __launch_bounds__(128) k_select(const __grid_constant__ PassConst pc, const int64_t* __restrict__ row_off, int h1_begin, int h1_end,
-                                                const int32_t* __restrict__ support, int64_t sup_stride, RowTable rt, int32_t* n_valid, int32_t* n_sel) {
+                                                const int32_t* __restrict__ count_u, RowTable rt, int32_t* n_valid, int32_t* n_sel) {
     const int lane = threadIdx.x & 31;
     const int h1 = h1_begin + blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (h1 >= h1_end) return;
     const int64_t r0 = row_off[h1], r1 = row_off[h1 + 1];
     int maxc = 0, nv = 0;
     for (int64_t r = r0 + lane; r < r1; r += 32) {
-        int c = 0;
-        for (int v = 0; v < pc.n_vali; v++) c += (support[int64_t(v) * sup_stride + r] != -2);
+        const int c = count_u[rt.row_u[r]];
         rt.count[r] = c;
         if (c > 0 && c >= pc.max_support) { nv++; maxc = max(maxc, c); }   // :432
     }
@@ -562,11 +763,11 @@ __global__ void __launch_bounds__(128) k_select(const __grid_constant__ PassCons
     for (int o = 16; o > 0; o >>= 1) ns += __shfl_xor_sync(FULL, ns, o);
     if (lane == 0) { n_valid[h1] = nv; n_sel[h1] = ns; }
 }
-void launch_select(const PassConst& pc, const int64_t* row_off, int h1_begin, int h1_end, const int32_t* support, int64_t sup_stride, RowTable rt,
+void launch_select(const PassConst& pc, const int64_t* row_off, int h1_begin, int h1_end, const int32_t* count_u, RowTable rt,
                    int32_t* n_valid, int32_t* n_sel, cudaStream_t st) {
     const int n = h1_end - h1_begin;
     if (n <= 0) return;
-    k_select<<<(n + 3) / 4, 128, 0, st>>>(pc, row_off, h1_begin, h1_end, support, sup_stride, rt, n_valid, n_sel);
+    k_select<<<(n + 3) / 4, 128, 0, st>>>(pc, row_off, h1_begin, h1_end, count_u, rt, n_valid, n_sel);
 }
 __global__ void __launch_bounds__(128) k_select_fill(const int64_t* __restrict__ row_off, int h1_begin, int h1_end, RowTable rt,
                                                      const int64_t* __restrict__ valid_off, const int64_t* __restrict__ pair_off, int32_t* v_h1,
@@ -602,27 +803,30 @@ void launch_select_fill(const int64_t* row_off, int h1_begin, int h1_end, RowTab
     k_select_fill<<<(n + 3) / 4, 128, 0, st>>>(row_off, h1_begin, h1_end, rt, valid_off, pair_off, v_h1, v_row, v_count, v_sel, p_h1, p_h2rep, p_row,
                                               p_count);
 }
-__global__ void k_gather_supports(const int32_t* __restrict__ p_row, int64_t P, int n_vali, const int32_t* __restrict__ support, int64_t sup_stride,
-                                  int32_t* __restrict__ out) {
+__global__ void k_gather_supports(const int32_t* __restrict__ p_row, const int32_t* __restrict__ row_u, int64_t P, int n_vali,
+                                  const int32_t* __restrict__ support, int64_t sup_stride, int32_t* __restrict__ out) {
     const int64_t t = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
     if (t >= P * n_vali) return;
     const int64_t p = t / n_vali;
     const int v = int(t % n_vali);
-    out[t] = support[int64_t(v) * sup_stride + p_row[p]];
+    out[t] = support[int64_t(v) * sup_stride + row_u[p_row[p]]];
 }
-void launch_gather_supports(const int32_t* p_row, int64_t P, int n_vali, const int32_t* support, int64_t sup_stride, int32_t* out, cudaStream_t st) {
+void launch_gather_supports(const int32_t* p_row, const int32_t* row_u, int64_t P, int n_vali, const int32_t* support, int64_t sup_stride,
+                            int32_t* out, cudaStream_t st) {
     const int64_t n = P * n_vali;
-    if (n > 0) k_gather_supports<<<unsigned((n + 255) / 256), 256, 0, st>>>(p_row, P, n_vali, support, sup_stride, out);
+    if (n > 0) k_gather_supports<<<unsigned((n + 255) / 256), 256, 0, st>>>(p_row, row_u, P, n_vali, support, sup_stride, out);
 }
-// [V][stride] -> [H][V] (the reference's supported_indices layout) through a 32x32 shared-memory tile
-__global__ void k_transpose_support(const int32_t* __restrict__ support, int64_t sup_stride, int64_t H, int n_vali, int32_t* __restrict__ out) {
+// out[r][v] = support[v][row_u[r]] through a 32x32 shared-memory tile (reads coalesced over rows, writes over views)
+__global__ void k_expand_support(const int32_t* __restrict__ support, int64_t sup_stride, const int32_t* __restrict__ row_u, int64_t H, int n_vali,
+                                 int32_t* __restrict__ out) {
     __shared__ int32_t tile[32][33];
     const int64_t r0 = blockIdx.x * 32LL;
     const int v0 = blockIdx.y * 32;
+    const int64_t rr = r0 + threadIdx.x;
+    const int64_t u = rr < H ? row_u[rr] : 0;
     for (int k = threadIdx.y; k < 32; k += blockDim.y) {
         const int v = v0 + k;
-        const int64_t r = r0 + threadIdx.x;
-        tile[k][threadIdx.x] = (v < n_vali && r < H) ? support[int64_t(v) * sup_stride + r] : 0;
+        tile[k][threadIdx.x] = (v < n_vali && rr < H) ? support[int64_t(v) * sup_stride + u] : 0;
     }
     __syncthreads();
     for (int k = threadIdx.y; k < 32; k += blockDim.y) {
@@ -631,12 +835,12 @@ __global__ void k_transpose_support(const int32_t* __restrict__ support, int64_t
         if (r < H && v < n_vali) out[r * n_vali + v] = tile[threadIdx.x][k];
     }
 }
-void launch_transpose_support(const int32_t* support, int64_t sup_stride, int64_t H, int n_vali, int32_t* out, cudaStream_t st) {
+void launch_expand_support(const int32_t* support, int64_t sup_stride, const int32_t* row_u, int64_t H, int n_vali, int32_t* out,
+                           cudaStream_t st) {
     if (H <= 0 || n_vali <= 0) return;
     dim3 grid(unsigned((H + 31) / 32), (n_vali + 31) / 32), block(32, 8);
-    k_transpose_support<<<grid, block, 0, st>>>(support, sup_stride, H, n_vali, out);
+    k_expand_support<<<grid, block, 0, st>>>(support, sup_stride, row_u, H, n_vali, out);
 }
-
 // ----------------------------------------------------------------------------- finalize
 // Finalize_Edge_Pairs_and_Reconstruct_3D_Edges geometry (EdgeSketch_Core.cpp:625-676) + Stack_3D_Edges transform (:742-748)
 __global__ void __launch_bounds__(128) k_finalize(const __grid_constant__ PassConst pc, const double* __restrict__ x1, const double* __restrict__ y1,

@@ -209,12 +209,9 @@ def algorithmic_bytes(kernel, c, V, edges_vali):
     """Algorithmic HBM bytes of one launch of `kernel` (DESIGN.md "Kernels and rooflines").
     c = counts of the pass, edges_vali = sum over validation views of E3."""
     HV, H = c["n_validations"], c["n_hypotheses"]
-    if kernel == "support":       # wedge31 + wedge32 + tangent in (48 B), support index out (4 B), (cos, sin) of every inlier,
-        return 52 * HV + 16 * c["n_inliers"] + 32 * edges_vali      # + one compulsory read of each staged view (32 B / edge)
-    if kernel == "reproject":     # clustered row in (x, y, theta, h1: 28 B, once per row), wedge32 + tangent out (32 B)
-        return 32 * HV + 28 * H + 24 * c["n_h1_total"]
-    if kernel == "validate":      # fused: support index out + hypothesis read once per row + staged views once
-        return 4 * HV + 48 * H + 32 * edges_vali
+    if kernel == "validate":      # fused reprojection + wedge + support test, one evaluation per (cluster, view):
+        U = c["n_unique_hypotheses"]   # support index out (4 B) + wedge31 in (16 B) per evaluation, hypothesis (56 B) once,
+        return (4 + 16) * U * V + 56 * U + 16 * c["n_inliers"] + 72 * edges_vali   # (cos,sin) per inlier, indexes once
     if kernel == "form":          # view-2 angle list (8 B / edge) per warp is L2-resident: compulsory = once + rows out
         return 8 * c["n_h1_total"] * 0 + 100 * H + 40 * c["n_candidates"]
     raise KeyError(kernel)
@@ -297,7 +294,7 @@ def run_b200(args, rank, world, local_rank):
         sampler = ClockSampler(local_rank)
         sampler.start()
         ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
-        parts = {k: 0.0 for k in ("set_pair_ms", "form_ms", "reproject_ms", "support_ms", "select_ms", "finalize_ms", "run_ms")}
+        parts = {k: 0.0 for k in ("set_pair_ms", "form_ms", "prep_ms", "validate_ms", "select_ms", "finalize_ms", "run_ms")}
         barrier()
         wall0 = time.perf_counter()
         for i in range(args.steps):
@@ -342,10 +339,10 @@ def run_b200(args, rank, world, local_rank):
     ms_per_step = dev_ms / args.steps
     value = vals_all / (ms_per_step * 1e-3)
     # ---- roofline of the dominant kernel (rank 0's pass), event-timed inside the library on the launching stream
-    ktime = {k: parts[k + "_ms"] / args.steps for k in ("form", "reproject", "support", "select")}
+    ktime = {k: parts[k + "_ms"] / args.steps for k in ("form", "prep", "validate", "select")}
     ktime = {k: v for k, v in ktime.items() if v > 0}
     dom = max(ktime, key=ktime.get)
-    kname = {"reproject": "k_reproject", "support": "k_support", "form": "k_form<true>", "select": "k_select"}.get(dom, dom)
+    kname = {"validate": "k_validate<false>", "form": "k_form<true>", "select": "k_select", "prep": "k_wedge31"}.get(dom, dom)
     edges_vali = sum(len(scene.edges[v]) for v in range(scene.n_views) if v not in pair)
     peak, peak_src = peaks()
     try:
@@ -357,16 +354,16 @@ def run_b200(args, rank, world, local_rank):
             "peak_source": peak_src, "kernel_ms": ktime[dom], "algorithmic_bytes": abytes,
             "kernel_ms_all": {k: round(v, 4) for k, v in ktime.items()},
             "note": "FP64-transcendental bound, not HBM bound (DESIGN.md): ~1.3k FP64 flop-equivalents per validation vs a few bytes"}
-    sup_ms = parts["support_ms"] / args.steps
-    if sup_ms > 0:
-        sb = algorithmic_bytes("support", counts, V, edges_vali)
-        roof["support_test"] = {"kernel": "k_support", "kernel_ms": sup_ms, "algorithmic_bytes": sb,
-                                "achieved": sb / (sup_ms * 1e-3) / 1e9, "frac": sb / (sup_ms * 1e-3) / 1e9 / peak}
+    val_ms = parts["validate_ms"] / args.steps
+    if val_ms > 0 and dom != "validate":
+        sb = algorithmic_bytes("validate", counts, V, edges_vali)
+        roof["validate_kernel"] = {"kernel": "k_validate<false>", "kernel_ms": val_ms, "algorithmic_bytes": sb,
+                                   "achieved": sb / (val_ms * 1e-3) / 1e9, "frac": sb / (val_ms * 1e-3) / 1e9 / peak}
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
             "data": "synthetic",
             "config": {"workload": workload_name(args.workload, scene, world), "l2": f"flushed between timed iterations ({L2_FLUSH_BYTES >> 20} MiB write)",
-                       "validations_per_step": vals_all, "hypotheses_rank0": counts["n_hypotheses"], "pairs_rank0": counts["n_pairs"],
+                       "validations_per_step": vals_all, "hypotheses_rank0": counts["n_hypotheses"], "unique_hypotheses_rank0": counts["n_unique_hypotheses"], "pairs_rank0": counts["n_pairs"],
                        "parallelism": "1 GPU" if world == 1 else f"{world} GPUs, one hypothesis view pair per GPU, NCCL gather of results"},
             "clocks": clocks,
             "e2e": {"value": vals_all * args.steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": h2d_all, "d2h_bytes_per_step": d2h_all,

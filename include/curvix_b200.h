@@ -65,6 +65,7 @@ typedef struct cvx_counts {
     int64_t n_supported;         /* validations that returned a support index != -2 */
     int64_t n_parallel;          /* validations short-circuited by is_Epipolar_Wedges_in_Parallel */
     int64_t n_inliers;           /* sum over validations of |wedge31 ∩ wedge32| (edges that reached getSupportIdx) */
+    int64_t n_unique_hypotheses; /* clusters: rows of one cluster carry the same averaged edge and are validated once */
 } cvx_counts;
 
 typedef struct cvx_ctx cvx_ctx;
@@ -117,7 +118,10 @@ int cvx_get_rows(cvx_ctx* ctx, int32_t* h1, int32_t* h2_orig, int32_t* local_idx
 
 /* replaces all_supported_indices (EdgeSketch_Core.hpp:160): H x V int32 row-major, -2 = no support */
 int cvx_get_support_matrix(cvx_ctx* ctx, int32_t* out);
-/* Intermediates of the validation stage (debug/parity): wedge31 (E1 x V x 2), wedge32 and tgt (H x V x 2). */
+/* Intermediates of the validation stage (debug/parity): wedge31 (E1 x V x 2), wedge32 and tgt (H x V x 2).  wedge32 / tgt are
+ * only materialised when cvx_set_keep_intermediates(ctx, 1) was called before the run (the production path keeps them in
+ * registers). */
+int cvx_set_keep_intermediates(cvx_ctx* ctx, int on);
 int cvx_get_intermediates(cvx_ctx* ctx, double* wedge31, double* wedge32, double* tgt);
 
 /* Rows with count >= max_support_views, ascending (h1,row): the input of the reference's std::sort + ratio test
@@ -153,7 +157,10 @@ int cvx_get_device_results(cvx_ctx* ctx, cvx_device_results* out);
 /* Timing of the last phases on the context stream (CUDA events, milliseconds). */
 typedef struct cvx_timings {
     float set_pair_ms; float run_ms; float finalize_ms;
-    float form_ms; float reproject_ms; float support_ms; float select_ms;
+    float form_ms;      /* candidate search + epipolar correction + clustering */
+    float prep_ms;      /* unique-hypothesis table + wedge of the view-1 edges in every validation view */
+    float validate_ms;  /* the validation kernel: reprojection + wedge + parallel test + support test */
+    float select_ms;    /* vote + ratio test + compaction */
     int32_t kernel_launches; int32_t pad;
 } cvx_timings;
 int cvx_get_timings(cvx_ctx* ctx, cvx_timings* out);

@@ -554,7 +554,7 @@ struct H1Result {
     std::vector<int> selected_order;          // rows in paired_edge order (after std::sort + ratio + capacity)
     std::vector<char> valid_selected;
     std::vector<std::pair<int, std::vector<int>>> clusters;  // (orig key, members)
-    int64_t n_degenerate = 0, n_supported = 0, n_parallel = 0, n_inliers = 0;
+    int64_t n_degenerate = 0, n_supported = 0, n_parallel = 0, n_inliers = 0, n_clusters = 0;
 };
 
 // getHYPO2_idx_Ore, PairEdgeHypo.cpp:88-102 (faithful: copies the list, strict both sides)
@@ -634,6 +634,7 @@ void process_h1(const orc_ctx& o, int H1, int mode, bool keep, const std::vector
     ClusterOut co;
     cl.run(&co);
     r->xbar = co.xbar; r->ybar = co.ybar; r->thbar = co.thbar; r->label = co.label;
+    for (int k = 0; k < n; k++) if (co.label[k] == k) r->n_clusters++;   // a label in use is the index of one of its members
     r->h2rep.resize(n);
     for (int k = 0; k < n; k++) r->h2rep[k] = r->h2orig[co.rep_local[k]];  // corrected(closest, 8)  EdgeClusterer.cpp:282
     r->rawat.resize(n);
@@ -860,7 +861,7 @@ int orc_run_edge_sketch(orc_ctx* o, int h1_begin, int h1_end, int mode, int num_
         if (!r.processed) continue;
         o->off_of_h1[H1] = off;
         c.n_h1_processed++; c.n_hypotheses += r.n; c.n_validations += int64_t(r.n) * V;
-        c.n_degenerate_wedges += r.n_degenerate; c.n_supported += r.n_supported; c.n_parallel += r.n_parallel; c.n_inliers += r.n_inliers;
+        c.n_degenerate_wedges += r.n_degenerate; c.n_supported += r.n_supported; c.n_parallel += r.n_parallel; c.n_inliers += r.n_inliers; c.n_unique_hypotheses += r.n_clusters;
         for (int k = 0; k < r.n; k++) {
             o->row_h1.push_back(H1); o->row_h2orig.push_back(r.h2orig[k]); o->row_local.push_back(r.local[k]);
             o->row_rawat.push_back(r.rawat[k]); o->row_label.push_back(r.label[k]); o->row_h2rep.push_back(r.h2rep[k]);

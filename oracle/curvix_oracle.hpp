@@ -53,6 +53,7 @@ typedef struct orc_counts {
     int64_t n_supported;       // validations with a support index != -2
     int64_t n_parallel;        // validations short-circuited by the parallel-wedge test
     int64_t n_inliers;         // sum over validations of |wedge31 ∩ wedge32|
+    int64_t n_unique_hypotheses; // clusters (sum over processed view-1 edges)
 } orc_counts;
 
 typedef struct orc_ctx orc_ctx;

@@ -28,7 +28,7 @@ class OrcConfig(C.Structure):
 class OrcCounts(C.Structure):
     _fields_ = [(n, C.c_int64) for n in (
         "n_h1_total", "n_h1_processed", "n_candidates", "n_hypotheses", "n_validations", "n_valid_rows",
-        "n_pairs", "n_degenerate_wedges", "n_supported", "n_parallel", "n_inliers")]
+        "n_pairs", "n_degenerate_wedges", "n_supported", "n_parallel", "n_inliers", "n_unique_hypotheses")]
 
     def as_dict(self):
         return {n: int(getattr(self, n)) for n, _ in self._fields_}

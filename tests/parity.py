@@ -80,7 +80,7 @@ def compare(orc, gpu, check_intermediates=False, check_finalize=True):
     rep["counts_oracle"], rep["counts_gpu"] = c_o, c_g
     exact = (not bad_h1) and n_sup_diff == 0
     if exact:
-        for k in ("n_h1_processed", "n_candidates", "n_hypotheses", "n_validations", "n_valid_rows", "n_supported", "n_parallel", "n_inliers",
+        for k in ("n_h1_processed", "n_candidates", "n_hypotheses", "n_validations", "n_valid_rows", "n_supported", "n_parallel", "n_inliers", "n_unique_hypotheses",
                   "n_degenerate_wedges"):
             assert c_o[k] == c_g[k], f"count {k}: oracle {c_o[k]} gpu {c_g[k]}"
     # ---- vote / selection, compared per view-1 edge on (h1, row within the edge); edges with a near-threshold

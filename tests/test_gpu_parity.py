@@ -15,6 +15,7 @@ def _gpu(scene, **cfg_kw):
     api = pkg("api")
     cfg = api.default_config(n_views=scene.n_views, img_rows=scene.rows, img_cols=scene.cols, **cfg_kw)
     g = api.EdgeSketch(cfg, 0)
+    g.keep_intermediates(True)    # parity runs compare wedge32 / reprojected tangents too (production keeps them in registers)
     g.set_cameras(scene.R, scene.T, scene.K)
     for v, e in enumerate(scene.edges):
         g.set_view_edges(v, e)
@@ -82,16 +83,17 @@ def test_h1_range_sharding_is_exact(oracle_mod, abc_scene):
         assert np.array_equal(np.concatenate([f[k] for _, f in parts]), fin[k])
 
 
-def test_chunked_run_matches_unchunked(oracle_mod, abc_scene, monkeypatch):
-    """The hypothesis rows are processed in chunks when the per-validation intermediates exceed the budget."""
+def test_intermediates_off_gives_identical_results(oracle_mod, abc_scene):
+    """The production path (wedge32 / tangent kept in registers) and the parity path (materialised) agree bit for bit."""
     g = _gpu(abc_scene)
     g.set_pair(47, 42); g.run()
     s_full = g.support_matrix(); p_full = g.pairs()
-    monkeypatch.setenv("CVX_INTER_BUDGET_MB", "8")
-    g2 = _gpu(abc_scene)
-    g2.set_pair(47, 42); g2.run()
-    assert np.array_equal(g2.support_matrix(), s_full)
-    assert np.array_equal(g2.pairs()["row"], p_full["row"])
+    g.keep_intermediates(False)
+    g.run()
+    assert np.array_equal(g.support_matrix(), s_full)
+    assert np.array_equal(g.pairs()["row"], p_full["row"]) and np.array_equal(g.pairs()["supports"], p_full["supports"])
+    with pytest.raises(Exception):
+        g.intermediates()
 
 
 def test_edge_cases(oracle_mod, data_mod):
