@@ -1,0 +1,58 @@
+"""The oracle against its committed goldens (tests/golden/oracle_abc_47_42.npz, made by make_oracle_goldens.py) and against
+itself: faithful mode (the reference's loop nest) == hoisted mode, thread-count independence, H1-range additivity."""
+import os
+
+import numpy as np
+
+from conftest import ROOT, make_oracle
+
+GOLD = os.path.join(ROOT, "tests", "golden", "oracle_abc_47_42.npz")
+
+
+def test_abc_pass_matches_committed_goldens(oracle_mod, abc_scene):
+    g = np.load(GOLD)
+    o = make_oracle(oracle_mod, abc_scene)
+    o.set_pair(47, 42)
+    c = o.run(mode=1)
+    assert dict(zip(g["count_names"].tolist(), g["counts"].tolist())) == c
+    t, r, p, f = o.h1_table(), o.rows(), o.pairs(), o.finalize()
+    assert np.array_equal(t["m"], g["m"]) and np.array_equal(t["n"], g["n"])
+    for k, gk in (("label", "label"), ("h2_orig", "h2_orig"), ("h2_rep", "h2_rep"), ("count", "row_count")):
+        assert np.array_equal(r[k], g[gk])
+    assert np.array_equal(p["h1"], g["pair_h1"]) and np.array_equal(p["h2rep"], g["pair_h2rep"])
+    assert np.array_equal(p["count"], g["pair_count"]) and np.array_equal(p["supports"], g["pair_supports"])
+    assert np.array_equal(f["nan_flag"], g["nan_flag"])
+    assert np.allclose(f["gamma_world"], g["gamma_world"], rtol=1e-12, atol=1e-14)
+    assert np.allclose(f["tangent_world"], g["tangent_world"], rtol=1e-12, atol=1e-14)
+    # sanity of the reconstruction itself: the object sits in the unit ball around the origin (ABC-NEF normalisation)
+    ok = g["nan_flag"] == 0
+    assert np.median(np.linalg.norm(g["gamma_world"][ok], axis=1)) < 1.0
+    assert np.allclose(np.linalg.norm(g["tangent_world"][ok], axis=1), 1.0, atol=1e-9)
+
+
+def test_faithful_equals_hoisted_and_threads(oracle_mod, tiny_scene):
+    scene, w = tiny_scene
+    o = make_oracle(oracle_mod, scene, max_support_views=w["max_support_views"])
+    o.set_pair(0, 1)
+    c1 = o.run(mode=1, threads=1); s1 = o.support_matrix(); p1 = o.pairs(); f1 = o.finalize()
+    c0 = o.run(mode=0, threads=3); s0 = o.support_matrix(); p0 = o.pairs(); f0 = o.finalize()
+    assert c0 == c1 and np.array_equal(s0, s1)
+    for k in ("h1", "h2rep", "count", "supports"):
+        assert np.array_equal(p0[k], p1[k])
+    assert np.array_equal(f0["gamma_world"], f1["gamma_world"]) and np.array_equal(f0["tangent_world"], f1["tangent_world"])
+    assert c1["n_pairs"] > 0
+
+
+def test_h1_range_additivity(oracle_mod, tiny_scene):
+    scene, w = tiny_scene
+    o = make_oracle(oracle_mod, scene, max_support_views=w["max_support_views"])
+    o.set_pair(2, 3)
+    full = o.run(mode=1); pf = o.pairs()
+    E1 = len(scene.edges[2])
+    parts = []
+    tot = 0
+    for a, b in ((0, E1 // 2), (E1 // 2, E1)):
+        c = o.run(a, b, mode=1); tot += c["n_validations"]; parts.append(o.pairs())
+    assert tot == full["n_validations"]
+    assert np.array_equal(np.concatenate([p["h1"] for p in parts]), pf["h1"])
+    assert np.array_equal(np.concatenate([p["supports"] for p in parts]), pf["supports"])
