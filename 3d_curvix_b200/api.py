@@ -16,6 +16,7 @@ SYMBOLS = [
     "cvx_set_hypothesis_pair", "cvx_run_edge_sketch", "cvx_get_counts", "cvx_get_h2_angles", "cvx_get_h1_wedges",
     "cvx_get_h1_table", "cvx_get_rows", "cvx_get_support_matrix", "cvx_set_keep_intermediates", "cvx_get_intermediates", "cvx_get_valid_rows",
     "cvx_get_pairs", "cvx_get_reference_order", "cvx_finalize", "cvx_get_device_results", "cvx_get_timings", "cvx_synchronize", "cvx_get_stream",
+    "cvx_claims_reset", "cvx_claims_accumulate", "cvx_claims_get_counts", "cvx_claims_get_mask",
     "cvx_support_problem_create", "cvx_support_problem_run", "cvx_support_problem_result", "cvx_support_problem_destroy",
 ]
 
@@ -240,6 +241,24 @@ class EdgeSketch:
         gc = np.empty((P, 3)); gw = np.empty((P, 3)); tw = np.empty((P, 3)); h2c = np.empty((P, 2)); nf = np.empty(P, np.int32)
         self._ck(self.lib.cvx_finalize(self.h, _vp(gc), _vp(gw), _vp(tw), _vp(h2c), _vp(nf)))
         return dict(gamma_cam=gc, gamma_world=gw, tangent_world=tw, h2_corrected=h2c, nan_flag=nf)
+
+    def claims_reset(self):
+        self._ck(self.lib.cvx_claims_reset(self.h))
+
+    def claims_accumulate(self):
+        """Mark the edges claimed by the accepted pairs of the last run (EdgeSketch_Core.cpp:682-726, 785-797)."""
+        self._ck(self.lib.cvx_claims_accumulate(self.h))
+
+    def claims_counts(self):
+        n = self.cfg.n_views
+        claimed = np.empty(n, np.int64); total = np.empty(n, np.int64)
+        self._ck(self.lib.cvx_claims_get_counts(self.h, _vp(claimed), _vp(total)))
+        return claimed, total
+
+    def claims_mask(self, view):
+        out = np.zeros(self.n_edges[view], np.uint8)
+        self._ck(self.lib.cvx_claims_get_mask(self.h, view, _vp(out)))
+        return out.astype(bool)
 
     def device_results(self):
         r = CvxDeviceResults()

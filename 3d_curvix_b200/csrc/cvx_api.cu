@@ -139,6 +139,11 @@ struct cvx_ctx {
     DevBuf<int32_t> v_h1, v_row, v_count, v_sel, p_h1, p_h2rep, p_row, p_count, p_sup, f_nan;
     DevBuf<double> f_gc, f_gw, f_tw, f_h2c;
     std::vector<int64_t> h_row_off;
+    // claimed-edge bitmap over the arena (one bit per edge slot) + per-view popcounts
+    uint32_t* d_claim = nullptr;
+    size_t claim_words = 0;
+    DevBuf<unsigned long long> d_claim_cnt;
+    DevBuf<uint8_t> d_claim_mask;
     cvx_counts counts;
     cvx_timings tm;
     cudaEvent_t ev[8];
@@ -209,6 +214,16 @@ int grow_arena(cvx_ctx* ctx, size_t need) {
     CU(regrow(ea.ang, 0, cap, st)); CU(regrow(ea.bin1, 0, cap, st)); CU(regrow(ea.bin2, 0, cap, st));
     CU(regrow(ea.ix1.ang, 0, cap, st)); CU(regrow(ea.ix1.tan, 0, cap, st)); CU(regrow(ea.ix1.idx, 0, cap, st));
     CU(regrow(ea.ix2.ang, 0, cap, st)); CU(regrow(ea.ix2.tan, 0, cap, st)); CU(regrow(ea.ix2.idx, 0, cap, st));
+    if (ctx->d_claim) {   // the claim bitmap covers the arena: grow it with the arena, new words cleared
+        const size_t words = cap / 32;
+        uint32_t* q = nullptr;
+        CU(cudaMalloc(&q, words * 4));
+        CU(cudaMemsetAsync(q, 0, words * 4, st));
+        CU(cudaMemcpyAsync(q, ctx->d_claim, ctx->claim_words * 4, cudaMemcpyDeviceToDevice, st));
+        CU(cudaStreamSynchronize(st));
+        cudaFree(ctx->d_claim);
+        ctx->d_claim = q; ctx->claim_words = words;
+    }
     ctx->arena_cap = cap;
     return CVX_OK;
 }
@@ -287,6 +302,8 @@ int cvx_destroy(cvx_ctx* ctx) {
     DevBuf<double2>* d2[] = {&ctx->d_wedge_h1, &ctx->u_xy, &ctx->d_w31, &ctx->d_w32, &ctx->d_tgt};
     for (auto* b : d2) b->release();
     ctx->u_geom.release(); ctx->d_vc.release(); ctx->d_ctr.release();
+    if (ctx->d_claim) cudaFree(ctx->d_claim);
+    ctx->d_claim_cnt.release(); ctx->d_claim_mask.release();
     for (auto& e : ctx->ev) cudaEventDestroy(e);
     cudaStreamDestroy(ctx->stream);
     delete ctx;
@@ -322,6 +339,8 @@ int cvx_set_view_edges(cvx_ctx* ctx, int view, int n, const double* x, const dou
     ctx->edge_n[view] = n;
     ctx->tables_dirty = true;
     const int64_t off = ctx->edge_off[view];
+    if (ctx->d_claim && ctx->edge_cap[view] > 0)   // new edges for this view: its claims no longer mean anything
+        CU(cudaMemsetAsync(ctx->d_claim + off / 32, 0, size_t(ctx->edge_cap[view]) / 32 * 4, ctx->stream));
     if (n > 0) {
         CU(cudaMemcpyAsync(ctx->ea.x + off, x, size_t(n) * 8, cudaMemcpyHostToDevice, ctx->stream));
         CU(cudaMemcpyAsync(ctx->ea.y + off, y, size_t(n) * 8, cudaMemcpyHostToDevice, ctx->stream));
@@ -701,6 +720,72 @@ int cvx_get_device_results(cvx_ctx* ctx, cvx_device_results* out) {
     out->n_pairs = ctx->P; out->n_vali_views = ctx->n_vali; out->pad = 0;
     out->pair_h1 = ctx->p_h1.p; out->pair_h2rep = ctx->p_h2rep.p; out->pair_count = ctx->p_count.p; out->pair_supports = ctx->p_sup.p;
     out->gamma_cam = ctx->f_gc.p; out->gamma_world = ctx->f_gw.p; out->tangent_world = ctx->f_tw.p;
+    return CVX_OK;
+}
+
+// ------------------------------------------------------------------------------------------------------------------
+// claimed edges (EdgeSketch_Core.cpp:776-813)
+// ------------------------------------------------------------------------------------------------------------------
+int cvx_claims_reset(cvx_ctx* ctx) {
+    if (!ctx) return CVX_ERR_INVALID;
+    CU(cudaSetDevice(ctx->device));
+    const size_t words = std::max<size_t>(ctx->arena_cap / 32, 1);
+    if (!ctx->d_claim || ctx->claim_words != words) {
+        if (ctx->d_claim) cudaFree(ctx->d_claim);
+        ctx->d_claim = nullptr;
+        CU(cudaMalloc(&ctx->d_claim, words * 4));
+        ctx->claim_words = words;
+    }
+    CU(cudaMemsetAsync(ctx->d_claim, 0, words * 4, ctx->stream));
+    return CVX_OK;
+}
+int cvx_claims_accumulate(cvx_ctx* ctx) {
+    if (!ctx || !ctx->have_run) return fail(ctx, CVX_ERR_INVALID, "cvx_claims_accumulate: no run");
+    CU(cudaSetDevice(ctx->device));
+    if (!ctx->d_claim) { const int rc = cvx_claims_reset(ctx); if (rc) return rc; }
+    const int rc = run_finalize(ctx);   // the NaN / dropped-representative flags decide which pairs reach the insertions
+    if (rc) return rc;
+    ClaimArgs a;
+    a.p_h1 = ctx->p_h1.p; a.p_h2rep = ctx->p_h2rep.p; a.p_sup = ctx->p_sup.p; a.nan_flag = ctx->f_nan.p; a.P = ctx->P;
+    a.row_off = ctx->d_row_off.p; a.rawat = ctx->r_rawat.p; a.label = ctx->r_label.p;
+    a.vali_view = ctx->d_vali.p; a.edge_off = ctx->d_edge_off.p; a.n_vali = ctx->n_vali; a.view1 = ctx->h1; a.view2 = ctx->h2;
+    a.E2 = ctx->edge_n[ctx->h2]; a.bits = ctx->d_claim;
+    launch_claim_pairs(a, ctx->stream);
+    ctx->tm.kernel_launches++;
+    CU(cudaGetLastError());
+    return CVX_OK;
+}
+int cvx_claims_get_counts(cvx_ctx* ctx, int64_t* claimed, int64_t* total) {
+    if (!ctx) return CVX_ERR_INVALID;
+    CU(cudaSetDevice(ctx->device));
+    const int N = ctx->n_views;
+    if (total) for (int v = 0; v < N; v++) total[v] = ctx->edge_n[v];
+    if (!claimed) return CVX_OK;
+    if (!ctx->d_claim) { for (int v = 0; v < N; v++) claimed[v] = 0; return CVX_OK; }
+    const int rc = sync_tables(ctx);
+    if (rc) return rc;
+    CU(ctx->d_claim_cnt.reserve(N));
+    launch_claim_count(ctx->d_claim, ctx->d_edge_off.p, ctx->d_edge_n.p, N, ctx->d_claim_cnt.p, ctx->stream);
+    ctx->tm.kernel_launches++;
+    std::vector<unsigned long long> h(N);
+    CU(cudaMemcpyAsync(h.data(), ctx->d_claim_cnt.p, size_t(N) * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    CU(cudaGetLastError());
+    for (int v = 0; v < N; v++) claimed[v] = int64_t(h[v]);
+    return CVX_OK;
+}
+int cvx_claims_get_mask(cvx_ctx* ctx, int view, uint8_t* out) {
+    if (!ctx || !out || view < 0 || view >= ctx->n_views) return fail(ctx, CVX_ERR_INVALID, "cvx_claims_get_mask: bad arguments");
+    CU(cudaSetDevice(ctx->device));
+    const int n = ctx->edge_n[view];
+    if (n == 0) return CVX_OK;
+    if (!ctx->d_claim) { std::memset(out, 0, size_t(n)); return CVX_OK; }
+    CU(ctx->d_claim_mask.reserve(size_t(n)));
+    launch_claim_expand(ctx->d_claim, ctx->edge_off[view], n, ctx->d_claim_mask.p, ctx->stream);
+    ctx->tm.kernel_launches++;
+    CU(cudaMemcpyAsync(out, ctx->d_claim_mask.p, size_t(n), cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    CU(cudaGetLastError());
     return CVX_OK;
 }
 

@@ -876,4 +876,70 @@ void launch_finalize(const PassConst& pc, const double* x1, const double* y1, co
                                                          h2c, nan_flag);
 }
 
+// ----------------------------------------------------------------------------- claimed edges (next-view selection input)
+// The reference walks edge_3D_to_supporting_edges and inserts (image, edge) of every supporting record into one std::set per
+// view (EdgeSketch_Core.cpp:785-797).  The records of a pass are, per accepted pair that reached the insertions
+// (EdgeSketch_Core.cpp:682-726): the view-1 edge, the view-2 representative, the members of its cluster as looked up through
+// hypo2_clusters[(h1, h2rep)] (key = HYPO2_idx_raw(local row), EdgeClusterer.cpp:216-236; default {h2rep}), and the
+// supporting edge of every validation view.  One warp per accepted pair sets the corresponding bits.
+__device__ __forceinline__ void claim_bit(uint32_t* bits, int64_t off, int idx) {
+    const int64_t e = off + idx;
+    atomicOr(&bits[e >> 5], 1u << (e & 31));
+}
+__global__ void __launch_bounds__(128) k_claim_pairs(const __grid_constant__ ClaimArgs a) {
+    const int lane = threadIdx.x & 31;
+    const int64_t p = blockIdx.x * int64_t(blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (p >= a.P) return;
+    if (a.nan_flag[p] != 0) return;                       // `continue` before the insertions (:639-642, :658-663)
+    const int h1 = a.p_h1[p], h2 = a.p_h2rep[p];
+    const int64_t off1 = a.edge_off[a.view1], off2 = a.edge_off[a.view2];
+    if (lane == 0) { claim_bit(a.bits, off1, h1); claim_bit(a.bits, off2, h2); }
+    for (int v = lane; v < a.n_vali; v += 32) {           // :694-724
+        const int s = a.p_sup[p * a.n_vali + v];
+        if (s != -2) claim_bit(a.bits, a.edge_off[a.vali_view[v]], s);
+    }
+    // cluster members: find the row whose raw_at_local equals h2rep (the map key), then every row with its label
+    const int64_t r0 = a.row_off[h1], r1 = a.row_off[h1 + 1];
+    int key_label = -1;
+    for (int64_t rc = r0; rc < r1; rc += 32) {
+        const int64_t r = rc + lane;
+        const bool hit = r < r1 && a.rawat[r] == h2;
+        const unsigned m = __ballot_sync(FULL, hit);
+        if (m) { key_label = __shfl_sync(FULL, hit ? a.label[r] : 0, __ffs(m) - 1); break; }
+    }
+    if (key_label < 0) return;                            // not a key: get_edges_in_same_cluster returns {h2rep} (hpp:193-202)
+    for (int64_t r = r0 + lane; r < r1; r += 32)
+        if (a.label[r] == key_label) { const int mi = a.rawat[r]; if (mi >= 0 && mi < a.E2) claim_bit(a.bits, off2, mi); }   // :686
+}
+void launch_claim_pairs(const ClaimArgs& a, cudaStream_t st) {
+    if (a.P > 0) k_claim_pairs<<<unsigned((a.P + 3) / 4), 128, 0, st>>>(a);
+}
+__global__ void __launch_bounds__(256) k_claim_count(const uint32_t* __restrict__ bits, const int64_t* __restrict__ edge_off,
+                                                     const int32_t* __restrict__ edge_n, unsigned long long* out) {
+    const int v = blockIdx.y;
+    const int64_t w0 = edge_off[v] >> 5;
+    const int n = edge_n[v], nw = (n + 31) >> 5;
+    int c = 0;
+    for (int w = blockIdx.x * blockDim.x + threadIdx.x; w < nw; w += gridDim.x * blockDim.x) {
+        uint32_t b = bits[w0 + w];
+        if (w == nw - 1 && (n & 31)) b &= (1u << (n & 31)) - 1u;
+        c += __popc(b);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(FULL, c, o);
+    if ((threadIdx.x & 31) == 0 && c) atomicAdd(&out[v], (unsigned long long)c);
+}
+void launch_claim_count(const uint32_t* bits, const int64_t* edge_off, const int32_t* edge_n, int n_views, unsigned long long* out, cudaStream_t st) {
+    cudaMemsetAsync(out, 0, size_t(n_views) * 8, st);
+    dim3 grid(8, n_views);
+    k_claim_count<<<grid, 256, 0, st>>>(bits, edge_off, edge_n, out);
+}
+__global__ void k_claim_expand(const uint32_t* __restrict__ bits, int64_t off, int n, uint8_t* __restrict__ out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) { const int64_t e = off + i; out[i] = (bits[e >> 5] >> (e & 31)) & 1u; }
+}
+void launch_claim_expand(const uint32_t* bits, int64_t off, int n, uint8_t* out, cudaStream_t st) {
+    if (n > 0) k_claim_expand<<<(n + 255) / 256, 256, 0, st>>>(bits, off, n, out);
+}
+
 }  // namespace cvx

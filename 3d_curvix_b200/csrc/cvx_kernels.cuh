@@ -121,4 +121,16 @@ void launch_finalize(const PassConst& pc, const double* x1, const double* y1, co
                      const double* th2, const int32_t* p_h1, const int32_t* p_h2rep, int64_t P, double* gamma_cam, double* gamma_world,
                      double* tangent_world, double* h2c, int32_t* nan_flag, cudaStream_t st);
 
+// claimed-edge bookkeeping (Calculate_Edge_Support_Ratios_And_Select_Next_Views, EdgeSketch_Core.cpp:785-797): one bit per edge
+// of every view in the arena (view v starts at word edge_off[v] / 32; slots are 32-edge aligned)
+struct ClaimArgs {
+    const int32_t *p_h1, *p_h2rep, *p_sup, *nan_flag; int64_t P;
+    const int64_t* row_off; const int32_t *rawat, *label;   // hypothesis table (cluster lookup through the reference's key quirk)
+    const int32_t* vali_view; const int64_t* edge_off; int n_vali, view1, view2, E2;
+    uint32_t* bits;
+};
+void launch_claim_pairs(const ClaimArgs& a, cudaStream_t st);
+void launch_claim_count(const uint32_t* bits, const int64_t* edge_off, const int32_t* edge_n, int n_views, unsigned long long* out, cudaStream_t st);
+void launch_claim_expand(const uint32_t* bits, int64_t off, int n, uint8_t* out, cudaStream_t st);
+
 }  // namespace cvx

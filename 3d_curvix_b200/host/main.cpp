@@ -1,0 +1,121 @@
+// main.cpp -- `curvix_main -c <settings.yaml>`: the reference's command line and pass loop (cmd/main.cpp:36-174) over the
+// drop-in EdgeSketch_Core.  Extra, optional flags (none changes results):
+//   --outputs DIR       where 3D_edges_*.txt / 3D_tangents_*.txt go   (default ../../outputs, definitions.h:4)
+//   --dataset-path DIR  overrides the settings file's Dataset_Path
+//   --device N          CUDA device ordinal
+//   --edge-cache DIR    binary cache of the parsed edge files
+//   --max-passes N      overrides Max_Num_Of_3D_Edge_Sketch_Passes
+//   --schedule FILE     one line per pass: what was run (views, hypotheses, validations, pairs, claimed ratio, timings)
+//   --keep-outputs      do not `rm -f` the 3D_edges_* / 3D_tangents_* files of the outputs folder first
+// The curve grouping that follows the sketch in the reference (EdgeMapping::consolidate_3D_edges -> final_curves.txt) is host
+// code of the reference and not part of this path; --support-links FILE dumps its input (3-D edge -> supporting 2-D edges).
+#include <sys/stat.h>
+
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <iostream>
+#include <memory>
+#include <string>
+
+#include "EdgeSketch_Core.hpp"
+
+static void usage() {
+    std::cout << "Usage: ./curvix_main [flag] [argument]\n\noptions:\n  -h, --help         show this help message and exit\n"
+                 "  -c, --config_file  path to the 3D Curvix setting file\n";   // definitions.h:69-72
+}
+
+int main(int argc, char** argv) {
+    std::string config, schedule_path, links_path;
+    curvix_host::HostOptions opt;
+    std::string dataset_override;
+    int max_passes = -1;
+    bool keep_outputs = false;
+    for (int i = 1; i < argc; i++) {
+        const std::string a = argv[i];
+        auto next = [&]() -> std::string { if (i + 1 >= argc) { usage(); std::exit(0); } return argv[++i]; };
+        if (a == "-h" || a == "--help") { usage(); return 0; }
+        else if (a == "-c" || a == "--config_file") config = next();
+        else if (a == "--outputs") opt.outputs_dir = next();
+        else if (a == "--dataset-path") dataset_override = next();
+        else if (a == "--device") opt.device = std::atoi(next().c_str());
+        else if (a == "--edge-cache") opt.edge_cache_dir = next();
+        else if (a == "--max-passes") max_passes = std::atoi(next().c_str());
+        else if (a == "--schedule") schedule_path = next();
+        else if (a == "--support-links") links_path = next();
+        else if (a == "--keep-outputs") keep_outputs = true;
+        else if (a == "--refined") opt.use_refined_poses = std::atoi(next().c_str());
+        else if (a == "--quiet") opt.quiet = true;
+        else { std::cerr << "ERROR: Invalid input arguments. See the following usage:" << std::endl; usage(); return 0; }
+    }
+    if (config.empty()) { std::cerr << "ERROR: No setting file is given!" << std::endl; usage(); return 0; }
+
+    // outputs folder (cmd/main.cpp:78-98)
+    struct stat st;
+    if (stat(opt.outputs_dir.c_str(), &st) != 0) {
+        const std::string cmd = "mkdir -p '" + opt.outputs_dir + "'";
+        if (std::system(cmd.c_str()) != 0) { std::cerr << "ERROR: Failed to create the outputs folder " << opt.outputs_dir << std::endl; return 0; }
+    }
+    if (!keep_outputs) {
+        const std::string cmd = "rm -f '" + opt.outputs_dir + "'/3D_edges_*.txt '" + opt.outputs_dir + "'/3D_tangents_*.txt";
+        if (std::system(cmd.c_str()) != 0) std::cerr << "ERROR: cannot remove old files under " << opt.outputs_dir << std::endl;
+    }
+
+    curvix_host::FlatYaml settings;
+    try {
+        settings = curvix_host::FlatYaml::load(config);
+        if (!dataset_override.empty()) settings.set("Dataset_Path", dataset_override);
+    } catch (const std::exception& e) {
+        std::cerr << "Exception: " << e.what() << std::endl;
+        return 0;
+    }
+
+    std::unique_ptr<EdgeSketch_Core> core;
+    try {
+        core.reset(new EdgeSketch_Core(settings, opt));
+    } catch (const std::exception& e) {
+        std::cerr << "Exception: " << e.what() << std::endl;
+        return 0;
+    }
+    EdgeSketch_Core& MWV_Edge_Rec = *core;
+    if (max_passes >= 0) MWV_Edge_Rec.Max_3D_Edge_Sketch_Passes = max_passes;
+    MWV_Edge_Rec.Read_Camera_Data();
+    std::shared_ptr<EdgeMapping> edgeMapping = std::make_shared<EdgeMapping>();
+    FILE* sched = schedule_path.empty() ? nullptr : std::fopen(schedule_path.c_str(), "w");
+
+    int edge_sketch_pass_count = 0;
+    while (edge_sketch_pass_count < MWV_Edge_Rec.Max_3D_Edge_Sketch_Passes) {   // cmd/main.cpp:123-155
+        const int v1 = MWV_Edge_Rec.hyp01_view_indx, v2 = MWV_Edge_Rec.hyp02_view_indx;
+        if (!opt.quiet) std::cout << "Selected views for hypotheses are " << v1 << " and " << v2 << std::endl;
+        MWV_Edge_Rec.Set_Hypothesis_Views_Camera();
+        MWV_Edge_Rec.Read_Edgels_Data();
+        MWV_Edge_Rec.Set_Hypothesis_Views_Edgels();
+        MWV_Edge_Rec.Run_3D_Edge_Sketch();
+        MWV_Edge_Rec.Finalize_Edge_Pairs_and_Reconstruct_3D_Edges(edgeMapping);
+        MWV_Edge_Rec.Stack_3D_Edges();
+        MWV_Edge_Rec.Calculate_Edge_Support_Ratios_And_Select_Next_Views(edgeMapping);
+        if (sched) {
+            const cvx_counts& c = MWV_Edge_Rec.last_counts;
+            std::fprintf(sched, "%d %d %d %lld %lld %lld %lld %.17g %.6f %.6f %.6f\n", edge_sketch_pass_count, v1, v2, (long long)c.n_hypotheses,
+                         (long long)c.n_validations, (long long)c.n_pairs, (long long)MWV_Edge_Rec.Gamma1s.rows, MWV_Edge_Rec.avg_ratio,
+                         MWV_Edge_Rec.pair_edges_time, MWV_Edge_Rec.finalize_edge_pair_time, MWV_Edge_Rec.find_next_hypothesis_view_time);
+            std::fflush(sched);
+        }
+        MWV_Edge_Rec.Clear_Data();
+        edge_sketch_pass_count++;
+        if (MWV_Edge_Rec.enable_aborting_3D_edge_sketch) break;
+    }
+    if (sched) std::fclose(sched);
+    if (!links_path.empty()) edgeMapping->write_support_links(links_path);
+
+    const double total_time = MWV_Edge_Rec.pair_edges_time + MWV_Edge_Rec.finalize_edge_pair_time + MWV_Edge_Rec.find_next_hypothesis_view_time;
+    std::cout << "Total computation time: " << total_time << " (s)" << std::endl;   // cmd/main.cpp:165-170
+    std::cout << "     - Time for Pairing up Edges:              " << MWV_Edge_Rec.pair_edges_time << " (s)" << std::endl;
+    std::cout << "     - Time for Finalizing Edge Pairs:         " << MWV_Edge_Rec.finalize_edge_pair_time << " (s)" << std::endl;
+    std::cout << "     - Time for Finding Next Hypothesis Views: " << MWV_Edge_Rec.find_next_hypothesis_view_time << " (s)" << std::endl;
+    std::cout << "     - (untimed in the reference) edge file reading + upload: " << MWV_Edge_Rec.read_edges_time << " (s)" << std::endl;
+    std::cout << "     - passes: " << edge_sketch_pass_count << ", 3D edges: " << MWV_Edge_Rec.all_3D_Edges.rows << ", 3D-2D links: "
+              << edgeMapping->num_support_links() << std::endl;
+    std::cout << "3D Curvix is Finished!" << std::endl;
+    return 0;
+}

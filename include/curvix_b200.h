@@ -154,6 +154,19 @@ typedef struct cvx_device_results {
 } cvx_device_results;
 int cvx_get_device_results(cvx_ctx* ctx, cvx_device_results* out);
 
+/* ---- claimed edges: replaces the bookkeeping half of Calculate_Edge_Support_Ratios_And_Select_Next_Views
+ * (EdgeSketch_Core.cpp:776-813).  The reference re-reads all edge files and walks EdgeMapping::edge_3D_to_supporting_edges
+ * into one std::set<int> per view; here the context keeps one bit per resident edge.  cvx_claims_accumulate marks, for every
+ * accepted pair of the last run that reaches the EdgeMapping insertions (EdgeSketch_Core.cpp:682-726): the view-1 edge, the
+ * view-2 representative, its cluster members (hypo2_clusters lookup, hpp:193-202) and the supporting edge of every
+ * validation view.  Bits persist across passes until cvx_claims_reset or a new cvx_set_view_edges of that view. */
+int cvx_claims_reset(cvx_ctx* ctx);
+int cvx_claims_accumulate(cvx_ctx* ctx);
+/* claimed[v] = number of claimed edges of view v, total[v] = edges of view v (n_views entries each; either may be NULL) */
+int cvx_claims_get_counts(cvx_ctx* ctx, int64_t* claimed, int64_t* total);
+/* out[i] = 1 when edge i of `view` is claimed (edge count of the view entries) */
+int cvx_claims_get_mask(cvx_ctx* ctx, int view, uint8_t* out);
+
 /* Timing of the last phases on the context stream (CUDA events, milliseconds). */
 typedef struct cvx_timings {
     float set_pair_ms; float run_ms; float finalize_ms;

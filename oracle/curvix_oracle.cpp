@@ -975,6 +975,67 @@ int orc_get_pair_cluster(orc_ctx* o, int p, int32_t* members, int cap) {  // Edg
     return n;
 }
 
+// EdgeSketch_Core.cpp:682-726 (which (image, edge) records a pass inserts) + :785-797 (one set per view)
+int orc_accumulate_claims(orc_ctx* o, uint8_t** masks) {
+    const ViewEdges& E1 = o->views[o->h1]; const ViewEdges& E2 = o->views[o->h2];
+    const size_t P = o->p_h1.size();
+    const int N = o->cfg.n_views, V = N - 2;
+    int n_inserting = 0;
+    for (size_t p = 0; p < P; p++) {
+        const int a = o->p_h1[p], b = o->p_h2rep[p];
+        double coeffs[3];
+        epip_line_coeffs(o->F21, E1.x[a], E1.y[a], coeffs);
+        double cx = kNaN, cy = kNaN;
+        if (!correct_one(coeffs, E2.x[b], E2.y[b], E2.th[b], o->cfg, &cx, &cy, nullptr)) continue;   // :639-642
+        const V3 G = triangulate2(E1.x[a], E1.y[a], cx, cy, o->g21.R21, o->g21.T21, o->K1inv);
+        if (std::isnan(G.v[0]) || std::isnan(G.v[1]) || std::isnan(G.v[2])) continue;                 // :658-663
+        n_inserting++;
+        masks[o->h1][a] |= 1; masks[o->h2][b] |= 1;                                                   // :680-681
+        auto it = o->hypo2_clusters.find((int64_t(a) << 32) | uint32_t(b));                           // hpp:193-202
+        if (it != o->hypo2_clusters.end())
+            for (int m : it->second)
+                if (m >= 0 && m < int(E2.x.size()) && m != b) masks[o->h2][m] |= 1;                    // :684-692
+        int col = 0;
+        for (int v = 0; v < N; v++) {                                                                 // :698-724
+            if (v == o->h1 || v == o->h2) continue;
+            const int s = o->support[size_t(o->p_row[p]) * size_t(V) + size_t(col)];
+            if (s != -2) masks[v][s] |= 1;
+            col++;
+        }
+    }
+    return n_inserting;
+}
+
+// EdgeSketch_Core.cpp:799-868
+int orc_select_next_views(int n_views, const int64_t* claimed, const int64_t* total, const int32_t* history, int n_history,
+                          double stop_ratio, int32_t* best1, int32_t* best2, double* avg_ratio) {
+    std::vector<double> ratios;
+    std::vector<std::pair<int, double>> frames;
+    for (int i = 0; i < n_views; i++) {
+        const double ratio = static_cast<double>(claimed[i]) / total[i];   // :806
+        ratios.push_back(ratio);
+        frames.push_back({i, ratio});
+    }
+    double sum = 0.0;
+    for (double r : ratios) sum += r;                                      // std::accumulate(.., 0.0), :813
+    const double avg = sum / ratios.size();
+    std::sort(frames.begin(), frames.end(), [](const std::pair<int, double>& x, const std::pair<int, double>& y) { return x.second < y.second; });
+    auto seen = [&](int v) { int c = 0; for (int k = 0; k < n_history; k++) c += (history[k] == v); return c; };
+    auto pick = [&](size_t k, int keep) { return k < frames.size() ? frames[k].first : keep; };   // the reference indexes past the end (UB): keep
+    int b1 = frames[0].first, b2 = frames[1].first, counter = 0;
+    while (true) {                                                         // :828-854
+        const int f1 = seen(b1), f2 = seen(b2);
+        if (f1 == 0 && f2 == 0) break;
+        if (f1 > 0 && f2 > 0) { b1 = pick(2 + counter, b1); b2 = pick(3 + counter, b2); }
+        else if (f1 > 0) { b1 = pick(1 + counter, b1); b2 = pick(2 + counter, b2); }
+        else if (f2 > 0) { b2 = pick(2 + counter, b2); }
+        counter++;
+        if (size_t(counter) > frames.size() - 2) break;
+    }
+    *best1 = b1; *best2 = b2; *avg_ratio = avg;
+    return avg > stop_ratio ? 1 : 0;                                       // :862
+}
+
 void orc_pair_geometry(const double* R1, const double* T1, const double* R2, const double* T2, const double* K1,
                        const double* K2, double* R21, double* T21, double* F, double* e1pix, double* e2pix) {
     M3 r1, r2, k1, k2; V3 t1, t2;

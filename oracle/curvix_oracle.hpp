@@ -94,6 +94,16 @@ int   orc_finalize(orc_ctx* o, double* gamma_cam /*P x 3*/, double* gamma_world,
 // cluster members of accepted pair p as looked up through hypo2_clusters (EdgeSketch_Core.hpp:193-202)
 int   orc_get_pair_cluster(orc_ctx* o, int p, int32_t* members, int cap);
 
+// Claimed edges of the accepted pairs of the last run, as Finalize inserts them into EdgeMapping (EdgeSketch_Core.cpp:682-726)
+// and Calculate_Edge_Support_Ratios_And_Select_Next_Views collects them per view (:785-797).  masks[v] points at n_edges(v)
+// bytes that are OR-ed with 1 for every claimed edge (accumulate over passes by reusing the buffers).  Needs orc_finalize
+// semantics internally (pairs whose representative is dropped or NaN insert nothing).
+int   orc_accumulate_claims(orc_ctx* o, uint8_t** masks /*n_views pointers*/);
+// Next hypothesis views from the claimed ratios (EdgeSketch_Core.cpp:799-868): literal std::sort by ratio + history filter.
+// Returns 1 when avg_ratio > stop_ratio (enable_aborting_3D_edge_sketch).
+int   orc_select_next_views(int n_views, const int64_t* claimed, const int64_t* total, const int32_t* history, int n_history,
+                            double stop_ratio, int32_t* best1, int32_t* best2, double* avg_ratio);
+
 // stand-alone functions for unit tests / KATs
 void  orc_pair_geometry(const double* R1, const double* T1, const double* R2, const double* T2, const double* K1,
                         const double* K2, double* R21, double* T21, double* F, double* e1pix, double* e2pix);

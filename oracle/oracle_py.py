@@ -192,10 +192,27 @@ class Oracle:
         self.lib.orc_finalize(self.h, _d(gc), _d(gw), _d(tw), _d(h2c), _i(nf))
         return dict(gamma_cam=gc, gamma_world=gw, tangent_world=tw, h2_corrected=h2c, nan_flag=nf)
 
+    def accumulate_claims(self, masks):
+        """masks: list of n_views uint8 arrays (edge count of each view); OR-ed in place.  Returns #pairs that inserted."""
+        arr = (C.c_void_p * len(masks))(*[m.ctypes.data for m in masks])
+        return self.lib.orc_accumulate_claims(self.h, arr)
+
     def pair_cluster(self, p, cap=4096):
         buf = np.empty(cap, np.int32)
         n = self.lib.orc_get_pair_cluster(self.h, p, _i(buf), cap)
         return buf[:min(n, cap)].copy()
+
+
+def select_next_views(claimed, total, history, stop_ratio, fast=False):
+    """EdgeSketch_Core.cpp:799-868 -> (best1, best2, avg_ratio, abort)."""
+    lib = load(fast)
+    claimed = np.ascontiguousarray(claimed, np.int64); total = np.ascontiguousarray(total, np.int64)
+    hist = np.ascontiguousarray(history, np.int32)
+    b1, b2, avg = C.c_int32(), C.c_int32(), C.c_double()
+    lib.orc_select_next_views.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_double, C.c_void_p, C.c_void_p, C.c_void_p]
+    ab = lib.orc_select_next_views(len(claimed), claimed.ctypes.data, total.ctypes.data, hist.ctypes.data, len(hist), float(stop_ratio),
+                                   C.addressof(b1), C.addressof(b2), C.addressof(avg))
+    return b1.value, b2.value, avg.value, bool(ab)
 
 
 def support_test(group_off, view_off, ang31, ang32, cs, sn, wedge31, wedge32, tgt, thr, parallel_deg, threads=0, fast=False):
