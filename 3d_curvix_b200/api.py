@@ -36,7 +36,8 @@ class CvxConfig(C.Structure):
 class CvxCounts(C.Structure):
     _fields_ = [(n, C.c_int64) for n in (
         "n_h1_total", "n_h1_processed", "n_candidates", "n_hypotheses", "n_validations", "n_valid_rows",
-        "n_pairs", "n_degenerate_wedges", "n_supported", "n_parallel", "n_inliers", "n_unique_hypotheses")]
+        "n_pairs", "n_degenerate_wedges", "n_supported", "n_parallel", "n_inliers", "n_unique_hypotheses",
+        "n_entries_visited", "n_heavy_queries")]
 
     def as_dict(self):
         return {n: int(getattr(self, n)) for n, _ in self._fields_}

@@ -114,8 +114,9 @@ struct cvx_ctx {
     PassConst pc;
     std::vector<int32_t> vali_views;
     DevBuf<ViewConst> d_vc;
-    DevBuf<int32_t> d_vali, d_bins1, d_bins2;
-    BinGrid bg = {};
+    DevBuf<int32_t> d_vali, d_cell_end, d_cell_end_b, d_scan_tmp;
+    DevBuf<ViewGrid> d_vg;
+    DevBuf<unsigned long long> d_minmax;
     DevBuf<double> d_ang2;
     DevBuf<double2> d_wedge_h1;
     DevBuf<int32_t> d_wflag_h1;
@@ -154,10 +155,13 @@ struct cvx_support_problem {
     int G, V;
     int64_t H, n_edges;
     DevBuf<int64_t> view_off;
-    DevBuf<int32_t> bins1, bins2, support, bin1, bin2, idx1, idx2, row_group;
+    DevBuf<int32_t> cell_end, cell_end_b, scan_tmp, support, cell, idx, idx_b, row_group;
+    DevBuf<double4> rec, rec_b;
+    DevBuf<ViewGrid> vg;
+    DevBuf<unsigned long long> minmax;
+    GridIndex gi;
     DevBuf<double> a31, a32, cs, sn;
-    DevBuf<double2> ang1, tan1, ang2, tan2, w31, w32, tgt;
-    BinGrid bg;
+    DevBuf<double2> w31, w32, tgt;
     double thr, par;
     cudaEvent_t e0, e1;
 };
@@ -196,11 +200,12 @@ cudaError_t regrow(T*& p, size_t keep, size_t cap, cudaStream_t st) {   // new a
     return e;
 }
 void free_arena(EdgeArena& ea) {
-    void* ps[] = {ea.x, ea.y, ea.th, ea.cs, ea.sn, ea.ang, ea.bin1, ea.bin2, ea.ix1.ang, ea.ix1.tan, ea.ix1.idx, ea.ix2.ang, ea.ix2.tan, ea.ix2.idx};
+    void* ps[] = {ea.x, ea.y, ea.th, ea.cs, ea.sn, ea.ang, ea.cell, ea.gi.A.rec, ea.gi.A.idx, ea.gi.B.rec, ea.gi.B.idx};
     for (void* p : ps) if (p) cudaFree(p);
-    int32_t *b1 = ea.ix1.bins, *b2 = ea.ix2.bins;   // owned by DevBufs
+    const GridIndex keep = ea.gi;   // cell_end / vg / minmax are owned by DevBufs
     ea = EdgeArena{};
-    ea.ix1.bins = b1; ea.ix2.bins = b2;
+    ea.gi.A.cell_end = keep.A.cell_end; ea.gi.B.cell_end = keep.B.cell_end; ea.gi.vg = keep.vg; ea.gi.minmax = keep.minmax;
+    ea.gi.CS = keep.CS;
 }
 int grow_arena(cvx_ctx* ctx, size_t need) {
     if (need <= ctx->arena_cap) return CVX_OK;
@@ -211,9 +216,8 @@ int grow_arena(cvx_ctx* ctx, size_t need) {
     cudaStream_t st = ctx->stream;
     CU(regrow(ea.x, used, cap, st)); CU(regrow(ea.y, used, cap, st)); CU(regrow(ea.th, used, cap, st));
     CU(regrow(ea.cs, used, cap, st)); CU(regrow(ea.sn, used, cap, st));
-    CU(regrow(ea.ang, 0, cap, st)); CU(regrow(ea.bin1, 0, cap, st)); CU(regrow(ea.bin2, 0, cap, st));
-    CU(regrow(ea.ix1.ang, 0, cap, st)); CU(regrow(ea.ix1.tan, 0, cap, st)); CU(regrow(ea.ix1.idx, 0, cap, st));
-    CU(regrow(ea.ix2.ang, 0, cap, st)); CU(regrow(ea.ix2.tan, 0, cap, st)); CU(regrow(ea.ix2.idx, 0, cap, st));
+    CU(regrow(ea.ang, 0, cap, st)); CU(regrow(ea.cell, 0, cap, st));
+    CU(regrow(ea.gi.A.rec, 0, cap, st)); CU(regrow(ea.gi.A.idx, 0, cap, st)); CU(regrow(ea.gi.B.rec, 0, cap, st)); CU(regrow(ea.gi.B.idx, 0, cap, st));
     if (ctx->d_claim) {   // the claim bitmap covers the arena: grow it with the arena, new words cleared
         const size_t words = cap / 32;
         uint32_t* q = nullptr;
@@ -241,13 +245,6 @@ int sync_tables(cvx_ctx* ctx) {
 
 const M3& K_of(const cvx_ctx* c, int v) { return c->multi_K ? c->K[v] : c->K[0]; }
 
-int pick_bins(int max_edges) {
-    // B uniform angular bins over [0,180]: fine enough that a bin holds O(1) edges even when the whole view
-    // lies inside a few degrees of epipolar angle
-    int B = 1 << 16;
-    while (B < 4 * max_edges && B < (1 << 20)) B <<= 1;
-    return B;
-}
 
 }  // namespace
 
@@ -288,7 +285,7 @@ int cvx_destroy(cvx_ctx* ctx) {
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
     free_arena(ctx->ea);
-    DevBuf<int32_t>* ib[] = {&ctx->d_edge_n, &ctx->d_vali, &ctx->d_bins1, &ctx->d_bins2, &ctx->d_wflag_h1, &ctx->d_m, &ctx->d_n, &ctx->d_ncl,
+    DevBuf<int32_t>* ib[] = {&ctx->d_edge_n, &ctx->d_vali, &ctx->d_cell_end, &ctx->d_cell_end_b, &ctx->d_scan_tmp, &ctx->d_wflag_h1, &ctx->d_m, &ctx->d_n, &ctx->d_ncl,
                              &ctx->d_nvalid, &ctx->d_nsel, &ctx->r_h1, &ctx->r_h2orig, &ctx->r_local, &ctx->r_rawat, &ctx->r_label, &ctx->r_h2rep,
                              &ctx->r_count, &ctx->r_flags, &ctx->r_urank, &ctx->r_row_u, &ctx->u_h1, &ctx->u_row, &ctx->u_mult, &ctx->u_count,
                              &ctx->d_support, &ctx->d_support_t, &ctx->v_h1, &ctx->v_row, &ctx->v_count, &ctx->v_sel, &ctx->p_h1, &ctx->p_h2rep,
@@ -301,7 +298,7 @@ int cvx_destroy(cvx_ctx* ctx) {
     for (auto* b : db) b->release();
     DevBuf<double2>* d2[] = {&ctx->d_wedge_h1, &ctx->u_xy, &ctx->d_w31, &ctx->d_w32, &ctx->d_tgt};
     for (auto* b : d2) b->release();
-    ctx->u_geom.release(); ctx->d_vc.release(); ctx->d_ctr.release();
+    ctx->u_geom.release(); ctx->d_vc.release(); ctx->d_ctr.release(); ctx->d_vg.release(); ctx->d_minmax.release();
     if (ctx->d_claim) cudaFree(ctx->d_claim);
     ctx->d_claim_cnt.release(); ctx->d_claim_mask.release();
     for (auto& e : ctx->ev) cudaEventDestroy(e);
@@ -402,10 +399,19 @@ int cvx_set_hypothesis_pair(cvx_ctx* ctx, int h1, int h2) {
     CU(cudaMemcpyAsync(ctx->d_vc.p, vc.data(), V * sizeof(ViewConst), cudaMemcpyHostToDevice, ctx->stream));
     CU(cudaMemcpyAsync(ctx->d_vali.p, ctx->vali_views.data(), V * sizeof(int32_t), cudaMemcpyHostToDevice, ctx->stream));
     // ---- stage every validation view into its bin grid (hoisted getOreListVali + cos/sin, EdgeSketch_Core.cpp:315-342)
-    ctx->bg.B = pick_bins(max_edges); ctx->bg.BS = ctx->bg.B + 1; ctx->bg.scale = ctx->bg.B / 180.0;
-    CU(ctx->d_bins1.reserve(size_t(std::max(V, 1)) * ctx->bg.BS)); CU(ctx->d_bins2.reserve(size_t(std::max(V, 1)) * ctx->bg.BS));
-    ctx->ea.ix1.bins = ctx->d_bins1.p; ctx->ea.ix2.bins = ctx->d_bins2.p;
-    launch_stage_views(ctx->ea, ctx->d_edge_off.p, ctx->d_edge_n.p, ctx->d_vali.p, V, max_edges, ctx->d_vc.p, ctx->bg, ctx->stream,
+    GridIndex& gi = ctx->ea.gi;
+    gi.CS = pick_cell_stride(max_edges);
+    CU(ctx->d_scan_tmp.reserve(size_t(2 * std::max(V, 1)) * size_t(scan_tiles(gi.CS))));
+    CU(ctx->d_cell_end.reserve(size_t(std::max(V, 1)) * size_t(gi.CS))); CU(ctx->d_cell_end_b.reserve(size_t(std::max(V, 1)) * size_t(gi.CS)));
+    CU(ctx->d_vg.reserve(std::max(V, 1)));
+    CU(ctx->d_minmax.reserve(size_t(std::max(V, 1)) * 4));
+    gi.A.cell_end = ctx->d_cell_end.p; gi.B.cell_end = ctx->d_cell_end_b.p; gi.vg = ctx->d_vg.p; gi.minmax = ctx->d_minmax.p;
+    GridSample gs;
+    std::memset(&gs, 0, sizeof(gs));
+    gs.x1 = ctx->ea.x + ctx->edge_off[h1]; gs.y1 = ctx->ea.y + ctx->edge_off[h1]; gs.E1 = ctx->edge_n[h1];
+    gs.x2 = ctx->ea.x + ctx->edge_off[h2]; gs.y2 = ctx->ea.y + ctx->edge_off[h2]; gs.E2 = ctx->edge_n[h2];
+    gs.delta = pc.delta; gs.rows = pc.rows; gs.cols = pc.cols;
+    launch_stage_views(ctx->ea, ctx->d_edge_off.p, ctx->d_edge_n.p, ctx->d_vali.p, V, max_edges, ctx->d_vc.p, gs, ctx->d_scan_tmp.p, ctx->stream,
                        &ctx->tm.kernel_launches);
     // ---- Set_Hypothesis_Views_Edgels, EdgeSketch_Core.cpp:145-166
     const int E1 = ctx->edge_n[h1], E2 = ctx->edge_n[h2];
@@ -489,7 +495,7 @@ int cvx_run_edge_sketch(cvx_ctx* ctx, int h1_begin, int h1_end) {
     ValidateArgs a;
     std::memset(&a, 0, sizeof(a));
     a.ut = ut; a.U = U; a.x1 = x1; a.y1 = y1; a.w31 = ctx->d_w31.p; a.w31_stride = E1; a.vc = ctx->d_vc.p;
-    a.vali_view = ctx->d_vali.p; a.edge_off = ctx->d_edge_off.p; a.bg = ctx->bg; a.ix1 = ctx->ea.ix1; a.ix2 = ctx->ea.ix2;
+    a.vali_view = ctx->d_vali.p; a.edge_off = ctx->d_edge_off.p; a.gi = ctx->ea.gi;
     a.cos_thresh = pc.cos_thresh; a.parallel_deg = pc.parallel_deg; a.delta = pc.delta; a.rows = pc.rows; a.cols = pc.cols; a.n_vali = V;
     a.support = ctx->d_support.p; a.sup_stride = int64_t(Ua); a.ctr = ctx->d_ctr.p;
     if (ctx->keep_inter) { a.w32_out = ctx->d_w32.p; a.tgt_out = ctx->d_tgt.p; }
@@ -505,7 +511,7 @@ int cvx_run_edge_sketch(cvx_ctx* ctx, int h1_begin, int h1_end) {
     int64_t tot[2] = {0, 0};
     CU(cudaMemcpyAsync(&tot[0], ctx->d_valid_off.p + E1, 8, cudaMemcpyDeviceToHost, st));
     CU(cudaMemcpyAsync(&tot[1], ctx->d_pair_off.p + E1, 8, cudaMemcpyDeviceToHost, st));
-    static_assert(sizeof(DevCounters) == 4 * CVX_CTR_SLOTS * 8, "DevCounters layout");
+    static_assert(sizeof(DevCounters) == 6 * CVX_CTR_SLOTS * 8, "DevCounters layout");
     DevCounters hc;
     CU(cudaMemcpyAsync(&hc, ctx->d_ctr.p, sizeof(hc), cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
@@ -534,6 +540,7 @@ int cvx_run_edge_sketch(cvx_ctx* ctx, int h1_begin, int h1_end) {
     for (int k = 0; k < CVX_CTR_SLOTS; k++) {
         c.n_degenerate_wedges += int64_t(hc.n_degenerate[k]); c.n_supported += int64_t(hc.n_supported[k]);
         c.n_parallel += int64_t(hc.n_parallel[k]); c.n_inliers += int64_t(hc.n_inliers[k]);
+        c.n_entries_visited += int64_t(hc.n_visited[k]); c.n_heavy_queries += int64_t(hc.n_heavy[k]);
     }
     for (int i = h1_begin; i < h1_end; i++) if (ctx->h_row_off[i + 1] > ctx->h_row_off[i]) c.n_h1_processed++;
     c.n_candidates = -1;   // filled lazily by cvx_get_counts (needs m[])
@@ -820,12 +827,15 @@ int cvx_support_problem_create(cvx_ctx* ctx, int G, const int64_t* group_off, in
     const size_t NE = size_t(std::max<int64_t>(p->n_edges, 1)), H = size_t(std::max<int64_t>(p->H, 1));
     int64_t max_edges = 1;
     for (int v = 0; v < V; v++) max_edges = std::max(max_edges, view_off[v + 1] - view_off[v]);
-    p->bg.B = pick_bins(int(max_edges)); p->bg.BS = p->bg.B + 1; p->bg.scale = p->bg.B / 180.0;
-    CU(p->view_off.reserve(V + 1)); CU(p->bins1.reserve(size_t(V) * p->bg.BS)); CU(p->bins2.reserve(size_t(V) * p->bg.BS));
-    CU(p->support.reserve(size_t(V) * H)); CU(p->bin1.reserve(NE)); CU(p->bin2.reserve(NE)); CU(p->idx1.reserve(NE)); CU(p->idx2.reserve(NE));
+    p->gi.CS = pick_cell_stride(max_edges);
+    CU(p->scan_tmp.reserve(size_t(2 * V) * size_t(scan_tiles(p->gi.CS))));
+    CU(p->view_off.reserve(V + 1)); CU(p->cell_end.reserve(size_t(V) * size_t(p->gi.CS))); CU(p->cell_end_b.reserve(size_t(V) * size_t(p->gi.CS))); CU(p->vg.reserve(V)); CU(p->minmax.reserve(size_t(V) * 4));
+    CU(p->support.reserve(size_t(V) * H)); CU(p->cell.reserve(NE)); CU(p->idx.reserve(NE)); CU(p->idx_b.reserve(NE));
     CU(p->row_group.reserve(H));
     CU(p->a31.reserve(NE)); CU(p->a32.reserve(NE)); CU(p->cs.reserve(NE)); CU(p->sn.reserve(NE));
-    CU(p->ang1.reserve(NE)); CU(p->tan1.reserve(NE)); CU(p->ang2.reserve(NE)); CU(p->tan2.reserve(NE));
+    CU(p->rec.reserve(NE)); CU(p->rec_b.reserve(NE));
+    p->gi.A = GridLayout{p->rec.p, p->idx.p, p->cell_end.p}; p->gi.B = GridLayout{p->rec_b.p, p->idx_b.p, p->cell_end_b.p};
+    p->gi.vg = p->vg.p; p->gi.minmax = p->minmax.p;
     CU(p->w31.reserve(size_t(V) * G)); CU(p->w32.reserve(size_t(V) * H)); CU(p->tgt.reserve(size_t(V) * H));
     std::vector<int32_t> rg(H, 0);
     for (int g = 0; g < G; g++) for (int64_t r = group_off[g]; r < group_off[g + 1]; r++) rg[size_t(r)] = g;
@@ -838,9 +848,11 @@ int cvx_support_problem_create(cvx_ctx* ctx, int G, const int64_t* group_off, in
     CU(cudaMemcpyAsync(p->w31.p, wedge31, size_t(V) * G * 16, cudaMemcpyHostToDevice, st));
     CU(cudaMemcpyAsync(p->w32.p, wedge32, size_t(V) * p->H * 16, cudaMemcpyHostToDevice, st));
     CU(cudaMemcpyAsync(p->tgt.p, tgt, size_t(V) * p->H * 16, cudaMemcpyHostToDevice, st));
-    ViewIndex ix1 = {p->ang1.p, p->tan1.p, p->idx1.p, p->bins1.p}, ix2 = {p->ang2.p, p->tan2.p, p->idx2.p, p->bins2.p};
-    launch_stage_given(p->a31.p, p->a32.p, p->cs.p, p->sn.p, p->view_off.p, V, max_edges, p->bin1.p, p->bin2.p, p->bg, ix1, ix2, st);
-    ctx->tm.kernel_launches += 3;
+    GridSample gs;
+    std::memset(&gs, 0, sizeof(gs));
+    gs.w31 = p->w31.p; gs.n31 = G; gs.w32 = p->w32.p; gs.n32 = p->H;
+    launch_stage_given(p->a31.p, p->a32.p, p->cs.p, p->sn.p, p->view_off.p, V, max_edges, p->cell.p, p->gi, gs, p->scan_tmp.p, st,
+                       &ctx->tm.kernel_launches);
     cudaEventCreate(&p->e0); cudaEventCreate(&p->e1);
     CU(cudaStreamSynchronize(st));   // rg (host vector) must outlive the copy
     CU(cudaGetLastError());
@@ -855,8 +867,7 @@ int cvx_support_problem_run(cvx_support_problem* p, float* kernel_ms) {
     ValidateArgs a;
     std::memset(&a, 0, sizeof(a));
     a.ut.h1 = p->row_group.p; a.U = p->H; a.w31 = p->w31.p; a.w31_stride = p->G; a.w32_in = p->w32.p; a.tgt_in = p->tgt.p;
-    a.vali_view = nullptr; a.edge_off = p->view_off.p; a.bg = p->bg;
-    a.ix1 = ViewIndex{p->ang1.p, p->tan1.p, p->idx1.p, p->bins1.p}; a.ix2 = ViewIndex{p->ang2.p, p->tan2.p, p->idx2.p, p->bins2.p};
+    a.vali_view = nullptr; a.edge_off = p->view_off.p; a.gi = p->gi;
     a.cos_thresh = p->thr; a.parallel_deg = p->par; a.n_vali = p->V;
     a.support = p->support.p; a.sup_stride = std::max<int64_t>(p->H, 1); a.ctr = nullptr;
     cudaEventRecord(p->e0, ctx->stream);
@@ -880,9 +891,9 @@ int cvx_support_problem_result(cvx_support_problem* p, int32_t* support) {
 int cvx_support_problem_destroy(cvx_support_problem* p) {
     if (!p) return CVX_ERR_INVALID;
     cudaSetDevice(p->ctx->device);
-    p->view_off.release(); p->bins1.release(); p->bins2.release(); p->support.release(); p->bin1.release(); p->bin2.release();
-    p->idx1.release(); p->idx2.release(); p->row_group.release(); p->a31.release(); p->a32.release(); p->cs.release(); p->sn.release();
-    p->ang1.release(); p->tan1.release(); p->ang2.release(); p->tan2.release(); p->w31.release(); p->w32.release(); p->tgt.release();
+    p->view_off.release(); p->scan_tmp.release(); p->cell_end.release(); p->cell_end_b.release(); p->idx_b.release(); p->rec_b.release(); p->vg.release(); p->minmax.release(); p->support.release(); p->cell.release();
+    p->idx.release(); p->row_group.release(); p->a31.release(); p->a32.release(); p->cs.release(); p->sn.release();
+    p->rec.release(); p->w31.release(); p->w32.release(); p->tgt.release();
     cudaEventDestroy(p->e0); cudaEventDestroy(p->e1);
     delete p;
     return CVX_OK;

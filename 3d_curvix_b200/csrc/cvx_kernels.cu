@@ -20,6 +20,9 @@
 #include "cvx_kernels.cuh"
 
 #include <float.h>
+#include <stdlib.h>
+
+#include <algorithm>
 
 namespace cvx {
 
@@ -30,11 +33,16 @@ __device__ __forceinline__ unsigned lanemask_lt() {
     asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m));
     return m;
 }
-__device__ __forceinline__ int bin_of(double a, double scale, int B) {
-    if (a != a) return B;   // NaN bin, never queried
-    int b = int(a * scale);
-    return b < 0 ? 0 : (b >= B ? B - 1 : b);
+__device__ __forceinline__ int grid_bin(double a, double lo, double sc, int G) {   // monotone in a: a <= b => bin(a) <= bin(b)
+    const int b = int((a - lo) * sc);
+    return b < 0 ? 0 : (b >= G ? G - 1 : b);
 }
+__device__ __forceinline__ int grid_bins(double a1, double a2, const ViewGrid& g) {   // (b1 << 16) | b2, -1 for NaN
+    if (a1 != a1 || a2 != a2) return -1;
+    return (grid_bin(a1, g.lo1, g.s1, g.G1) << 16) | grid_bin(a2, g.lo2, g.s2, g.G2);
+}
+__device__ __forceinline__ int cell_A(int packed, const ViewGrid& g) { return packed < 0 ? g.G1 * g.G2 : (packed >> 16) * g.G2 + (packed & 0xffff); }
+__device__ __forceinline__ int cell_B(int packed, const ViewGrid& g) { return packed < 0 ? g.G1 * g.G2 : (packed & 0xffff) * g.G1 + (packed >> 16); }
 
 // ----------------------------------------------------------------------------- upload-time
 __global__ void k_edge_trig(const double* __restrict__ th, double* __restrict__ cs, double* __restrict__ sn, int64_t n) {
@@ -47,111 +55,327 @@ void launch_edge_trig(const double* th, double* cs, double* sn, int64_t n, cudaS
 }
 
 // ----------------------------------------------------------------------------- per-pass view staging
-// getOreListVali for both hypothesis views (EdgeSketch_Core.cpp:337,342), hoisted out of the H1 loop.
-__global__ void k_stage_angles(EdgeArena ea, const int64_t* __restrict__ edge_off, const int32_t* __restrict__ edge_n,
-                               const int32_t* __restrict__ vali_view, const ViewConst* __restrict__ vc, BinGrid bg) {
+#define GRID_MAX_BINS 16384
+#define GRID_CELLS_PER_WEDGE 2.0   // a wedge spans 3 (at most 4) rows of cells: what a lane keeps in registers (VAL_LIGHT_ROWS)
+int pick_cell_stride(int64_t max_edges) {
+    int64_t per_edge = 16;   // cell budget per edge of the largest view (tuning knob for experiments: CVX_GRID_CELLS_PER_EDGE)
+    if (const char* e = getenv("CVX_GRID_CELLS_PER_EDGE")) per_edge = std::max(1, atoi(e));
+    int64_t budget = std::max<int64_t>(per_edge * max_edges, 4096);
+    budget = std::min<int64_t>(budget, int64_t(1) << 26);
+    return int((budget + 1 + 3) & ~int64_t(3));
+}
+// order-preserving map double -> u64 (so that atomicMin / atomicMax on the keys order like the doubles)
+__device__ __forceinline__ unsigned long long ord_key(double d) {
+    const unsigned long long u = (unsigned long long)__double_as_longlong(d);
+    return (u >> 63) ? ~u : (u | 0x8000000000000000ULL);
+}
+__device__ __forceinline__ double ord_val(unsigned long long k) {
+    return __longlong_as_double((long long)((k >> 63) ? (k & 0x7fffffffffffffffULL) : ~k));
+}
+// warp-reduced min / max of the two angles into minmax[v][4]; NaNs are skipped by the callers
+__device__ __forceinline__ void minmax_commit(double mn1, double mx1, double mn2, double mx2, unsigned long long* mm) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        mn1 = fmin(mn1, __shfl_xor_sync(FULL, mn1, o)); mx1 = fmax(mx1, __shfl_xor_sync(FULL, mx1, o));
+        mn2 = fmin(mn2, __shfl_xor_sync(FULL, mn2, o)); mx2 = fmax(mx2, __shfl_xor_sync(FULL, mx2, o));
+    }
+    if ((threadIdx.x & 31) == 0 && mn1 <= mx1) {
+        atomicMin(&mm[0], ord_key(mn1)); atomicMax(&mm[1], ord_key(mx1));
+        atomicMin(&mm[2], ord_key(mn2)); atomicMax(&mm[3], ord_key(mx2));
+    }
+}
+__global__ void k_minmax_init(unsigned long long* mm, int n_vali) {
+    const int v = blockIdx.x * blockDim.x + threadIdx.x;
+    if (v < n_vali) { mm[4 * v] = mm[4 * v + 2] = 0xfff0000000000000ULL; mm[4 * v + 1] = mm[4 * v + 3] = 0x000fffffffffffffULL; }   // +inf / -inf
+}
+// getOreListVali for both hypothesis views (EdgeSketch_Core.cpp:337,342), hoisted out of the H1 loop, + per-view angle ranges
+__global__ void __launch_bounds__(256) k_stage_angles(EdgeArena ea, const int64_t* __restrict__ edge_off, const int32_t* __restrict__ edge_n,
+                                                      const int32_t* __restrict__ vali_view, const ViewConst* __restrict__ vc) {
     const int v = blockIdx.y;
     const int view = vali_view[v];
     const int n = edge_n[view];
     const int64_t off = edge_off[view];
     const double e31x = vc[v].e2_31[0], e31y = vc[v].e2_31[1], e32x = vc[v].e2_32[0], e32y = vc[v].e2_32[1];
+    double mn1 = DBL_MAX, mx1 = -DBL_MAX, mn2 = DBL_MAX, mx2 = -DBL_MAX;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         const double x = ea.x[off + i], y = ea.y[off + i];
         const double a31 = ore_angle(x, y, e31x, e31y);
         const double a32 = ore_angle(x, y, e32x, e32y);
-        const int b1 = bin_of(a31, bg.scale, bg.B), b2 = bin_of(a32, bg.scale, bg.B);
-        ea.ang[off + i] = make_double2(a31, a32); ea.bin1[off + i] = b1; ea.bin2[off + i] = b2;
-        atomicAdd(&ea.ix1.bins[int64_t(v) * bg.BS + b1], 1);
-        atomicAdd(&ea.ix2.bins[int64_t(v) * bg.BS + b2], 1);
+        ea.ang[off + i] = make_double2(a31, a32);
+        if (a31 == a31 && a32 == a32) { mn1 = fmin(mn1, a31); mx1 = fmax(mx1, a31); mn2 = fmin(mn2, a32); mx2 = fmax(mx2, a32); }
     }
+    minmax_commit(mn1, mx1, mn2, mx2, ea.gi.minmax + 4 * v);
 }
-// in-place exclusive scan of one bin histogram (one block per histogram; hists = [ix1 views..., ix2 views...])
-__global__ void __launch_bounds__(1024) k_scan_bins(int32_t* bins1, int32_t* bins2, int n_vali, int BS) {
-    __shared__ int part[1024];
-    int32_t* b = (blockIdx.x < n_vali ? bins1 + int64_t(blockIdx.x) * BS : bins2 + int64_t(blockIdx.x - n_vali) * BS);
-    const int per = (BS + 1023) / 1024;
-    const int lo = min(int(threadIdx.x) * per, BS), hi = min(lo + per, BS);
-    int s = 0;
-    for (int i = lo; i < hi; i++) s += b[i];
-    part[threadIdx.x] = s;
-    __syncthreads();
-    for (int d = 1; d < 1024; d <<= 1) {
-        int t = (threadIdx.x >= d) ? part[threadIdx.x - d] : 0;
-        __syncthreads();
-        part[threadIdx.x] += t;
-        __syncthreads();
+// Grid sizing, one warp per validation view.  The lanes sample wedges (64 of each kind): their typical (geometric mean)
+// width sets the cell size in that angle -- half a wedge -- within the per-view cell budget.  A wrong estimate only
+// costs time: membership is always decided by the exact tests on the stored angles.
+template <bool GIVEN>
+__global__ void __launch_bounds__(128) k_grid_params(GridIndex gi, int n_vali, const __grid_constant__ GridSample gs, const ViewConst* __restrict__ vc) {
+    const int v = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (v >= n_vali) return;
+    double sl1 = 0, sl2 = 0;
+    int n1 = 0, n2 = 0;
+    for (int k = lane; k < 64; k += 32) {
+        double wd1 = nan(""), wd2 = nan("");
+        if (GIVEN) {
+            if (gs.n31 > 0) { const double2 w = gs.w31[int64_t(v) * gs.n31 + (gs.n31 * k) / 64]; wd1 = w.y - w.x; }
+            if (gs.n32 > 0) { const double2 w = gs.w32[int64_t(v) * gs.n32 + (gs.n32 * k) / 64]; wd2 = w.y - w.x; }
+        } else {
+            const ViewConst& c = vc[v];
+            double lo, hi;
+            if (gs.E1 > 0) {
+                const int i = int((int64_t(gs.E1) * k) / 64);
+                wedge_row(gs.x1[i], gs.y1[i], c.F31, c.e1_31[0], c.e1_31[1], c.e2_31[0], c.e2_31[1], gs.delta, gs.rows, gs.cols, &lo, &hi);
+                wd1 = hi - lo;
+            }
+            if (gs.E2 > 0) {
+                const int i = int((int64_t(gs.E2) * k) / 64);
+                wedge_row(gs.x2[i], gs.y2[i], c.F32, c.e1_32[0], c.e1_32[1], c.e2_32[0], c.e2_32[1], gs.delta, gs.rows, gs.cols, &lo, &hi);
+                wd2 = hi - lo;
+            }
+        }
+        if (wd1 == wd1) { sl1 += log(fmax(wd1, 1e-6)); n1++; }
+        if (wd2 == wd2) { sl2 += log(fmax(wd2, 1e-6)); n2++; }
     }
-    int run = part[threadIdx.x] - s;
-    for (int i = lo; i < hi; i++) { int c = b[i]; b[i] = run; run += c; }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        sl1 += __shfl_xor_sync(FULL, sl1, o); sl2 += __shfl_xor_sync(FULL, sl2, o);
+        n1 += __shfl_xor_sync(FULL, n1, o); n2 += __shfl_xor_sync(FULL, n2, o);
+    }
+    if (lane != 0) return;
+    const unsigned long long* mm = gi.minmax + 4 * v;
+    ViewGrid g;
+    g.lo1 = ord_val(mm[0]); g.hi1 = ord_val(mm[1]); g.lo2 = ord_val(mm[2]); g.hi2 = ord_val(mm[3]);
+    if (!(g.lo1 <= g.hi1)) { g.lo1 = g.hi1 = g.lo2 = g.hi2 = 0.0; }   // view without (finite) edges
+    const double range1 = g.hi1 - g.lo1, range2 = g.hi2 - g.lo2;
+    const double cw1 = n1 ? exp(sl1 / n1) / GRID_CELLS_PER_WEDGE : range1 / 64, cw2 = n2 ? exp(sl2 / n2) / GRID_CELLS_PER_WEDGE : range2 / 64;
+    double G1 = range1 > 0 ? fmin(ceil(range1 / cw1), double(GRID_MAX_BINS)) : 1.0;
+    double G2 = range2 > 0 ? fmin(ceil(range2 / cw2), double(GRID_MAX_BINS)) : 1.0;
+    const double budget = double(gi.CS - 4);
+    if (G1 * G2 > budget) {
+        const double f = sqrt(budget / (G1 * G2));
+        G1 = fmax(1.0, floor(G1 * f)); G2 = fmax(1.0, floor(G2 * f));
+        if (G1 * G2 > budget) G2 = fmax(1.0, floor(budget / G1));
+        if (G1 * G2 > budget) G1 = fmax(1.0, floor(budget / G2));
+    }
+    g.G1 = int(G1); g.G2 = int(G2);
+    g.s1 = range1 > 0 ? G1 / range1 : 0.0;
+    g.s2 = range2 > 0 ? G2 / range2 : 0.0;
+    gi.vg[v] = g;
 }
-// counting-sort scatter; afterwards bins[v][b] holds the END of bin b (start of bin b is bins[v][b-1])
-__global__ void k_stage_scatter(EdgeArena ea, const int64_t* __restrict__ edge_off, const int32_t* __restrict__ edge_n,
-                                const int32_t* __restrict__ vali_view, BinGrid bg) {
+__global__ void __launch_bounds__(256) k_stage_hist(EdgeArena ea, const int64_t* __restrict__ edge_off, const int32_t* __restrict__ edge_n,
+                                                    const int32_t* __restrict__ vali_view) {
     const int v = blockIdx.y;
     const int view = vali_view[v];
     const int n = edge_n[view];
     const int64_t off = edge_off[view];
+    const ViewGrid g = ea.gi.vg[v];
+    int32_t* ceA = ea.gi.A.cell_end + int64_t(v) * ea.gi.CS;
+    int32_t* ceB = ea.gi.B.cell_end + int64_t(v) * ea.gi.CS;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         const double2 a = ea.ang[off + i];
-        const double2 t = make_double2(ea.cs[off + i], ea.sn[off + i]);
-        const int p1 = atomicAdd(&ea.ix1.bins[int64_t(v) * bg.BS + ea.bin1[off + i]], 1);
-        const int p2 = atomicAdd(&ea.ix2.bins[int64_t(v) * bg.BS + ea.bin2[off + i]], 1);
-        ea.ix1.ang[off + p1] = a; ea.ix1.tan[off + p1] = t; ea.ix1.idx[off + p1] = i;
-        ea.ix2.ang[off + p2] = a; ea.ix2.tan[off + p2] = t; ea.ix2.idx[off + p2] = i;
+        const int c = grid_bins(a.x, a.y, g);
+        ea.cell[off + i] = c;
+        atomicAdd(&ceA[cell_A(c, g)], 1);
+        atomicAdd(&ceB[cell_B(c, g)], 1);
+    }
+}
+// Segmented exclusive scan of the cell histograms (one segment per view and layout, G1 * G2 + 1 used cells each), in place:
+// tile sums -> scan of the tile sums of a segment -> tile-local scan + tile offset.  Coalesced int4 traffic throughout.
+#define SCAN_TILE 4096   // 1024 threads x int4
+int scan_tiles(int CS) { return (CS + SCAN_TILE - 1) / SCAN_TILE; }
+__device__ __forceinline__ int32_t* scan_segment(int32_t* cellsA, int32_t* cellsB, int n_vali, int CS, const ViewGrid* vg, int* n_used) {
+    const int seg = blockIdx.y;
+    const int v = seg < n_vali ? seg : seg - n_vali;
+    *n_used = vg[v].G1 * vg[v].G2 + 1;
+    return (seg < n_vali ? cellsA : cellsB) + int64_t(v) * CS;
+}
+__device__ __forceinline__ int block_sum_1024(int x, int* sh) {   // returns the block total; sh[32]
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(FULL, x, o);
+    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = x;
+    __syncthreads();
+    int t = (threadIdx.x < 32) ? sh[threadIdx.x] : 0;
+    if (threadIdx.x < 32) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(FULL, t, o);
+        if (threadIdx.x == 0) sh[0] = t;
+    }
+    __syncthreads();
+    return sh[0];
+}
+__global__ void __launch_bounds__(1024) k_cell_tile_sums(int32_t* cellsA, int32_t* cellsB, int n_vali, int CS, const ViewGrid* __restrict__ vg,
+                                                         int32_t* __restrict__ tile_sums, int tiles) {
+    __shared__ int sh[32];
+    int n;
+    const int32_t* b = scan_segment(cellsA, cellsB, n_vali, CS, vg, &n);
+    const int base = blockIdx.x * SCAN_TILE;
+    if (base >= n) return;
+    const int i = base + threadIdx.x * 4;
+    int s = 0;
+    if (i + 3 < n) { const int4 q = *reinterpret_cast<const int4*>(b + i); s = q.x + q.y + q.z + q.w; }
+    else for (int k = i; k < n; k++) s += b[k];
+    const int tot = block_sum_1024(s, sh);
+    if (threadIdx.x == 0) tile_sums[blockIdx.y * tiles + blockIdx.x] = tot;
+}
+__global__ void __launch_bounds__(1024) k_cell_tile_scan(int32_t* tile_sums, int tiles, int n_vali, int CS, const ViewGrid* __restrict__ vg) {
+    // one block per segment; tiles <= 16384 (CS <= 2^26): each thread owns a contiguous run
+    __shared__ int part[1024];
+    const int seg = blockIdx.x;
+    const int v = seg < n_vali ? seg : seg - n_vali;
+    const int used = (vg[v].G1 * vg[v].G2 + 1 + SCAN_TILE - 1) / SCAN_TILE;
+    int32_t* t = tile_sums + seg * tiles;
+    const int per = (used + 1023) / 1024;
+    const int lo = min(int(threadIdx.x) * per, used), hi = min(lo + per, used);
+    int s = 0;
+    for (int i = lo; i < hi; i++) s += t[i];
+    part[threadIdx.x] = s;
+    __syncthreads();
+    for (int d = 1; d < 1024; d <<= 1) {
+        const int x = (threadIdx.x >= d) ? part[threadIdx.x - d] : 0;
+        __syncthreads();
+        part[threadIdx.x] += x;
+        __syncthreads();
+    }
+    int run = part[threadIdx.x] - s;
+    for (int i = lo; i < hi; i++) { const int c = t[i]; t[i] = run; run += c; }
+}
+__global__ void __launch_bounds__(1024) k_cell_scan_apply(int32_t* cellsA, int32_t* cellsB, int n_vali, int CS, const ViewGrid* __restrict__ vg,
+                                                          const int32_t* __restrict__ tile_sums, int tiles) {
+    __shared__ int wsum[32];
+    int n;
+    int32_t* b = scan_segment(cellsA, cellsB, n_vali, CS, vg, &n);
+    const int base = blockIdx.x * SCAN_TILE;
+    if (base >= n) return;
+    const int i = base + threadIdx.x * 4;
+    int q[4] = {0, 0, 0, 0};
+    if (i + 3 < n) { const int4 t = *reinterpret_cast<const int4*>(b + i); q[0] = t.x; q[1] = t.y; q[2] = t.z; q[3] = t.w; }
+    else for (int k = 0; k < 4; k++) if (i + k < n) q[k] = b[i + k];
+    const int mine = q[0] + q[1] + q[2] + q[3];
+    int inc = mine;                                     // inclusive scan across the warp
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(FULL, inc, o); if (lane >= o) inc += t; }
+    if (lane == 31) wsum[wid] = inc;
+    __syncthreads();
+    if (wid == 0) {
+        int w = wsum[lane], winc = w;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(FULL, winc, o); if (lane >= o) winc += t; }
+        wsum[lane] = winc - w;                          // exclusive offset of each warp
+    }
+    __syncthreads();
+    int run = tile_sums[blockIdx.y * tiles + blockIdx.x] + wsum[wid] + inc - mine;
+    int o4[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) { o4[k] = run; run += q[k]; }
+    if (i + 3 < n) *reinterpret_cast<int4*>(b + i) = make_int4(o4[0], o4[1], o4[2], o4[3]);
+    else for (int k = 0; k < 4; k++) if (i + k < n) b[i + k] = o4[k];
+}
+static void launch_cell_scan(const GridIndex& gi, int n_vali, int32_t* scan_tmp, cudaStream_t st) {
+    const int tiles = scan_tiles(gi.CS);
+    dim3 grid(tiles, 2 * n_vali);
+    k_cell_tile_sums<<<grid, 1024, 0, st>>>(gi.A.cell_end, gi.B.cell_end, n_vali, gi.CS, gi.vg, scan_tmp, tiles);
+    k_cell_tile_scan<<<2 * n_vali, 1024, 0, st>>>(scan_tmp, tiles, n_vali, gi.CS, gi.vg);
+    k_cell_scan_apply<<<grid, 1024, 0, st>>>(gi.A.cell_end, gi.B.cell_end, n_vali, gi.CS, gi.vg, scan_tmp, tiles);
+}
+// counting-sort scatter; afterwards cell_end[v][c] holds the END of cell c (start of cell c is cell_end[v][c-1])
+__global__ void __launch_bounds__(256) k_stage_scatter(EdgeArena ea, const int64_t* __restrict__ edge_off, const int32_t* __restrict__ edge_n,
+                                                       const int32_t* __restrict__ vali_view) {
+    const int v = blockIdx.y;
+    const int view = vali_view[v];
+    const int n = edge_n[view];
+    const int64_t off = edge_off[view];
+    const ViewGrid g = ea.gi.vg[v];
+    int32_t* ceA = ea.gi.A.cell_end + int64_t(v) * ea.gi.CS;
+    int32_t* ceB = ea.gi.B.cell_end + int64_t(v) * ea.gi.CS;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const int c = ea.cell[off + i];
+        const double2 a = ea.ang[off + i];
+        const double4 rec = make_double4(a.x, a.y, ea.cs[off + i], ea.sn[off + i]);
+        const int pa = atomicAdd(&ceA[cell_A(c, g)], 1);
+        const int pb = atomicAdd(&ceB[cell_B(c, g)], 1);
+        ea.gi.A.rec[off + pa] = rec; ea.gi.A.idx[off + pa] = i;
+        ea.gi.B.rec[off + pb] = rec; ea.gi.B.idx[off + pb] = i;
     }
 }
 void launch_stage_views(const EdgeArena& ea, const int64_t* edge_off, const int32_t* edge_n, const int32_t* vali_view, int n_vali,
-                        int max_edges, const ViewConst* vc, const BinGrid& bg, cudaStream_t st, int* launches) {
+                        int max_edges, const ViewConst* vc, const GridSample& gs, int32_t* scan_tmp, cudaStream_t st, int* launches) {
     if (n_vali <= 0) return;
-    cudaMemsetAsync(ea.ix1.bins, 0, size_t(n_vali) * bg.BS * sizeof(int32_t), st);
-    cudaMemsetAsync(ea.ix2.bins, 0, size_t(n_vali) * bg.BS * sizeof(int32_t), st);
+    cudaMemsetAsync(ea.gi.A.cell_end, 0, size_t(n_vali) * ea.gi.CS * sizeof(int32_t), st);
+    cudaMemsetAsync(ea.gi.B.cell_end, 0, size_t(n_vali) * ea.gi.CS * sizeof(int32_t), st);
     int bx = (max_edges + 255) / 256;
     if (bx < 1) bx = 1;
     if (bx > 1024) bx = 1024;
     dim3 grid(bx, n_vali);
-    k_stage_angles<<<grid, 256, 0, st>>>(ea, edge_off, edge_n, vali_view, vc, bg);
-    k_scan_bins<<<2 * n_vali, 1024, 0, st>>>(ea.ix1.bins, ea.ix2.bins, n_vali, bg.BS);
-    k_stage_scatter<<<grid, 256, 0, st>>>(ea, edge_off, edge_n, vali_view, bg);
-    if (launches) *launches += 3;
+    k_minmax_init<<<(n_vali + 127) / 128, 128, 0, st>>>(ea.gi.minmax, n_vali);
+    k_stage_angles<<<grid, 256, 0, st>>>(ea, edge_off, edge_n, vali_view, vc);
+    k_grid_params<false><<<(n_vali + 3) / 4, 128, 0, st>>>(ea.gi, n_vali, gs, vc);
+    k_stage_hist<<<grid, 256, 0, st>>>(ea, edge_off, edge_n, vali_view);
+    launch_cell_scan(ea.gi, n_vali, scan_tmp, st);
+    k_stage_scatter<<<grid, 256, 0, st>>>(ea, edge_off, edge_n, vali_view);
+    if (launches) *launches += 8;
 }
 
-// stand-alone support test: the per-view angle / tangent arrays are given; only the two indexes are built here
-__global__ void k_given_hist(const double* __restrict__ a31, const double* __restrict__ a32, const int64_t* __restrict__ view_off,
-                             int32_t* __restrict__ bin1, int32_t* __restrict__ bin2, BinGrid bg, int32_t* bins1, int32_t* bins2) {
+// stand-alone support test: the per-view angle / tangent arrays are given; only the grid is built here
+__global__ void __launch_bounds__(256) k_given_minmax(const double* __restrict__ a31, const double* __restrict__ a32,
+                                                      const int64_t* __restrict__ view_off, unsigned long long* minmax) {
     const int v = blockIdx.y;
     const int64_t b0 = view_off[v], n = view_off[v + 1] - b0;
+    double mn1 = DBL_MAX, mx1 = -DBL_MAX, mn2 = DBL_MAX, mx2 = -DBL_MAX;
     for (int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; i < n; i += int64_t(gridDim.x) * blockDim.x) {
-        const int b1 = bin_of(a31[b0 + i], bg.scale, bg.B), b2 = bin_of(a32[b0 + i], bg.scale, bg.B);
-        bin1[b0 + i] = b1; bin2[b0 + i] = b2;
-        atomicAdd(&bins1[int64_t(v) * bg.BS + b1], 1);
-        atomicAdd(&bins2[int64_t(v) * bg.BS + b2], 1);
+        const double x = a31[b0 + i], y = a32[b0 + i];
+        if (x == x && y == y) { mn1 = fmin(mn1, x); mx1 = fmax(mx1, x); mn2 = fmin(mn2, y); mx2 = fmax(mx2, y); }
+    }
+    minmax_commit(mn1, mx1, mn2, mx2, minmax + 4 * v);
+}
+__global__ void __launch_bounds__(256) k_given_hist(const double* __restrict__ a31, const double* __restrict__ a32,
+                                                    const int64_t* __restrict__ view_off, int32_t* __restrict__ cell, GridIndex gi) {
+    const int v = blockIdx.y;
+    const int64_t b0 = view_off[v], n = view_off[v + 1] - b0;
+    const ViewGrid g = gi.vg[v];
+    int32_t* ceA = gi.A.cell_end + int64_t(v) * gi.CS;
+    int32_t* ceB = gi.B.cell_end + int64_t(v) * gi.CS;
+    for (int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; i < n; i += int64_t(gridDim.x) * blockDim.x) {
+        const int c = grid_bins(a31[b0 + i], a32[b0 + i], g);
+        cell[b0 + i] = c;
+        atomicAdd(&ceA[cell_A(c, g)], 1);
+        atomicAdd(&ceB[cell_B(c, g)], 1);
     }
 }
-__global__ void k_given_scatter(const double* __restrict__ a31, const double* __restrict__ a32, const double* __restrict__ cs,
-                                const double* __restrict__ sn, const int64_t* __restrict__ view_off, const int32_t* __restrict__ bin1,
-                                const int32_t* __restrict__ bin2, BinGrid bg, ViewIndex ix1, ViewIndex ix2) {
+__global__ void __launch_bounds__(256) k_given_scatter(const double* __restrict__ a31, const double* __restrict__ a32, const double* __restrict__ cs,
+                                                       const double* __restrict__ sn, const int64_t* __restrict__ view_off,
+                                                       const int32_t* __restrict__ cell, GridIndex gi) {
     const int v = blockIdx.y;
     const int64_t b0 = view_off[v], n = view_off[v + 1] - b0;
+    const ViewGrid g = gi.vg[v];
+    int32_t* ceA = gi.A.cell_end + int64_t(v) * gi.CS;
+    int32_t* ceB = gi.B.cell_end + int64_t(v) * gi.CS;
     for (int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; i < n; i += int64_t(gridDim.x) * blockDim.x) {
-        const double2 a = make_double2(a31[b0 + i], a32[b0 + i]);
-        const double2 t = make_double2(cs[b0 + i], sn[b0 + i]);
-        const int p1 = atomicAdd(&ix1.bins[int64_t(v) * bg.BS + bin1[b0 + i]], 1);
-        const int p2 = atomicAdd(&ix2.bins[int64_t(v) * bg.BS + bin2[b0 + i]], 1);
-        ix1.ang[b0 + p1] = a; ix1.tan[b0 + p1] = t; ix1.idx[b0 + p1] = int32_t(i);
-        ix2.ang[b0 + p2] = a; ix2.tan[b0 + p2] = t; ix2.idx[b0 + p2] = int32_t(i);
+        const int c = cell[b0 + i];
+        const double4 rec = make_double4(a31[b0 + i], a32[b0 + i], cs[b0 + i], sn[b0 + i]);
+        const int pa = atomicAdd(&ceA[cell_A(c, g)], 1);
+        const int pb = atomicAdd(&ceB[cell_B(c, g)], 1);
+        gi.A.rec[b0 + pa] = rec; gi.A.idx[b0 + pa] = int32_t(i);
+        gi.B.rec[b0 + pb] = rec; gi.B.idx[b0 + pb] = int32_t(i);
     }
 }
 void launch_stage_given(const double* a31, const double* a32, const double* cs, const double* sn, const int64_t* view_off, int n_vali,
-                        int64_t max_edges, int32_t* bin1, int32_t* bin2, const BinGrid& bg, ViewIndex ix1, ViewIndex ix2, cudaStream_t st) {
-    cudaMemsetAsync(ix1.bins, 0, size_t(n_vali) * bg.BS * sizeof(int32_t), st);
-    cudaMemsetAsync(ix2.bins, 0, size_t(n_vali) * bg.BS * sizeof(int32_t), st);
+                        int64_t max_edges, int32_t* cell, GridIndex gi, const GridSample& gs, int32_t* scan_tmp, cudaStream_t st, int* launches) {
+    cudaMemsetAsync(gi.A.cell_end, 0, size_t(n_vali) * gi.CS * sizeof(int32_t), st);
+    cudaMemsetAsync(gi.B.cell_end, 0, size_t(n_vali) * gi.CS * sizeof(int32_t), st);
     int64_t bx = (max_edges + 255) / 256;
     if (bx < 1) bx = 1;
     if (bx > 2048) bx = 2048;
     dim3 grid((unsigned)bx, n_vali);
-    k_given_hist<<<grid, 256, 0, st>>>(a31, a32, view_off, bin1, bin2, bg, ix1.bins, ix2.bins);
-    k_scan_bins<<<2 * n_vali, 1024, 0, st>>>(ix1.bins, ix2.bins, n_vali, bg.BS);
-    k_given_scatter<<<grid, 256, 0, st>>>(a31, a32, cs, sn, view_off, bin1, bin2, bg, ix1, ix2);
+    k_minmax_init<<<(n_vali + 127) / 128, 128, 0, st>>>(gi.minmax, n_vali);
+    k_given_minmax<<<grid, 256, 0, st>>>(a31, a32, view_off, gi.minmax);
+    k_grid_params<true><<<(n_vali + 3) / 4, 128, 0, st>>>(gi, n_vali, gs, nullptr);
+    k_given_hist<<<grid, 256, 0, st>>>(a31, a32, view_off, cell, gi);
+    launch_cell_scan(gi, n_vali, scan_tmp, st);
+    k_given_scatter<<<grid, 256, 0, st>>>(a31, a32, cs, sn, view_off, cell, gi);
+    if (launches) *launches += 8;
 }
 
 // ----------------------------------------------------------------------------- pass-level tables
@@ -623,22 +847,44 @@ void launch_wedge31(const PassConst& pc, const ViewConst* vc, const double* x1, 
 
 // One thread per (unique hypothesis, validation view):
 //   getGamma3LocationAndTangent (EdgeSketch_Core.cpp:330, view-dependent part), getOreListBar of the clustered view-2 edge
-//   (:340), is_Epipolar_Wedges_in_Parallel (hpp:112-128), getHYPO2_idx_Ore x2 + set_intersection (:348-374) as a walk over
-//   the narrower of the two angular indexes with the exact strict tests of PairEdgeHypo.cpp:94 on both angles, and
-//   getSupportIdx (getSupportedEdgels.cpp:32-47: d >= thr && d > prev in ascending index order == maximum, ties to the
-//   lowest index).  Threads of a warp are consecutive hypotheses of (mostly) one view-1 edge: they share wedge31, the bin
-//   lookups and -- when the a31-keyed index is the narrower one -- the whole walk (broadcast loads).
+//   (:340), is_Epipolar_Wedges_in_Parallel (hpp:112-128), getHYPO2_idx_Ore x2 + set_intersection (:348-374) as a query of the
+//   view's (a31, a32) bin grid -- the cells overlapped by wedge31 x wedge32 -- with the exact strict tests of
+//   PairEdgeHypo.cpp:94 on both angles, and getSupportIdx (getSupportedEdgels.cpp:32-47: d >= thr && d > prev in ascending
+//   index order == maximum, ties to the lowest index).  Threads of a warp are consecutive hypotheses of (mostly) one view-1
+//   edge and one view: they share wedge31 and hit neighbouring cells.  Queries that overlap many cells or long cells (wedges
+//   that wrap around 0/180 degrees, epipole inside the image: SURVEY.md a3) are walked by the whole warp instead of one lane.
 #define VAL_THREADS 128
+#define VAL_LIGHT_ROWS 4       // row ranges a lane keeps in registers
+#define VAL_COOP_MIN 96        // a query becomes a whole-warp job when its work exceeds this and 4x the warp's mean
+struct SupportAcc {
+    double best;   // prev_prod, getSupportedEdgels.cpp:33
+    int bidx;
+    unsigned n_in, n_vis;
+};
+__device__ __forceinline__ void support_visit(SupportAcc& s, const double4 e, int j, const double2 w1, const double2 w2, const double2 tg,
+                                              double thr, const int32_t* __restrict__ idx_) {
+    s.n_vis++;
+    if (e.x > w1.x && e.x < w1.y && e.y > w2.x && e.y < w2.y) {          // PairEdgeHypo.cpp:94, both wedges
+        s.n_in++;
+        const double d = fabs(tg.x * e.z + tg.y * e.w);                   // getSupportedEdgels.cpp:38
+        if (d >= thr && d >= s.best) {
+            const int idx = idx_[j];
+            if (d > s.best || (s.bidx != -2 && idx < s.bidx)) { s.best = d; s.bidx = idx; }
+        }
+    }
+}
 template <bool GIVEN>
 __global__ void __launch_bounds__(VAL_THREADS) k_validate(const __grid_constant__ PassConst pc, const __grid_constant__ ValidateArgs a) {
     const int64_t u = blockIdx.x * int64_t(VAL_THREADS) + threadIdx.x;
     const int v = blockIdx.y;
-    unsigned long long c_sup = 0, c_par = 0, c_inl = 0, c_deg = 0;
+    const int lane = threadIdx.x & 31;
+    unsigned long long c_sup = 0, c_par = 0, c_inl = 0, c_deg = 0, c_vis = 0, c_hvy = 0, mult = 0;
+    double2 w1 = make_double2(0, 0), w2 = make_double2(0, 0), tg = make_double2(0, 0);
+    bool active = false;
     if (u < a.U) {
         const int h1 = a.ut.h1[u];
-        const unsigned long long mult = GIVEN ? 1ULL : (unsigned long long)a.ut.mult[u];
-        const double2 w1 = a.w31[int64_t(v) * a.w31_stride + h1];
-        double2 w2, tg;
+        mult = GIVEN ? 1ULL : (unsigned long long)a.ut.mult[u];
+        w1 = a.w31[int64_t(v) * a.w31_stride + h1];
         if (GIVEN) {
             w2 = a.w32_in[int64_t(v) * a.U + u];
             tg = a.tgt_in[int64_t(v) * a.U + u];
@@ -655,65 +901,128 @@ __global__ void __launch_bounds__(VAL_THREADS) k_validate(const __grid_constant_
         }
         const bool w1_bad = (w1.x != w1.x), w2_bad = (w2.x != w2.x);
         if (w2_bad) c_deg = mult;
-        bool active = false;
         if (!w1_bad && !w2_bad) {
             const double d0 = fabs(w1.x - w2.x), d1 = fabs(w1.x - w2.y), d2 = fabs(w1.y - w2.x), d3 = fabs(w1.y - w2.y);
             const double dmax = fmax(fmax(d0, d1), fmax(d2, d3));
             if (dmax <= a.parallel_deg) c_par = mult;                       // hpp:120 (inclusive)
             else active = true;
         }
-        double best = 0.0;   // prev_prod, getSupportedEdgels.cpp:33
-        int bidx = -2;
-        if (active) {
-            const int64_t off = a.edge_off[a.vali_view ? a.vali_view[v] : v];
-            const int32_t* bins1 = a.ix1.bins + int64_t(v) * a.bg.BS;
-            const int32_t* bins2 = a.ix2.bins + int64_t(v) * a.bg.BS;
-            const int p0 = bin_of(w1.x, a.bg.scale, a.bg.B), p1 = bin_of(w1.y, a.bg.scale, a.bg.B);
-            const int q0 = bin_of(w2.x, a.bg.scale, a.bg.B), q1 = bin_of(w2.y, a.bg.scale, a.bg.B);
-            const int beg1 = p0 ? bins1[p0 - 1] : 0, end1 = bins1[p1];
-            const int beg2 = q0 ? bins2[q0 - 1] : 0, end2 = bins2[q1];
-            const bool use1 = (end1 - beg1) <= (end2 - beg2);
-            const ViewIndex& ix = use1 ? a.ix1 : a.ix2;
-            const int beg = use1 ? beg1 : beg2, end = use1 ? end1 : end2;
-            const double2* __restrict__ ang = ix.ang + off;
-            const double2* __restrict__ tan_ = ix.tan + off;
-            const int32_t* __restrict__ idx_ = ix.idx + off;
-            unsigned n_in = 0;
-            for (int j = beg; j < end; j++) {
-                const double2 e = ang[j];
-                if (e.x > w1.x && e.x < w1.y && e.y > w2.x && e.y < w2.y) {          // PairEdgeHypo.cpp:94, both wedges
-                    n_in++;
-                    const double2 t = tan_[j];
-                    const double d = fabs(tg.x * t.x + tg.y * t.y);                   // getSupportedEdgels.cpp:38
-                    const int idx = idx_[j];
-                    if (d >= a.cos_thresh && (d > best || (d == best && bidx != -2 && idx < bidx))) { best = d; bidx = idx; }
+    }
+    // ---- wedge31 n wedge32 through the view's bin grid
+    const ViewGrid vg = a.gi.vg[v];
+    const int64_t off = a.edge_off[a.vali_view ? a.vali_view[v] : v];
+    const int64_t ce_off = int64_t(v) * a.gi.CS;
+    SupportAcc acc = {0.0, -2, 0u, 0u};
+    int r0 = 0, r1 = -1, c0 = 0, c1 = 0, work = 0, G = 1;
+    int beg[VAL_LIGHT_ROWS], end[VAL_LIGHT_ROWS];
+    bool useB = false;
+    // every edge angle of the view lies in [lo, hi]: a wedge outside that range has no member (strict tests)
+    if (active && w1.y > vg.lo1 && w1.x < vg.hi1 && w2.y > vg.lo2 && w2.x < vg.hi2) {
+        const int p0 = grid_bin(w1.x, vg.lo1, vg.s1, vg.G1), p1 = grid_bin(w1.y, vg.lo1, vg.s1, vg.G1);
+        const int q0 = grid_bin(w2.x, vg.lo2, vg.s2, vg.G2), q1 = grid_bin(w2.y, vg.lo2, vg.s2, vg.G2);
+        useB = (p1 - p0) > (q1 - q0);                   // rows along the angle in which the rectangle is narrower
+        r0 = useB ? q0 : p0; r1 = useB ? q1 : p1; c0 = useB ? p0 : q0; c1 = useB ? p1 : q1;
+        G = useB ? vg.G1 : vg.G2;                       // row stride of the chosen layout
+        const int32_t* __restrict__ ce = (useB ? a.gi.B.cell_end : a.gi.A.cell_end) + ce_off;
+        if (r1 - r0 < VAL_LIGHT_ROWS) {
+#pragma unroll
+            for (int r = 0; r < VAL_LIGHT_ROWS; r++) {
+                beg[r] = end[r] = 0;
+                if (r0 + r <= r1) {
+                    const int cc = (r0 + r) * G + c0;
+                    beg[r] = cc ? ce[cc - 1] : 0;
+                    end[r] = ce[(r0 + r) * G + c1];
+                    work += end[r] - beg[r];
                 }
             }
-            c_inl = mult * n_in;
-            if (bidx != -2) c_sup = mult;
+        } else {
+            work = 8 * (r1 - r0 + 1);                   // not looked up yet: an estimate is enough for the split below
         }
-        a.support[int64_t(v) * a.sup_stride + u] = bidx;
+    } else {
+        active = false;
+    }
+    // a query much heavier than its warp's mean is walked by the whole warp; the rest by their own lane
+    int wsum = work, wcnt = active ? 1 : 0;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) { wsum += __shfl_xor_sync(FULL, wsum, o); wcnt += __shfl_xor_sync(FULL, wcnt, o); }
+    const bool heavy = active && work > VAL_COOP_MIN && work * max(wcnt, 1) > 4 * wsum;
+    if (active && !heavy) {
+        const GridLayout& L = useB ? a.gi.B : a.gi.A;
+        const double4* __restrict__ rec = L.rec + off;
+        const int32_t* __restrict__ idx_ = L.idx + off;
+        if (r1 - r0 < VAL_LIGHT_ROWS) {
+#pragma unroll
+            for (int r = 0; r < VAL_LIGHT_ROWS; r++)
+                for (int j = beg[r]; j < end[r]; j++) support_visit(acc, rec[j], j, w1, w2, tg, a.cos_thresh, idx_);
+        } else {
+            const int32_t* __restrict__ ce = L.cell_end + ce_off;
+            for (int b = r0; b <= r1; b++) {
+                const int cc = b * G + c0;
+                const int jb = cc ? ce[cc - 1] : 0, je = ce[b * G + c1];
+                for (int j = jb; j < je; j++) support_visit(acc, rec[j], j, w1, w2, tg, a.cos_thresh, idx_);
+            }
+        }
+    }
+    // ---- warp-cooperative walk of the heavy queries, one at a time
+    unsigned hm = __ballot_sync(FULL, heavy);
+    while (hm) {
+        const int src = __ffs(hm) - 1;
+        hm &= hm - 1;
+        const double2 sw1 = make_double2(__shfl_sync(FULL, w1.x, src), __shfl_sync(FULL, w1.y, src));
+        const double2 sw2 = make_double2(__shfl_sync(FULL, w2.x, src), __shfl_sync(FULL, w2.y, src));
+        const double2 stg = make_double2(__shfl_sync(FULL, tg.x, src), __shfl_sync(FULL, tg.y, src));
+        const int sr0 = __shfl_sync(FULL, r0, src), sr1 = __shfl_sync(FULL, r1, src);
+        const int sc0 = __shfl_sync(FULL, c0, src), sc1 = __shfl_sync(FULL, c1, src);
+        const bool sB = __shfl_sync(FULL, int(useB), src) != 0;
+        const int sG = __shfl_sync(FULL, G, src);
+        const GridLayout& L = sB ? a.gi.B : a.gi.A;
+        const double4* __restrict__ rec = L.rec + off;
+        const int32_t* __restrict__ idx_ = L.idx + off;
+        const int32_t* __restrict__ ce = L.cell_end + ce_off;
+        SupportAcc ca = {0.0, -2, 0u, 0u};
+        if (sr1 - sr0 + 1 >= 8) {                       // many rows: one lane per row
+            for (int b = sr0 + lane; b <= sr1; b += 32) {
+                const int cc = b * sG + sc0;
+                const int jb = cc ? ce[cc - 1] : 0, je = ce[b * sG + sc1];
+                for (int j = jb; j < je; j++) support_visit(ca, rec[j], j, sw1, sw2, stg, a.cos_thresh, idx_);
+            }
+        } else {                                        // few long rows: the lanes stride over the entries
+            for (int b = sr0; b <= sr1; b++) {
+                const int cc = b * sG + sc0;
+                const int jb = cc ? ce[cc - 1] : 0, je = ce[b * sG + sc1];
+                for (int j = jb + lane; j < je; j += 32) support_visit(ca, rec[j], j, sw1, sw2, stg, a.cos_thresh, idx_);
+            }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {              // maximum, ties to the lowest edge index
+            const double od = __shfl_xor_sync(FULL, ca.best, o);
+            const int oi = __shfl_xor_sync(FULL, ca.bidx, o);
+            ca.n_in += __shfl_xor_sync(FULL, ca.n_in, o); ca.n_vis += __shfl_xor_sync(FULL, ca.n_vis, o);
+            if (oi != -2 && (ca.bidx == -2 || od > ca.best || (od == ca.best && oi < ca.bidx))) { ca.best = od; ca.bidx = oi; }
+        }
+        if (lane == src) { acc = ca; c_hvy = 1; }
+    }
+    if (u < a.U) {
+        c_inl = mult * acc.n_in; c_vis = acc.n_vis;
+        if (acc.bidx != -2) c_sup = mult;
+        a.support[int64_t(v) * a.sup_stride + u] = acc.bidx;
     }
     if (a.ctr == nullptr) return;
-    // block-aggregated statistics -> one slot per block
-    __shared__ unsigned long long red[4][VAL_THREADS / 32];
+    // warp-aggregated statistics -> one counter slot per warp (no block barrier: warps retire independently)
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
         c_sup += __shfl_xor_sync(FULL, c_sup, o); c_par += __shfl_xor_sync(FULL, c_par, o);
         c_inl += __shfl_xor_sync(FULL, c_inl, o); c_deg += __shfl_xor_sync(FULL, c_deg, o);
+        c_vis += __shfl_xor_sync(FULL, c_vis, o); c_hvy += __shfl_xor_sync(FULL, c_hvy, o);
     }
-    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    if (lane == 0) { red[0][wid] = c_sup; red[1][wid] = c_par; red[2][wid] = c_inl; red[3][wid] = c_deg; }
-    __syncthreads();
-    if (threadIdx.x < 4) {
-        unsigned long long s = 0;
-        for (int w = 0; w < VAL_THREADS / 32; w++) s += red[threadIdx.x][w];
-        if (s) {
-            const int slot = (blockIdx.x + blockIdx.y) & (CVX_CTR_SLOTS - 1);
-            unsigned long long* dst = threadIdx.x == 0 ? a.ctr->n_supported : threadIdx.x == 1 ? a.ctr->n_parallel
-                                      : threadIdx.x == 2 ? a.ctr->n_inliers : a.ctr->n_degenerate;
-            atomicAdd(&dst[slot], s);
-        }
+    if (lane == 0) {
+        const int slot = int((blockIdx.x * (VAL_THREADS / 32) + (threadIdx.x >> 5) + blockIdx.y) & (CVX_CTR_SLOTS - 1));
+        if (c_sup) atomicAdd(&a.ctr->n_supported[slot], c_sup);
+        if (c_par) atomicAdd(&a.ctr->n_parallel[slot], c_par);
+        if (c_inl) atomicAdd(&a.ctr->n_inliers[slot], c_inl);
+        if (c_deg) atomicAdd(&a.ctr->n_degenerate[slot], c_deg);
+        if (c_vis) atomicAdd(&a.ctr->n_visited[slot], c_vis);
+        if (c_hvy) atomicAdd(&a.ctr->n_heavy[slot], c_hvy);
     }
 }
 void launch_validate(const PassConst& pc, const ValidateArgs& a, bool given, cudaStream_t st) {

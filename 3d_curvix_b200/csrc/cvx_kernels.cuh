@@ -10,26 +10,42 @@
 
 namespace cvx {
 
-// One angular index of the validation views: every view's edges counting-sorted by the bin of one of their two
-// epipolar angles.  Entry e of view slot v lives at [edge_off[view] + e]; bins[v][b] = END (exclusive) of bin b.
-struct ViewIndex {
-    double2* ang;    // (a31, a32): epipolar angle about the epipole of hypothesis view 1 / view 2 (degrees, [0,180))
-    double2* tan;    // (cos theta, sin theta) of the edge orientation
-    int32_t* idx;    // original edge index inside its view
-    int32_t* bins;   // [V][BS]
+// The per-pass acceleration structure of the validation views: a uniform G1 x G2 bin grid over the two epipolar angles
+// (a31, a32) of every edge of a view -- the angular image of the pixel grid, since (a31, a32) is a smooth one-to-one map of
+// the image plane away from the epipoles.  The reference enumerates wedge31 n wedge32 with two Theta(E3) scans and a
+// set_intersection (EdgeSketch_Core.cpp:348-374); here the intersection of the two angle ranges is a small rectangle of
+// cells.  Edges of view slot v are counting-sorted by cell, in two layouts: A with cell = b1 * G2 + b2 (the cells of one a31
+// row are contiguous in a32) and B with cell = b2 * G1 + b1.  A query walks the layout in which its rectangle has fewer rows
+// (a wedge about a nearby epipole is wide in its own angle: one contiguous range in the other layout).  Entry e of a view
+// lives at [edge_off[view] + e]; cell_end[v][c] = END (exclusive) of cell c, cell G1*G2 holds NaN angles.
+struct ViewGrid {        // per validation view: bin_k = int((a_k - lo_k) * s_k), clamped to [0, G_k)
+    double lo1, hi1, s1, lo2, hi2, s2;
+    int32_t G1, G2;      // bins along a31 / a32, sized per view so that a cell is about a third of a typical wedge (G1 * G2 < CS)
+};
+struct GridLayout {
+    double4* rec;        // (a31, a32, cos theta, sin theta): the two epipolar angles (degrees, [0,180)) and the edge's unit tangent
+    int32_t* idx;        // original edge index inside its view
+    int32_t* cell_end;   // [V][CS]
+};
+struct GridIndex {
+    GridLayout A, B;
+    ViewGrid* vg;        // [V]
+    unsigned long long* minmax;   // [V][4] scratch: ordered keys of min a31, max a31, min a32, max a32
+    int32_t CS;          // cell_end stride per view (cell budget + 1, multiple of 4)
 };
 
 // Per-edge arrays of all views, concatenated; view v occupies [edge_off[v], edge_off[v] + edge_n[v]).
 struct EdgeArena {
     double *x, *y, *th, *cs, *sn;   // static per view (uploaded / derived once per cvx_set_view_edges)
     double2* ang;                   // per pass scratch: (a31, a32)
-    int32_t *bin1, *bin2;           // per pass scratch: bin of a31 / a32
-    ViewIndex ix1, ix2;             // per pass: index keyed by a31 and index keyed by a32
+    int32_t* cell;                  // per pass scratch: (b1 << 16) | b2 of the edge, -1 for NaN angles
+    GridIndex gi;                   // per pass: the bin grid of every validation view
 };
 
 #define CVX_CTR_SLOTS 64
 struct DevCounters {   // spread over slots to keep same-address atomics off the critical path; summed on the host
-    unsigned long long n_degenerate[CVX_CTR_SLOTS], n_supported[CVX_CTR_SLOTS], n_parallel[CVX_CTR_SLOTS], n_inliers[CVX_CTR_SLOTS];
+    unsigned long long n_degenerate[CVX_CTR_SLOTS], n_supported[CVX_CTR_SLOTS], n_parallel[CVX_CTR_SLOTS], n_inliers[CVX_CTR_SLOTS],
+        n_visited[CVX_CTR_SLOTS], n_heavy[CVX_CTR_SLOTS];
 };
 
 // Hypothesis table (one row per epipolar-corrected candidate), grouped by view-1 edge.
@@ -49,19 +65,24 @@ struct UniqTable {
     double4* geom;                      // view-independent reprojection terms: (rho1, Tv1x, Tv1y, Tv1z)
 };
 
-struct BinGrid {
-    int32_t B, BS;     // B angular bins over [0,180], BS = B + 1 (last = NaN bin)
-    double scale;      // B / 180
-};
 
 void launch_edge_trig(const double* th, double* cs, double* sn, int64_t n, cudaStream_t st);
 
-// stage all validation views of a pass: angles -> two histograms -> scan -> scatter into the two indexes
+int pick_cell_stride(int64_t max_edges);   // CS: cell budget per view (~16 cells per edge of the largest view) + 1
+// scratch of the segmented cell scan: 2 * n_vali * scan_tiles(CS) ints
+int scan_tiles(int CS);
+// what the grid sizing samples: wedges of view-1 edges in a validation view and of view-2 edges in it
+struct GridSample {
+    const double *x1, *y1, *x2, *y2; int E1, E2;    // fused path: edges of the two hypothesis views (wedge_row is evaluated on samples)
+    const double2 *w31, *w32; int64_t n31, n32;     // given path: wedge arrays [V][n31], [V][n32]
+    double delta; int rows, cols;
+};
+// stage all validation views of a pass: angles + ranges -> grid sizing -> cell histogram -> scan -> scatter into the grid
 void launch_stage_views(const EdgeArena& ea, const int64_t* edge_off, const int32_t* edge_n, const int32_t* vali_view, int n_vali,
-                        int max_edges, const ViewConst* vc, const BinGrid& bg, cudaStream_t st, int* launches);
+                        int max_edges, const ViewConst* vc, const GridSample& gs, int32_t* scan_tmp, cudaStream_t st, int* launches);
 // stage externally supplied per-view arrays (stand-alone support test): a31/a32/cs/sn concatenated with view_off[V+1]
 void launch_stage_given(const double* a31, const double* a32, const double* cs, const double* sn, const int64_t* view_off, int n_vali,
-                        int64_t max_edges, int32_t* bin1, int32_t* bin2, const BinGrid& bg, ViewIndex ix1, ViewIndex ix2, cudaStream_t st);
+                        int64_t max_edges, int32_t* cell, GridIndex gi, const GridSample& gs, int32_t* scan_tmp, cudaStream_t st, int* launches);
 
 void launch_h2_angles(const double* x2, const double* y2, int n, double ex, double ey, double* out, cudaStream_t st);
 void launch_h1_wedges(const PassConst& pc, const double* x1, const double* y1, int n, double2* wedge, int32_t* flag, cudaStream_t st);
@@ -93,7 +114,7 @@ struct ValidateArgs {
     const double2* w32_in; const double2* tgt_in;
     // per-view edge indexes
     const int32_t* vali_view; const int64_t* edge_off;
-    BinGrid bg; ViewIndex ix1, ix2;
+    GridIndex gi;
     double cos_thresh, parallel_deg, delta;
     int rows, cols, n_vali;
     // outputs

@@ -66,6 +66,8 @@ typedef struct cvx_counts {
     int64_t n_parallel;          /* validations short-circuited by is_Epipolar_Wedges_in_Parallel */
     int64_t n_inliers;           /* sum over validations of |wedge31 ∩ wedge32| (edges that reached getSupportIdx) */
     int64_t n_unique_hypotheses; /* clusters: rows of one cluster carry the same averaged edge and are validated once */
+    int64_t n_entries_visited;   /* bin-grid entries tested by the validation kernel (per unique hypothesis x view, unweighted) */
+    int64_t n_heavy_queries;     /* grid queries walked by a whole warp (wide wedges / long cells) */
 } cvx_counts;
 
 typedef struct cvx_ctx cvx_ctx;
