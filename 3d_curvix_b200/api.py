@@ -8,7 +8,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libcurvix_b200.so")
+LIB_PATH = os.environ.get("CVX_LIB_PATH") or os.path.join(_HERE, "libcurvix_b200.so")   # env override: kernel-variant experiments
 
 # every symbol include/curvix_b200.h declares
 SYMBOLS = [

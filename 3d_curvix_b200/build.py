@@ -39,7 +39,9 @@ def build_cuda(force=False, verbose=False):
     if not force and not _stale(LIB, deps):
         return LIB
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
-    cmd = [nvcc] + NVCC_FLAGS + ["-ccbin", _cxx(), "-shared", "-o", LIB] + srcs
+    out = os.environ.get("CVX_LIB_OUT", LIB)            # experiments: alternative output name + extra -D flags
+    extra = os.environ.get("CVX_NVCC_EXTRA", "").split()
+    cmd = [nvcc] + NVCC_FLAGS + extra + ["-ccbin", _cxx(), "-shared", "-o", out] + srcs
     if verbose:
         cmd.insert(1, "-Xptxas=-v")
         print(" ".join(cmd))

@@ -117,7 +117,9 @@ struct cvx_ctx {
     DevBuf<int32_t> d_vali, d_cell_end, d_cell_end_b, d_scan_tmp;
     DevBuf<ViewGrid> d_vg;
     DevBuf<unsigned long long> d_minmax;
-    DevBuf<double> d_ang2;
+    DevBuf<double> d_ang2, d_h2_sorted_ang;
+    DevBuf<int32_t> d_h2_sorted_idx, d_h2_bin_end, d_h2_bin_of;
+    AngleIndex h2ix = {};
     DevBuf<double2> d_wedge_h1;
     DevBuf<int32_t> d_wflag_h1;
     // run
@@ -293,7 +295,8 @@ int cvx_destroy(cvx_ctx* ctx) {
     for (auto* b : ib) b->release();
     DevBuf<int64_t>* lb[] = {&ctx->d_edge_off, &ctx->d_row_off, &ctx->d_u_off, &ctx->d_valid_off, &ctx->d_pair_off};
     for (auto* b : lb) b->release();
-    DevBuf<double>* db[] = {&ctx->d_ang2, &ctx->r_xc, &ctx->r_yc, &ctx->r_th, &ctx->r_xbar, &ctx->r_ybar, &ctx->r_thbar, &ctx->r_thn, &ctx->r_orient,
+    ctx->d_h2_sorted_idx.release(); ctx->d_h2_bin_end.release(); ctx->d_h2_bin_of.release();
+    DevBuf<double>* db[] = {&ctx->d_ang2, &ctx->d_h2_sorted_ang, &ctx->r_xc, &ctx->r_yc, &ctx->r_th, &ctx->r_xbar, &ctx->r_ybar, &ctx->r_thbar, &ctx->r_thn, &ctx->r_orient,
                             &ctx->f_gc, &ctx->f_gw, &ctx->f_tw, &ctx->f_h2c};
     for (auto* b : db) b->release();
     DevBuf<double2>* d2[] = {&ctx->d_wedge_h1, &ctx->u_xy, &ctx->d_w31, &ctx->d_w32, &ctx->d_tgt};
@@ -417,6 +420,14 @@ int cvx_set_hypothesis_pair(cvx_ctx* ctx, int h1, int h2) {
     const int E1 = ctx->edge_n[h1], E2 = ctx->edge_n[h2];
     CU(ctx->d_ang2.reserve(std::max(E2, 1))); CU(ctx->d_wedge_h1.reserve(std::max(E1, 1))); CU(ctx->d_wflag_h1.reserve(std::max(E1, 1)));
     launch_h2_angles(ctx->ea.x + ctx->edge_off[h2], ctx->ea.y + ctx->edge_off[h2], E2, pc.e2_21[0], pc.e2_21[1], ctx->d_ang2.p, ctx->stream);
+    {   // angle-sorted index of view 2 for the candidate search
+        AngleIndex& ix = ctx->h2ix;
+        ix.B = pick_angle_bins(E2); ix.scale = ix.B / 180.0;
+        CU(ctx->d_h2_sorted_ang.reserve(std::max(E2, 1))); CU(ctx->d_h2_sorted_idx.reserve(std::max(E2, 1)));
+        CU(ctx->d_h2_bin_end.reserve(size_t(ix.B) + 1)); CU(ctx->d_h2_bin_of.reserve(std::max(E2, 1)));
+        ix.ang = ctx->d_h2_sorted_ang.p; ix.idx = ctx->d_h2_sorted_idx.p; ix.bin_end = ctx->d_h2_bin_end.p;
+        launch_h2_index(ctx->d_ang2.p, E2, ctx->d_h2_bin_of.p, ix, ctx->stream, &ctx->tm.kernel_launches);
+    }
     launch_h1_wedges(pc, ctx->ea.x + ctx->edge_off[h1], ctx->ea.y + ctx->edge_off[h1], E1, ctx->d_wedge_h1.p, ctx->d_wflag_h1.p, ctx->stream);
     ctx->tm.kernel_launches += 2;
     cudaEventRecord(ctx->ev[1], ctx->stream);
@@ -453,7 +464,7 @@ int cvx_run_edge_sketch(cvx_ctx* ctx, int h1_begin, int h1_end) {
     CU(cudaMemsetAsync(ctx->d_ctr.p, 0, sizeof(DevCounters), st));
     cudaEventRecord(ctx->ev[0], st);
     // ---- hypothesis formation
-    launch_form_count(pc, x1, y1, h1_begin, h1_end, ctx->d_wedge_h1.p, x2, y2, th2, ctx->d_ang2.p, E2, ctx->d_m.p, ctx->d_n.p, st);
+    launch_form_count(pc, x1, y1, h1_begin, h1_end, ctx->d_wedge_h1.p, x2, y2, th2, ctx->d_ang2.p, E2, ctx->h2ix, ctx->d_m.p, ctx->d_n.p, st);
     launch_scan_i32_i64(ctx->d_n.p, ctx->d_row_off.p, E1, st);
     ctx->tm.kernel_launches += 2;
     ctx->h_row_off.resize(size_t(E1) + 1);
@@ -468,7 +479,7 @@ int cvx_run_edge_sketch(cvx_ctx* ctx, int h1_begin, int h1_end) {
     DevBuf<double>* db[] = {&ctx->r_xc, &ctx->r_yc, &ctx->r_th, &ctx->r_xbar, &ctx->r_ybar, &ctx->r_thbar, &ctx->r_thn, &ctx->r_orient};
     for (auto* b : db) CU(b->reserve(Ha));
     RowTable rt = row_table(ctx);
-    launch_form_fill(pc, x1, y1, h1_begin, h1_end, ctx->d_wedge_h1.p, x2, y2, th2, ctx->d_ang2.p, E2, ctx->d_n.p, ctx->d_row_off.p, rt,
+    launch_form_fill(pc, x1, y1, h1_begin, h1_end, ctx->d_wedge_h1.p, x2, y2, th2, ctx->d_ang2.p, E2, ctx->h2ix, ctx->d_m.p, ctx->d_n.p, ctx->d_row_off.p, rt,
                      ctx->d_ncl.p, st);
     launch_scan_i32_i64(ctx->d_ncl.p, ctx->d_u_off.p, E1, st);
     ctx->tm.kernel_launches += 2;

@@ -386,6 +386,54 @@ __global__ void k_h2_angles(const double* __restrict__ x2, const double* __restr
 void launch_h2_angles(const double* x2, const double* y2, int n, double ex, double ey, double* out, cudaStream_t st) {
     if (n > 0) k_h2_angles<<<(n + 255) / 256, 256, 0, st>>>(x2, y2, n, ex, ey, out);
 }
+int pick_angle_bins(int n) {
+    int B = 1 << 12;
+    while (B < 4 * n && B < (1 << 20)) B <<= 1;
+    return B;
+}
+__device__ __forceinline__ int angle_bin(double a, double scale, int B) {   // monotone in a
+    if (a != a) return B;
+    const int b = int(a * scale);
+    return b < 0 ? 0 : (b >= B ? B - 1 : b);
+}
+__global__ void k_h2_hist(const double* __restrict__ ang, int n, AngleIndex ix, int32_t* __restrict__ bin_of) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int b = angle_bin(ang[i], ix.scale, ix.B);
+    bin_of[i] = b;
+    atomicAdd(&ix.bin_end[b], 1);
+}
+__global__ void __launch_bounds__(1024) k_scan_bins1(int32_t* b, int n) {   // in-place exclusive scan, one block
+    __shared__ int part[1024];
+    const int per = (n + 1023) / 1024;
+    const int lo = min(int(threadIdx.x) * per, n), hi = min(lo + per, n);
+    int s = 0;
+    for (int i = lo; i < hi; i++) s += b[i];
+    part[threadIdx.x] = s;
+    __syncthreads();
+    for (int d = 1; d < 1024; d <<= 1) {
+        const int t = (threadIdx.x >= d) ? part[threadIdx.x - d] : 0;
+        __syncthreads();
+        part[threadIdx.x] += t;
+        __syncthreads();
+    }
+    int run = part[threadIdx.x] - s;
+    for (int i = lo; i < hi; i++) { const int c = b[i]; b[i] = run; run += c; }
+}
+__global__ void k_h2_scatter(const double* __restrict__ ang, int n, AngleIndex ix, const int32_t* __restrict__ bin_of) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int p = atomicAdd(&ix.bin_end[bin_of[i]], 1);   // afterwards bin_end[b] = END of bin b
+    ix.ang[p] = ang[i]; ix.idx[p] = i;
+}
+void launch_h2_index(const double* ang2, int n, int32_t* bin_scratch, AngleIndex ix, cudaStream_t st, int* launches) {
+    cudaMemsetAsync(ix.bin_end, 0, size_t(ix.B + 1) * sizeof(int32_t), st);
+    if (n <= 0) return;
+    k_h2_hist<<<(n + 255) / 256, 256, 0, st>>>(ang2, n, ix, bin_scratch);
+    k_scan_bins1<<<1, 1024, 0, st>>>(ix.bin_end, ix.B + 1);
+    k_h2_scatter<<<(n + 255) / 256, 256, 0, st>>>(ang2, n, ix, bin_scratch);
+    if (launches) *launches += 3;
+}
 __global__ void k_h1_wedges(const __grid_constant__ PassConst pc, const double* __restrict__ x1, const double* __restrict__ y1, int n,
                             double2* __restrict__ wedge, int32_t* __restrict__ flag) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -701,16 +749,47 @@ __device__ void cluster_warp_global(int n, const PassConst& pc, const double* xc
 }
 
 // ----------------------------------------------------------------------------- formation
-// One warp per view-1 edge: Skip_this_Edge (hpp:92-110), getHYPO2_idx_Ore (PairEdgeHypo.cpp:88-102) as a
-// ballot-compacted scan over the view-2 angle list (keeps the reference's ascending-index order for free),
-// edgelsHYPO2_epipolar_correction (PairEdgeHypo.cpp:225-293), then clustering.
+// One warp per view-1 edge: Skip_this_Edge (hpp:92-110); getHYPO2_idx_Ore (PairEdgeHypo.cpp:88-102) as a bin-range read of the
+// angle-sorted view-2 index with the reference's exact strict test; edgelsHYPO2_epipolar_correction (PairEdgeHypo.cpp:225-293);
+// then clustering.  Clustering is order dependent, so the fill pass first restores the reference's candidate order
+// (ascending view-2 index) by rank-sorting the gathered candidates in shared memory; edges with more candidates than the
+// shared-memory list holds fall back to the ordered linear scan of the whole angle list.
+#define FORM_CAND_CAP 512
+static_assert(2 * FORM_CAND_CAP * sizeof(int32_t) <= sizeof(ClusterSm<CL_N>), "candidate lists alias the clustering storage");
+
+// processes 32 candidates (lane: view-2 edge i, valid when in) of an ordered candidate stream; returns through mbase / nbase
+template <bool FILL>
+__device__ __forceinline__ void form_chunk(bool in, int i, const double* coef, const PassConst& pc, const double* __restrict__ x2,
+                                           const double* __restrict__ y2, const double* __restrict__ th2, int h1, int n_total, int64_t row0,
+                                           RowTable& rt, unsigned lt, int& mbase, int& nbase) {
+    const unsigned mm = __ballot_sync(FULL, in);
+    if (mm == 0) return;
+    bool ok = false;
+    double cx = 0, cy = 0, t2 = 0;
+    if (in) {
+        t2 = th2[i];
+        ok = correct_one(coef, x2[i], y2[i], t2, pc.loc_pert, pc.tang_thresh, pc.orient_pert, &cx, &cy);
+    }
+    const unsigned mo = __ballot_sync(FULL, ok);
+    if (FILL && in) {
+        const int k = mbase + __popc(mm & lt);                           // pre-correction position (col 9)
+        if (k < n_total) rt.rawat[row0 + k] = i;                         // HYPO2_idx_raw(local row): EdgeClusterer.cpp:221 quirk
+        if (ok) {
+            const int64_t r = row0 + nbase + __popc(mo & lt);
+            rt.h1[r] = h1; rt.h2orig[r] = i; rt.local[r] = k;
+            rt.xc[r] = cx; rt.yc[r] = cy; rt.th[r] = t2;                 // theta written back is the ORIGINAL one (:288)
+        }
+    }
+    mbase += __popc(mm); nbase += __popc(mo);
+}
+
 template <bool FILL>
 __global__ void __launch_bounds__(FORM_WARPS * 32) k_form(const __grid_constant__ PassConst pc, const double* __restrict__ x1,
                                                           const double* __restrict__ y1, int h1_begin, int h1_end,
                                                           const double2* __restrict__ wedge_h1, const double* __restrict__ x2,
                                                           const double* __restrict__ y2, const double* __restrict__ th2,
-                                                          const double* __restrict__ ang2, int E2, int32_t* m_out, int32_t* n_out,
-                                                          const int64_t* __restrict__ row_off, RowTable rt, int32_t* n_clusters) {
+                                                          const double* __restrict__ ang2, int E2, const AngleIndex ix, int32_t* m_out,
+                                                          int32_t* n_out, const int64_t* __restrict__ row_off, RowTable rt, int32_t* n_clusters) {
     extern __shared__ __align__(16) unsigned char form_smem[];
     const int lane = threadIdx.x & 31;
     const int h1 = h1_begin + blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
@@ -718,11 +797,12 @@ __global__ void __launch_bounds__(FORM_WARPS * 32) k_form(const __grid_constant_
     const double x = x1[h1], y = y1[h1];
     const bool skip = (x < 10 || x > double(pc.cols - 10) || y < 10 || y > double(pc.rows - 10));   // hpp:94
     const double2 w = wedge_h1[h1];
-    int n_total = 0;
+    int n_total = 0, m_total = 0;
     int64_t row0 = 0;
     if (FILL) {
         n_total = n_out[h1];
         if (n_total == 0) { if (lane == 0) n_clusters[h1] = 0; return; }
+        m_total = m_out[h1];
         row0 = row_off[h1];
     } else if (skip || w.x != w.x) {
         if (lane == 0) { m_out[h1] = 0; n_out[h1] = 0; }
@@ -732,37 +812,54 @@ __global__ void __launch_bounds__(FORM_WARPS * 32) k_form(const __grid_constant_
     epip_line_coeffs(pc.F21, x, y, coef);
     const unsigned lt = lanemask_lt();
     int mbase = 0, nbase = 0;
-    for (int base = 0; base < E2; base += 32) {
-        const int i = base + lane;
-        bool in = false, ok = false;
-        double cx = 0, cy = 0, t2 = 0;
-        if (i < E2) {
-            const double a = ang2[i];
-            in = (a > w.x && a < w.y);                                       // PairEdgeHypo.cpp:94 (strict both sides)
-        }
-        const unsigned mm = __ballot_sync(FULL, in);
-        if (mm == 0) continue;
-        if (in) {
-            t2 = th2[i];
-            ok = correct_one(coef, x2[i], y2[i], t2, pc.loc_pert, pc.tang_thresh, pc.orient_pert, &cx, &cy);
-        }
-        const unsigned mo = __ballot_sync(FULL, ok);
-        if (FILL) {
-            if (in) {
-                const int k = mbase + __popc(mm & lt);                       // pre-correction position (col 9)
-                if (k < n_total) rt.rawat[row0 + k] = i;                     // HYPO2_idx_raw(local row): EdgeClusterer.cpp:221 quirk
-                if (ok) {
-                    const int64_t r = row0 + nbase + __popc(mo & lt);
-                    rt.h1[r] = h1; rt.h2orig[r] = i; rt.local[r] = k;
-                    rt.xc[r] = cx; rt.yc[r] = cy; rt.th[r] = t2;             // theta written back is the ORIGINAL one (:288)
-                }
-            }
-        }
-        mbase += __popc(mm); nbase += __popc(mo);
-    }
+    // bin range of the wedge in the angle-sorted index (a superset; membership is the exact strict test below)
+    const int b0 = angle_bin(w.x, ix.scale, ix.B), b1 = angle_bin(w.y, ix.scale, ix.B);
+    const int beg = b0 ? ix.bin_end[b0 - 1] : 0, end = ix.bin_end[b1];
     if (!FILL) {
+        // counting needs no order
+        for (int base = beg; base < end; base += 32) {
+            const int j = base + lane;
+            bool in = false;
+            int i = 0;
+            if (j < end) { const double a = ix.ang[j]; in = (a > w.x && a < w.y); i = ix.idx[j]; }   // PairEdgeHypo.cpp:94 (strict both sides)
+            form_chunk<false>(in, i, coef, pc, x2, y2, th2, h1, 0, 0, rt, lt, mbase, nbase);
+        }
         if (lane == 0) { m_out[h1] = mbase; n_out[h1] = nbase; }
         return;
+    }
+    if (m_total <= FORM_CAND_CAP) {
+        // gather (unordered), rank-sort by view-2 index, then the reference's ordered pass over the candidates
+        int32_t* cand = reinterpret_cast<int32_t*>(form_smem + size_t(threadIdx.x >> 5) * sizeof(ClusterSm<CL_N>));
+        int32_t* sorted = cand + FORM_CAND_CAP;
+        int m = 0;
+        for (int base = beg; base < end; base += 32) {
+            const int j = base + lane;
+            bool in = false;
+            if (j < end) { const double a = ix.ang[j]; in = (a > w.x && a < w.y); }
+            const unsigned mm = __ballot_sync(FULL, in);
+            if (in) cand[m + __popc(mm & lt)] = ix.idx[j];
+            m += __popc(mm);
+        }
+        __syncwarp();
+        for (int c = lane; c < m; c += 32) {
+            const int mine = cand[c];
+            int rank = 0;
+            for (int k = 0; k < m; k++) rank += (cand[k] < mine);
+            sorted[rank] = mine;
+        }
+        __syncwarp();
+        for (int base = 0; base < m; base += 32) {
+            const int c = base + lane;
+            const bool in = c < m;
+            form_chunk<true>(in, in ? sorted[c] : 0, coef, pc, x2, y2, th2, h1, n_total, row0, rt, lt, mbase, nbase);
+        }
+    } else {
+        for (int base = 0; base < E2; base += 32) {
+            const int i = base + lane;
+            bool in = false;
+            if (i < E2) { const double a = ang2[i]; in = (a > w.x && a < w.y); }
+            form_chunk<true>(in, i, coef, pc, x2, y2, th2, h1, n_total, row0, rt, lt, mbase, nbase);
+        }
     }
     __syncwarp();
     if (n_total <= CL_N && pc.max_cluster <= 32) {
@@ -776,23 +873,24 @@ __global__ void __launch_bounds__(FORM_WARPS * 32) k_form(const __grid_constant_
     }
 }
 void launch_form_count(const PassConst& pc, const double* x1, const double* y1, int h1_begin, int h1_end, const double2* wedge_h1,
-                       const double* x2, const double* y2, const double* th2, const double* ang2, int E2, int32_t* m_out, int32_t* n_out,
-                       cudaStream_t st) {
+                       const double* x2, const double* y2, const double* th2, const double* ang2, int E2, AngleIndex ix, int32_t* m_out,
+                       int32_t* n_out, cudaStream_t st) {
     const int n = h1_end - h1_begin;
     if (n <= 0) return;
     RowTable rt = {};
-    k_form<false><<<(n + FORM_WARPS - 1) / FORM_WARPS, FORM_WARPS * 32, 0, st>>>(pc, x1, y1, h1_begin, h1_end, wedge_h1, x2, y2, th2, ang2, E2,
+    k_form<false><<<(n + FORM_WARPS - 1) / FORM_WARPS, FORM_WARPS * 32, 0, st>>>(pc, x1, y1, h1_begin, h1_end, wedge_h1, x2, y2, th2, ang2, E2, ix,
                                                                                 m_out, n_out, nullptr, rt, nullptr);
 }
 void launch_form_fill(const PassConst& pc, const double* x1, const double* y1, int h1_begin, int h1_end, const double2* wedge_h1,
-                      const double* x2, const double* y2, const double* th2, const double* ang2, int E2, const int32_t* n_of,
-                      const int64_t* row_off, RowTable rt, int32_t* n_clusters, cudaStream_t st) {
+                      const double* x2, const double* y2, const double* th2, const double* ang2, int E2, AngleIndex ix, const int32_t* m_of,
+                      const int32_t* n_of, const int64_t* row_off, RowTable rt, int32_t* n_clusters, cudaStream_t st) {
     const int n = h1_end - h1_begin;
     if (n <= 0) return;
     const size_t smem = FORM_WARPS * sizeof(ClusterSm<CL_N>);
     cudaFuncSetAttribute(k_form<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));   // per device, cheap
-    k_form<true><<<(n + FORM_WARPS - 1) / FORM_WARPS, FORM_WARPS * 32, smem, st>>>(pc, x1, y1, h1_begin, h1_end, wedge_h1, x2, y2, th2, ang2, E2,
-                                                                                  nullptr, const_cast<int32_t*>(n_of), row_off, rt, n_clusters);
+    k_form<true><<<(n + FORM_WARPS - 1) / FORM_WARPS, FORM_WARPS * 32, smem, st>>>(pc, x1, y1, h1_begin, h1_end, wedge_h1, x2, y2, th2, ang2, E2, ix,
+                                                                                  const_cast<int32_t*>(m_of), const_cast<int32_t*>(n_of), row_off, rt,
+                                                                                  n_clusters);
 }
 
 // ----------------------------------------------------------------------------- unique-hypothesis table
@@ -853,28 +951,40 @@ void launch_wedge31(const PassConst& pc, const ViewConst* vc, const double* x1, 
 //   index order == maximum, ties to the lowest index).  Threads of a warp are consecutive hypotheses of (mostly) one view-1
 //   edge and one view: they share wedge31 and hit neighbouring cells.  Queries that overlap many cells or long cells (wedges
 //   that wrap around 0/180 degrees, epipole inside the image: SURVEY.md a3) are walked by the whole warp instead of one lane.
-#define VAL_THREADS 128
+#ifndef VAL_THREADS
+#define VAL_THREADS 256
+#endif
+#ifndef VAL_BATCH
+#define VAL_BATCH 2           // entries a lane loads per step of its walk (independent loads in flight)
+#endif
+#ifndef VAL_MIN_BLOCKS
+#define VAL_MIN_BLOCKS 4      // 64 registers: the kernel is latency bound, occupancy beats a deeper batch (profiles/r01f_variants.txt)
+#endif
 #define VAL_LIGHT_ROWS 4       // row ranges a lane keeps in registers
-#define VAL_COOP_MIN 96        // a query becomes a whole-warp job when its work exceeds this and 4x the warp's mean
+#define VAL_COOP_MIN 32        // a query becomes a whole-warp job when its work exceeds this and VAL_COOP_RATIO x the warp's mean
+#define VAL_COOP_RATIO 2
 struct SupportAcc {
     double best;   // prev_prod, getSupportedEdgels.cpp:33
-    int bidx;
+    int bj;        // position (in the walked layout) of the best entry so far, -1 = none
     unsigned n_in, n_vis;
 };
+// One candidate entry.  The edge index is only needed to break exact ties (equal |t . t^|: the reference keeps the first in
+// ascending index order), so it is not loaded on the common path: the walk carries the POSITION of the best entry.
 __device__ __forceinline__ void support_visit(SupportAcc& s, const double4 e, int j, const double2 w1, const double2 w2, const double2 tg,
                                               double thr, const int32_t* __restrict__ idx_) {
     s.n_vis++;
     if (e.x > w1.x && e.x < w1.y && e.y > w2.x && e.y < w2.y) {          // PairEdgeHypo.cpp:94, both wedges
         s.n_in++;
         const double d = fabs(tg.x * e.z + tg.y * e.w);                   // getSupportedEdgels.cpp:38
-        if (d >= thr && d >= s.best) {
-            const int idx = idx_[j];
-            if (d > s.best || (s.bidx != -2 && idx < s.bidx)) { s.best = d; s.bidx = idx; }
+        if (d >= thr) {
+            if (d > s.best) { s.best = d; s.bj = j; }
+            else if (d == s.best && s.bj >= 0 && idx_[j] < idx_[s.bj]) s.bj = j;
         }
     }
 }
+// GIVEN: wedge32 / tangent are inputs (stand-alone support test on pre-formed hypotheses).
 template <bool GIVEN>
-__global__ void __launch_bounds__(VAL_THREADS) k_validate(const __grid_constant__ PassConst pc, const __grid_constant__ ValidateArgs a) {
+__global__ void __launch_bounds__(VAL_THREADS, VAL_MIN_BLOCKS) k_validate(const __grid_constant__ PassConst pc, const __grid_constant__ ValidateArgs a) {
     const int64_t u = blockIdx.x * int64_t(VAL_THREADS) + threadIdx.x;
     const int v = blockIdx.y;
     const int lane = threadIdx.x & 31;
@@ -883,7 +993,7 @@ __global__ void __launch_bounds__(VAL_THREADS) k_validate(const __grid_constant_
     bool active = false;
     if (u < a.U) {
         const int h1 = a.ut.h1[u];
-        mult = GIVEN ? 1ULL : (unsigned long long)a.ut.mult[u];
+        mult = a.ut.mult ? (unsigned long long)a.ut.mult[u] : 1ULL;
         w1 = a.w31[int64_t(v) * a.w31_stride + h1];
         if (GIVEN) {
             w2 = a.w32_in[int64_t(v) * a.U + u];
@@ -912,7 +1022,7 @@ __global__ void __launch_bounds__(VAL_THREADS) k_validate(const __grid_constant_
     const ViewGrid vg = a.gi.vg[v];
     const int64_t off = a.edge_off[a.vali_view ? a.vali_view[v] : v];
     const int64_t ce_off = int64_t(v) * a.gi.CS;
-    SupportAcc acc = {0.0, -2, 0u, 0u};
+    SupportAcc acc = {0.0, -1, 0u, 0u};
     int r0 = 0, r1 = -1, c0 = 0, c1 = 0, work = 0, G = 1;
     int beg[VAL_LIGHT_ROWS], end[VAL_LIGHT_ROWS];
     bool useB = false;
@@ -945,15 +1055,29 @@ __global__ void __launch_bounds__(VAL_THREADS) k_validate(const __grid_constant_
     int wsum = work, wcnt = active ? 1 : 0;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) { wsum += __shfl_xor_sync(FULL, wsum, o); wcnt += __shfl_xor_sync(FULL, wcnt, o); }
-    const bool heavy = active && work > VAL_COOP_MIN && work * max(wcnt, 1) > 4 * wsum;
+    const bool heavy = active && work > VAL_COOP_MIN && work * max(wcnt, 1) > VAL_COOP_RATIO * wsum;
     if (active && !heavy) {
         const GridLayout& L = useB ? a.gi.B : a.gi.A;
         const double4* __restrict__ rec = L.rec + off;
         const int32_t* __restrict__ idx_ = L.idx + off;
         if (r1 - r0 < VAL_LIGHT_ROWS) {
+            // the (at most VAL_LIGHT_ROWS) ranges are walked as one flattened list, VAL_BATCH entries per step, so that several
+            // independent 32-byte loads are in flight per lane instead of one (the walk is latency bound)
+            const int l0 = end[0] - beg[0], l1 = l0 + (end[1] - beg[1]), l2 = l1 + (end[2] - beg[2]);
+            for (int k = 0; k < work; k += VAL_BATCH) {
+                int j[VAL_BATCH];
+                double4 e[VAL_BATCH];
 #pragma unroll
-            for (int r = 0; r < VAL_LIGHT_ROWS; r++)
-                for (int j = beg[r]; j < end[r]; j++) support_visit(acc, rec[j], j, w1, w2, tg, a.cos_thresh, idx_);
+                for (int t = 0; t < VAL_BATCH; t++) {
+                    const int kk = min(k + t, work - 1);
+                    j[t] = kk < l0 ? beg[0] + kk : kk < l1 ? beg[1] + (kk - l0) : kk < l2 ? beg[2] + (kk - l1) : beg[3] + (kk - l2);
+                }
+#pragma unroll
+                for (int t = 0; t < VAL_BATCH; t++) e[t] = rec[j[t]];
+#pragma unroll
+                for (int t = 0; t < VAL_BATCH; t++)
+                    if (t == 0 || k + t < work) support_visit(acc, e[t], j[t], w1, w2, tg, a.cos_thresh, idx_);
+            }
         } else {
             const int32_t* __restrict__ ce = L.cell_end + ce_off;
             for (int b = r0; b <= r1; b++) {
@@ -964,6 +1088,7 @@ __global__ void __launch_bounds__(VAL_THREADS) k_validate(const __grid_constant_
         }
     }
     // ---- warp-cooperative walk of the heavy queries, one at a time
+    int bidx = -2;
     unsigned hm = __ballot_sync(FULL, heavy);
     while (hm) {
         const int src = __ffs(hm) - 1;
@@ -979,7 +1104,7 @@ __global__ void __launch_bounds__(VAL_THREADS) k_validate(const __grid_constant_
         const double4* __restrict__ rec = L.rec + off;
         const int32_t* __restrict__ idx_ = L.idx + off;
         const int32_t* __restrict__ ce = L.cell_end + ce_off;
-        SupportAcc ca = {0.0, -2, 0u, 0u};
+        SupportAcc ca = {0.0, -1, 0u, 0u};
         if (sr1 - sr0 + 1 >= 8) {                       // many rows: one lane per row
             for (int b = sr0 + lane; b <= sr1; b += 32) {
                 const int cc = b * sG + sc0;
@@ -993,19 +1118,21 @@ __global__ void __launch_bounds__(VAL_THREADS) k_validate(const __grid_constant_
                 for (int j = jb + lane; j < je; j += 32) support_visit(ca, rec[j], j, sw1, sw2, stg, a.cos_thresh, idx_);
             }
         }
+        int ci = ca.bj >= 0 ? idx_[ca.bj] : -2;         // edge index of the lane's best
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {              // maximum, ties to the lowest edge index
             const double od = __shfl_xor_sync(FULL, ca.best, o);
-            const int oi = __shfl_xor_sync(FULL, ca.bidx, o);
+            const int oi = __shfl_xor_sync(FULL, ci, o);
             ca.n_in += __shfl_xor_sync(FULL, ca.n_in, o); ca.n_vis += __shfl_xor_sync(FULL, ca.n_vis, o);
-            if (oi != -2 && (ca.bidx == -2 || od > ca.best || (od == ca.best && oi < ca.bidx))) { ca.best = od; ca.bidx = oi; }
+            if (oi != -2 && (ci == -2 || od > ca.best || (od == ca.best && oi < ci))) { ca.best = od; ci = oi; }
         }
-        if (lane == src) { acc = ca; c_hvy = 1; }
+        if (lane == src) { acc = ca; bidx = ci; c_hvy = 1; }
     }
+    if (active && !heavy && acc.bj >= 0) bidx = ((useB ? a.gi.B.idx : a.gi.A.idx) + off)[acc.bj];
     if (u < a.U) {
         c_inl = mult * acc.n_in; c_vis = acc.n_vis;
-        if (acc.bidx != -2) c_sup = mult;
-        a.support[int64_t(v) * a.sup_stride + u] = acc.bidx;
+        if (bidx != -2) c_sup = mult;
+        a.support[int64_t(v) * a.sup_stride + u] = bidx;
     }
     if (a.ctr == nullptr) return;
     // warp-aggregated statistics -> one counter slot per warp (no block barrier: warps retire independently)

@@ -85,15 +85,25 @@ void launch_stage_given(const double* a31, const double* a32, const double* cs, 
                         int64_t max_edges, int32_t* cell, GridIndex gi, const GridSample& gs, int32_t* scan_tmp, cudaStream_t st, int* launches);
 
 void launch_h2_angles(const double* x2, const double* y2, int n, double ex, double ey, double* out, cudaStream_t st);
+// The view-2 edges counting-sorted by the bin of their epipolar angle (B uniform bins over [0,180], bin B = NaN):
+// the candidate search of a view-1 edge (getHYPO2_idx_Ore, PairEdgeHypo.cpp:88-102) reads one bin range instead of all of view 2.
+struct AngleIndex {
+    double* ang;        // sorted angles
+    int32_t* idx;       // original view-2 edge index
+    int32_t* bin_end;   // [B + 1] END (exclusive) of every bin
+    int32_t B; double scale;   // scale = B / 180
+};
+int pick_angle_bins(int n);   // B for n edges
+void launch_h2_index(const double* ang2, int n, int32_t* bin_scratch, AngleIndex ix, cudaStream_t st, int* launches);
 void launch_h1_wedges(const PassConst& pc, const double* x1, const double* y1, int n, double2* wedge, int32_t* flag, cudaStream_t st);
 
 // formation: count pass (m, n per view-1 edge) and fill pass (rows + clustering + per-edge cluster count)
 void launch_form_count(const PassConst& pc, const double* x1, const double* y1, int h1_begin, int h1_end, const double2* wedge_h1,
-                       const double* x2, const double* y2, const double* th2, const double* ang2, int E2, int32_t* m_out,
+                       const double* x2, const double* y2, const double* th2, const double* ang2, int E2, AngleIndex ix, int32_t* m_out,
                        int32_t* n_out, cudaStream_t st);
 void launch_form_fill(const PassConst& pc, const double* x1, const double* y1, int h1_begin, int h1_end, const double2* wedge_h1,
-                      const double* x2, const double* y2, const double* th2, const double* ang2, int E2, const int32_t* n_of,
-                      const int64_t* row_off, RowTable rt, int32_t* n_clusters, cudaStream_t st);
+                      const double* x2, const double* y2, const double* th2, const double* ang2, int E2, AngleIndex ix, const int32_t* m_of,
+                      const int32_t* n_of, const int64_t* row_off, RowTable rt, int32_t* n_clusters, cudaStream_t st);
 // unique-hypothesis table from the clustered rows (+ view-independent reprojection terms)
 void launch_uniq_fill(const PassConst& pc, const double* x1, const double* y1, const double* th1, RowTable rt, int64_t H,
                       const int64_t* row_off, const int64_t* u_off, UniqTable ut, cudaStream_t st);

@@ -66,9 +66,30 @@ CVX_HD void cross3(const double* a, const double* b, double* c) {
     c[2] = a[0] * b[1] - a[1] * b[0];
 }
 CVX_HD double norm3(const double* a) { return sqrt((a[0] * a[0] + a[1] * a[1]) + a[2] * a[2]); }
+// The libdevice FP64 transcendentals are ~100-200 instructions each; wedge_row alone calls atan seven times.  One shared
+// out-of-line copy per function keeps the validation kernel's code footprint inside the instruction cache.
+#if defined(__CUDACC__)
+static __device__ __noinline__ double cvx_atan_dev(double x) { return atan(x); }
+static __device__ __noinline__ double cvx_cos_dev(double x) { return cos(x); }
+static __device__ __noinline__ void cvx_sincos_dev(double a, double* s, double* c) { sincos(a, s, c); }
+#endif
+CVX_HD double cvx_atan(double x) {
+#if defined(__CUDA_ARCH__)
+    return cvx_atan_dev(x);
+#else
+    return atan(x);
+#endif
+}
+CVX_HD double cvx_cos(double x) {
+#if defined(__CUDA_ARCH__)
+    return cvx_cos_dev(x);
+#else
+    return cos(x);
+#endif
+}
 CVX_HD void sincos_d(double a, double* s, double* c) {
 #if defined(__CUDA_ARCH__)
-    sincos(a, s, c);
+    cvx_sincos_dev(a, s, c);
 #else
     *s = sin(a); *c = cos(a);
 #endif
@@ -76,7 +97,7 @@ CVX_HD void sincos_d(double a, double* s, double* c) {
 
 // ---- epipolar angle of an edge about an epipole: getOrientationList.cpp:391-461 (getOreList / getOreListVali)
 CVX_HD double ore_angle(double x, double y, double ex, double ey) {
-    const double a = atan((y - ey) / (x - ex));
+    const double a = cvx_atan((y - ey) / (x - ex));
     double deg = (a * 180) / M_PI;
     if (deg < 0) deg = deg + 180;
     return deg;
@@ -104,7 +125,7 @@ CVX_HD bool wedge_border_point(double A, double B, double C, int rows, int cols,
     return true;
 }
 CVX_HD void wedge_border_slopes(double px, double py, double ore_deg, double e2x, double e2y, double delta, int cols, double* sp, double* sn) {
-    const double dlt = fabs(cos(ore_deg / 180 * M_PI) * delta);   // :243
+    const double dlt = fabs(cvx_cos(ore_deg / 180 * M_PI) * delta);   // :243
     double slope_p, slope_n;
     if (px == 0 || px == double(cols)) {                          // :246 vertical border: shift in y
         const double fdx = px - e2x;
@@ -115,8 +136,8 @@ CVX_HD void wedge_border_slopes(double px, double py, double ore_deg, double e2x
         slope_p = fdy / (px - e2x - dlt);
         slope_n = fdy / (px - e2x + dlt);
     }
-    *sp = atan(slope_p) / M_PI * 180;
-    *sn = atan(slope_n) / M_PI * 180;
+    *sp = cvx_atan(slope_p) / M_PI * 180;
+    *sn = cvx_atan(slope_n) / M_PI * 180;
 }
 // returns flag (0 = ok; bit0/bit1: line 1/2 crosses != 2 borders; bit2: NaN) and writes lo/hi (NaN when flagged)
 CVX_HD int wedge_row(double x, double y, const double* F, double e1x, double e1y, double e2x, double e2y, double delta, int rows,
@@ -124,7 +145,7 @@ CVX_HD int wedge_row(double x, double y, const double* F, double e1x, double e1y
     const double dy = y - e1y, dx = x - e1x;                      // :54-55
     const double d12 = sqrt((dy * dy + dx * dx) - delta * delta); // :58-60
     const double th = asin(delta / d12);                          // :62
-    const double ang = atan(dy / dx);                             // :57,63
+    const double ang = cvx_atan(dy / dx);                             // :57,63
     double s1, c1, s2, c2;
     sincos_d(ang + th, &s1, &c1);                                 // :66,73-74
     sincos_d(ang - th, &s2, &c2);                                 // :67,75-76
@@ -134,8 +155,8 @@ CVX_HD int wedge_row(double x, double y, const double* F, double e1x, double e1y
     const double p1x = dx1 + e1x, p1y = dy1 + e1y, p2x = dx2 + e1x, p2y = dy2 + e1y;   // :102-106
     const double A1 = (F[0] * p1x + F[1] * p1y) + F[2], B1 = (F[3] * p1x + F[4] * p1y) + F[5], C1 = (F[6] * p1x + F[7] * p1y) + F[8];  // :109
     const double A2 = (F[0] * p2x + F[1] * p2y) + F[2], B2 = (F[3] * p2x + F[4] * p2y) + F[5], C2 = (F[6] * p2x + F[7] * p2y) + F[8];  // :115
-    double ore1 = atan(B1 / A1) / M_PI * 180;                     // :121
-    double ore2 = atan(B2 / A2) / M_PI * 180;                     // :124
+    double ore1 = cvx_atan(B1 / A1) / M_PI * 180;                     // :121
+    double ore2 = cvx_atan(B2 / A2) / M_PI * 180;                     // :124
     if (ore1 < 0) ore1 = ore1 + 180;                              // :128
     if (ore2 < 0) ore2 = ore2 + 180;                              // :132
     const double ore_lo = (ore1 < ore2) ? ore1 : ore2, ore_hi = (ore1 < ore2) ? ore2 : ore1;   // :135-139

@@ -4,7 +4,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 api = importlib.import_module("3d_curvix_b200.api"); data = importlib.import_module("3d_curvix_b200.data")
 w = data.workload(sys.argv[1] if len(sys.argv) > 1 else "cfg2")
 scene = data.make_synthetic_scene(**w["scene"])
-for f in (4, 16, 64):
+for f in [int(x) for x in os.environ.get("SWEEP", "16").split(",")]:
     os.environ["CVX_GRID_CELLS_PER_EDGE"] = str(f)
     cfg = api.default_config(n_views=scene.n_views, img_rows=scene.rows, img_cols=scene.cols, max_support_views=w["max_support_views"])
     g = api.EdgeSketch(cfg, 0)
