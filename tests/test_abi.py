@@ -29,7 +29,7 @@ def test_library_exports_every_declared_symbol():
 def test_struct_layouts_match_header():
     api = pkg("api")
     assert C.sizeof(api.CvxConfig) == 11 * 8 + 6 * 4
-    assert C.sizeof(api.CvxCounts) == 12 * 8
+    assert C.sizeof(api.CvxCounts) == 14 * 8
     assert C.sizeof(api.CvxTimings) == 7 * 4 + 2 * 4
     cfg = api.default_config()
     assert (cfg.delta, cfg.delta_theta_deg, cfg.lowes_ratio, cfg.pi_truncated) == (0.4, 15.0, 0.6, 3.1415926)
