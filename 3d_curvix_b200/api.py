@@ -12,12 +12,13 @@ LIB_PATH = os.environ.get("CVX_LIB_PATH") or os.path.join(_HERE, "libcurvix_b200
 
 # every symbol include/curvix_b200.h declares
 SYMBOLS = [
-    "cvx_default_config", "cvx_create", "cvx_destroy", "cvx_last_error", "cvx_set_cameras", "cvx_set_view_edges",
+    "cvx_default_config", "cvx_create", "cvx_destroy", "cvx_last_error", "cvx_set_cameras", "cvx_set_view_edges", "cvx_set_all_view_edges",
     "cvx_set_hypothesis_pair", "cvx_run_edge_sketch", "cvx_get_counts", "cvx_get_h2_angles", "cvx_get_h1_wedges",
     "cvx_get_h1_table", "cvx_get_rows", "cvx_get_support_matrix", "cvx_set_keep_intermediates", "cvx_get_intermediates", "cvx_get_valid_rows",
     "cvx_get_pairs", "cvx_get_reference_order", "cvx_finalize", "cvx_get_device_results", "cvx_get_timings", "cvx_synchronize", "cvx_get_stream",
     "cvx_claims_reset", "cvx_claims_accumulate", "cvx_claims_get_counts", "cvx_claims_get_mask",
-    "cvx_support_problem_create", "cvx_support_problem_run", "cvx_support_problem_result", "cvx_support_problem_destroy",
+    "cvx_support_problem_create", "cvx_support_problem_run", "cvx_support_problem_stats", "cvx_support_problem_result",
+    "cvx_support_problem_destroy",
 ]
 
 
@@ -74,6 +75,12 @@ def load():
     lib.cvx_create.argtypes = [C.POINTER(CvxConfig), C.c_int, C.POINTER(C.c_void_p)]
     lib.cvx_support_problem_create.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p] + [C.c_void_p] * 7 + \
         [C.c_double, C.c_double, C.POINTER(C.c_void_p)]
+    for f in ("cvx_support_problem_run", "cvx_support_problem_stats", "cvx_support_problem_result", "cvx_support_problem_destroy"):
+        getattr(lib, f).argtypes = None
+    lib.cvx_support_problem_run.argtypes = [C.c_void_p, C.POINTER(C.c_float)]
+    lib.cvx_support_problem_stats.argtypes = [C.c_void_p] + [C.POINTER(C.c_int64)] * 4
+    lib.cvx_support_problem_result.argtypes = [C.c_void_p, C.c_void_p]
+    lib.cvx_support_problem_destroy.argtypes = [C.c_void_p]
     _lib = lib
     return lib
 
@@ -145,6 +152,19 @@ class EdgeSketch:
     def set_view_edges_ptr(self, v, n, px, py, pth):
         self._ck(self.lib.cvx_set_view_edges(self.h, v, n, C.c_void_p(px), C.c_void_p(py), C.c_void_p(pth), None))
         self.n_edges[v] = n
+
+    def set_all_view_edges(self, edges):
+        """edges: list (one per view) of E x >=3 arrays [x y theta ...]; one packed upload for all views."""
+        n = np.array([len(e) for e in edges], np.int32)
+        cat = np.concatenate([np.asarray(e, np.float64)[:, :3] for e in edges], axis=0) if n.sum() else np.zeros((0, 3))
+        cols = [np.ascontiguousarray(cat[:, k]) for k in range(3)]
+        self.set_all_view_edges_ptr(n, cols[0].ctypes.data, cols[1].ctypes.data, cols[2].ctypes.data)
+
+    def set_all_view_edges_ptr(self, n, px, py, pth):
+        """n: int32 array of per-view edge counts; px/py/pth: raw host pointers to the packed columns (may be pinned)."""
+        n = np.ascontiguousarray(n, np.int32)
+        self._ck(self.lib.cvx_set_all_view_edges(self.h, len(n), _vp(n), C.c_void_p(px), C.c_void_p(py), C.c_void_p(pth)))
+        self.n_edges = [int(k) for k in n]
 
     def set_pair(self, h1, h2):
         self._ck(self.lib.cvx_set_hypothesis_pair(self.h, h1, h2))
@@ -222,6 +242,13 @@ class EdgeSketch:
         self._ck(self.lib.cvx_get_valid_rows(self.h, _vp(a["h1"]), _vp(a["row"]), _vp(a["count"]), _vp(a["selected"])))
         return a
 
+    def results_into(self, ptrs):
+        """Accepted pairs + supports + 3-D edges + tangents into caller-owned host buffers (raw pointers, e.g. pinned memory sized for
+        n_pairs): ptrs = dict with any of h1, h2rep, row, count, supports, gamma_cam, gamma_world, tangent_world, h2_corrected, nan_flag."""
+        q = lambda k: C.c_void_p(ptrs[k]) if ptrs.get(k) else None
+        self._ck(self.lib.cvx_get_pairs(self.h, q("h1"), q("h2rep"), q("row"), q("count"), q("supports")))
+        self._ck(self.lib.cvx_finalize(self.h, q("gamma_cam"), q("gamma_world"), q("tangent_world"), q("h2_corrected"), q("nan_flag")))
+
     def pairs(self, with_supports=True):
         P = self.counts()["n_pairs"]
         a = {k: np.empty(P, np.int32) for k in ("h1", "h2rep", "row", "count")}
@@ -285,6 +312,11 @@ class SupportProblem:
         ms = C.c_float()
         self.sk._ck(self.lib.cvx_support_problem_run(self.p, C.byref(ms)))
         return ms.value
+
+    def stats(self):
+        v = [C.c_int64() for _ in range(4)]
+        self.sk._ck(self.lib.cvx_support_problem_stats(self.p, *[C.byref(x) for x in v]))
+        return dict(zip(("n_inliers", "n_visited", "n_supported", "n_parallel"), (int(x.value) for x in v)))
 
     def result(self):
         out = np.empty((self.V, self.H), np.int32)

@@ -139,6 +139,10 @@ struct cvx_ctx {
     bool keep_inter = false, have_inter = false;   // wedge32 / tangent of every (unique hypothesis, view): parity debugging only
     DevBuf<int32_t> d_support, d_support_t;
     DevBuf<DevCounters> d_ctr;
+    DevBuf<int32_t> d_big_list;
+    DevBuf<double> d_ingest;            // cvx_set_all_view_edges: packed columns before the scatter into the arena slots
+    DevBuf<int64_t> d_ingest_tab;
+    std::vector<int64_t> h_ingest_tab;
     DevBuf<int32_t> v_h1, v_row, v_count, v_sel, p_h1, p_h2rep, p_row, p_count, p_sup, f_nan;
     DevBuf<double> f_gc, f_gw, f_tw, f_h2c;
     std::vector<int64_t> h_row_off;
@@ -301,7 +305,7 @@ int cvx_destroy(cvx_ctx* ctx) {
     for (auto* b : db) b->release();
     DevBuf<double2>* d2[] = {&ctx->d_wedge_h1, &ctx->u_xy, &ctx->d_w31, &ctx->d_w32, &ctx->d_tgt};
     for (auto* b : d2) b->release();
-    ctx->u_geom.release(); ctx->d_vc.release(); ctx->d_ctr.release(); ctx->d_vg.release(); ctx->d_minmax.release();
+    ctx->u_geom.release(); ctx->d_vc.release(); ctx->d_ctr.release(); ctx->d_big_list.release(); ctx->d_ingest.release(); ctx->d_ingest_tab.release(); ctx->d_vg.release(); ctx->d_minmax.release();
     if (ctx->d_claim) cudaFree(ctx->d_claim);
     ctx->d_claim_cnt.release(); ctx->d_claim_mask.release();
     for (auto& e : ctx->ev) cudaEventDestroy(e);
@@ -349,6 +353,49 @@ int cvx_set_view_edges(cvx_ctx* ctx, int view, int n, const double* x, const dou
         ctx->tm.kernel_launches++;
     }
     ctx->have_run = false;
+    return CVX_OK;
+}
+
+int cvx_set_all_view_edges(cvx_ctx* ctx, int n_views, const int32_t* n, const double* x, const double* y, const double* theta) {
+    if (!ctx || n_views != ctx->n_views || !n) return fail(ctx, CVX_ERR_INVALID, "cvx_set_all_view_edges: bad arguments (n_views must equal cfg.n_views)");
+    CU(cudaSetDevice(ctx->device));
+    int64_t total = 0, max_n = 0;
+    for (int v = 0; v < n_views; v++) {
+        if (n[v] < 0) return fail(ctx, CVX_ERR_INVALID, "cvx_set_all_view_edges: negative edge count");
+        total += n[v]; max_n = std::max<int64_t>(max_n, n[v]);
+    }
+    if (total > 0 && (!x || !y || !theta)) return fail(ctx, CVX_ERR_INVALID, "cvx_set_all_view_edges: null column");
+    // arena slots first (growing moves the arena: do it before any pointer is taken)
+    for (int v = 0; v < n_views; v++) {
+        if (n[v] > ctx->edge_cap[v]) {
+            const size_t slot = (size_t(n[v]) + 31) & ~size_t(31);
+            const int rc = grow_arena(ctx, ctx->arena_used + slot);
+            if (rc) return rc;
+            ctx->edge_off[v] = int64_t(ctx->arena_used);
+            ctx->edge_cap[v] = int32_t(slot);
+            ctx->arena_used += slot;
+        }
+        ctx->edge_n[v] = n[v];
+    }
+    ctx->tables_dirty = true; ctx->have_run = false;
+    cudaStream_t st = ctx->stream;
+    if (ctx->d_claim) CU(cudaMemsetAsync(ctx->d_claim, 0, ctx->claim_words * 4, st));   // every view is new: no claim survives
+    if (total == 0) return CVX_OK;
+    CU(ctx->d_ingest.reserve(size_t(3) * size_t(total)));
+    CU(ctx->d_ingest_tab.reserve(size_t(3) * n_views));
+    std::vector<int64_t>& tab = ctx->h_ingest_tab;
+    CU(cudaStreamSynchronize(st));            // tab may still be the source of the previous call's copy
+    tab.assign(size_t(3) * n_views, 0);
+    int64_t acc = 0;
+    for (int v = 0; v < n_views; v++) { tab[v] = acc; tab[n_views + v] = ctx->edge_off[v]; tab[2 * n_views + v] = n[v]; acc += n[v]; }
+    double* sx = ctx->d_ingest.p; double* sy = sx + total; double* sth = sy + total;
+    CU(cudaMemcpyAsync(ctx->d_ingest_tab.p, tab.data(), tab.size() * 8, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(sx, x, size_t(total) * 8, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(sy, y, size_t(total) * 8, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(sth, theta, size_t(total) * 8, cudaMemcpyHostToDevice, st));
+    launch_ingest_views(sx, sy, sth, ctx->d_ingest_tab.p, n_views, max_n, ctx->ea, st);
+    ctx->tm.kernel_launches++;
+    CU(cudaGetLastError());
     return CVX_OK;
 }
 
@@ -462,6 +509,8 @@ int cvx_run_edge_sketch(cvx_ctx* ctx, int h1_begin, int h1_end) {
     CU(cudaMemsetAsync(ctx->d_m.p, 0, E1a * 4, st)); CU(cudaMemsetAsync(ctx->d_n.p, 0, E1a * 4, st)); CU(cudaMemsetAsync(ctx->d_ncl.p, 0, E1a * 4, st));
     CU(cudaMemsetAsync(ctx->d_nvalid.p, 0, E1a * 4, st)); CU(cudaMemsetAsync(ctx->d_nsel.p, 0, E1a * 4, st));
     CU(cudaMemsetAsync(ctx->d_ctr.p, 0, sizeof(DevCounters), st));
+    CU(ctx->d_big_list.reserve(size_t(E1a) + 1));                     // queue of view-1 edges for k_cluster_big + its counter
+    CU(cudaMemsetAsync(ctx->d_big_list.p + E1a, 0, 4, st));
     cudaEventRecord(ctx->ev[0], st);
     // ---- hypothesis formation
     launch_form_count(pc, x1, y1, h1_begin, h1_end, ctx->d_wedge_h1.p, x2, y2, th2, ctx->d_ang2.p, E2, ctx->h2ix, ctx->d_m.p, ctx->d_n.p, st);
@@ -480,9 +529,9 @@ int cvx_run_edge_sketch(cvx_ctx* ctx, int h1_begin, int h1_end) {
     for (auto* b : db) CU(b->reserve(Ha));
     RowTable rt = row_table(ctx);
     launch_form_fill(pc, x1, y1, h1_begin, h1_end, ctx->d_wedge_h1.p, x2, y2, th2, ctx->d_ang2.p, E2, ctx->h2ix, ctx->d_m.p, ctx->d_n.p, ctx->d_row_off.p, rt,
-                     ctx->d_ncl.p, st);
+                     ctx->d_ncl.p, ctx->d_big_list.p, ctx->d_big_list.p + E1a, st);
     launch_scan_i32_i64(ctx->d_ncl.p, ctx->d_u_off.p, E1, st);
-    ctx->tm.kernel_launches += 2;
+    ctx->tm.kernel_launches += 3;
     cudaEventRecord(ctx->ev[1], st);
     int64_t U = 0;
     CU(cudaMemcpyAsync(&U, ctx->d_u_off.p + E1, 8, cudaMemcpyDeviceToHost, st));
@@ -574,6 +623,8 @@ int cvx_get_counts(cvx_ctx* ctx, cvx_counts* out) {
     return CVX_OK;
 }
 
+#define D2HA(dst, src, n, T)                                                                                      \
+    do { if ((dst) && (n) > 0) CU(cudaMemcpyAsync((dst), (src), size_t(n) * sizeof(T), cudaMemcpyDeviceToHost, ctx->stream)); } while (0)
 #define D2H(dst, src, n, T)                                                                                       \
     do { if ((dst) && (n) > 0) CU(cudaMemcpy((dst), (src), size_t(n) * sizeof(T), cudaMemcpyDeviceToHost)); } while (0)
 
@@ -669,8 +720,10 @@ int cvx_get_pairs(cvx_ctx* ctx, int32_t* h1, int32_t* h2rep, int32_t* row, int32
     if (!ctx || !ctx->have_run) return fail(ctx, CVX_ERR_INVALID, "no run");
     CU(cudaSetDevice(ctx->device));
     const int64_t P = ctx->P;
-    D2H(h1, ctx->p_h1.p, P, int32_t); D2H(h2rep, ctx->p_h2rep.p, P, int32_t); D2H(row, ctx->p_row.p, P, int32_t);
-    D2H(count, ctx->p_count.p, P, int32_t); D2H(supports, ctx->p_sup.p, P * ctx->n_vali, int32_t);
+    // asynchronous copies + one synchronize: pinned destinations stream at link speed, pageable ones behave as before
+    D2HA(h1, ctx->p_h1.p, P, int32_t); D2HA(h2rep, ctx->p_h2rep.p, P, int32_t); D2HA(row, ctx->p_row.p, P, int32_t);
+    D2HA(count, ctx->p_count.p, P, int32_t); D2HA(supports, ctx->p_sup.p, P * ctx->n_vali, int32_t);
+    CU(cudaStreamSynchronize(ctx->stream));
     return CVX_OK;
 }
 
@@ -725,8 +778,9 @@ int cvx_finalize(cvx_ctx* ctx, double* gamma_cam, double* gamma_world, double* t
     const int rc = run_finalize(ctx);
     if (rc) return rc;
     const int64_t P = ctx->P;
-    D2H(gamma_cam, ctx->f_gc.p, P * 3, double); D2H(gamma_world, ctx->f_gw.p, P * 3, double); D2H(tangent_world, ctx->f_tw.p, P * 3, double);
-    D2H(h2_corrected_xy, ctx->f_h2c.p, P * 2, double); D2H(nan_flag, ctx->f_nan.p, P, int32_t);
+    D2HA(gamma_cam, ctx->f_gc.p, P * 3, double); D2HA(gamma_world, ctx->f_gw.p, P * 3, double); D2HA(tangent_world, ctx->f_tw.p, P * 3, double);
+    D2HA(h2_corrected_xy, ctx->f_h2c.p, P * 2, double); D2HA(nan_flag, ctx->f_nan.p, P, int32_t);
+    CU(cudaStreamSynchronize(ctx->stream));
     return CVX_OK;
 }
 
@@ -890,6 +944,33 @@ int cvx_support_problem_run(cvx_support_problem* p, float* kernel_ms) {
     float ms = 0;
     cudaEventElapsedTime(&ms, p->e0, p->e1);
     if (kernel_ms) *kernel_ms = ms;
+    return CVX_OK;
+}
+int cvx_support_problem_stats(cvx_support_problem* p, int64_t* n_inliers, int64_t* n_visited, int64_t* n_supported, int64_t* n_parallel) {
+    if (!p) return CVX_ERR_INVALID;
+    cvx_ctx* ctx = p->ctx;
+    CU(cudaSetDevice(ctx->device));
+    ValidateArgs a;
+    std::memset(&a, 0, sizeof(a));
+    a.ut.h1 = p->row_group.p; a.U = p->H; a.w31 = p->w31.p; a.w31_stride = p->G; a.w32_in = p->w32.p; a.tgt_in = p->tgt.p;
+    a.vali_view = nullptr; a.edge_off = p->view_off.p; a.gi = p->gi;
+    a.cos_thresh = p->thr; a.parallel_deg = p->par; a.n_vali = p->V;
+    a.support = p->support.p; a.sup_stride = std::max<int64_t>(p->H, 1); a.ctr = ctx->d_ctr.p;
+    CU(cudaMemsetAsync(ctx->d_ctr.p, 0, sizeof(DevCounters), ctx->stream));
+    launch_validate(ctx->pc, a, true, ctx->stream);
+    ctx->tm.kernel_launches++;
+    DevCounters hc;
+    CU(cudaMemcpyAsync(&hc, ctx->d_ctr.p, sizeof(hc), cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    CU(cudaGetLastError());
+    int64_t inl = 0, vis = 0, sup = 0, par = 0;
+    for (int k = 0; k < CVX_CTR_SLOTS; k++) {
+        inl += int64_t(hc.n_inliers[k]); vis += int64_t(hc.n_visited[k]); sup += int64_t(hc.n_supported[k]); par += int64_t(hc.n_parallel[k]);
+    }
+    if (n_inliers) *n_inliers = inl;
+    if (n_visited) *n_visited = vis;
+    if (n_supported) *n_supported = sup;
+    if (n_parallel) *n_parallel = par;
     return CVX_OK;
 }
 int cvx_support_problem_result(cvx_support_problem* p, int32_t* support) {

@@ -54,6 +54,26 @@ void launch_edge_trig(const double* th, double* cs, double* sn, int64_t n, cudaS
     k_edge_trig<<<unsigned((n + 255) / 256), 256, 0, st>>>(th, cs, sn, n);
 }
 
+// All views in one launch: packed host-order columns (already on the device in a staging buffer) -> per-view arena slots, with
+// cos/sin of the orientation.  tab = [src_off | dst_off | n] (3 x n_views int64).
+__global__ void __launch_bounds__(256) k_ingest_views(const double* __restrict__ sx, const double* __restrict__ sy, const double* __restrict__ st,
+                                                      const int64_t* __restrict__ tab, int n_views, EdgeArena ea) {
+    const int v = blockIdx.y;
+    const int64_t n = tab[2 * n_views + v];
+    const int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+    if (i >= n) return;
+    const int64_t s = tab[v] + i, d = tab[n_views + v] + i;
+    const double th = st[s];
+    ea.x[d] = sx[s]; ea.y[d] = sy[s]; ea.th[d] = th;
+    ea.cs[d] = cos(th); ea.sn[d] = sin(th);                       // EdgeSketch_Core.cpp:321-322, hoisted
+}
+void launch_ingest_views(const double* sx, const double* sy, const double* st_, const int64_t* tab, int n_views, int64_t max_n, EdgeArena ea,
+                         cudaStream_t st) {
+    if (max_n <= 0 || n_views <= 0) return;
+    dim3 grid(unsigned((max_n + 255) / 256), n_views);
+    k_ingest_views<<<grid, 256, 0, st>>>(sx, sy, st_, tab, n_views, ea);
+}
+
 // ----------------------------------------------------------------------------- per-pass view staging
 #define GRID_MAX_BINS 16384
 #define GRID_CELLS_PER_WEDGE 2.0   // a wedge spans 3 (at most 4) rows of cells: what a lane keeps in registers (VAL_LIGHT_ROWS)
@@ -480,7 +500,8 @@ struct ClusterSm {
     uint32_t adj[N * (N / 32)];
     int16_t label[N], size[N], rank[N], mem[32];
 };
-#define CL_N 128          // rows handled by the shared-memory path; larger groups take the global-memory fallback
+#define CL_N 128          // rows handled by the shared-memory path inside k_form
+#define CL_BIG_N 512      // rows handled by k_cluster_big (one warp per block, 52 KB of shared memory); beyond: global-memory fallback
 #define FORM_WARPS 4
 
 // Gaussian-weighted average over the members s.mem[0..cnt) (ascending index): EdgeClusterer.cpp:60-125.  All sums run
@@ -789,7 +810,8 @@ __global__ void __launch_bounds__(FORM_WARPS * 32) k_form(const __grid_constant_
                                                           const double2* __restrict__ wedge_h1, const double* __restrict__ x2,
                                                           const double* __restrict__ y2, const double* __restrict__ th2,
                                                           const double* __restrict__ ang2, int E2, const AngleIndex ix, int32_t* m_out,
-                                                          int32_t* n_out, const int64_t* __restrict__ row_off, RowTable rt, int32_t* n_clusters) {
+                                                          int32_t* n_out, const int64_t* __restrict__ row_off, RowTable rt, int32_t* n_clusters,
+                                                          int32_t* big_list, int32_t* big_count) {
     extern __shared__ __align__(16) unsigned char form_smem[];
     const int lane = threadIdx.x & 31;
     const int h1 = h1_begin + blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
@@ -866,10 +888,29 @@ __global__ void __launch_bounds__(FORM_WARPS * 32) k_form(const __grid_constant_
         ClusterSm<CL_N>& s = reinterpret_cast<ClusterSm<CL_N>*>(form_smem)[threadIdx.x >> 5];
         cluster_warp_sm<CL_N>(n_total, pc, s, rt.xc + row0, rt.yc + row0, rt.th + row0, rt.h2orig + row0, rt.xbar + row0, rt.ybar + row0,
                               rt.thbar + row0, rt.label + row0, rt.h2rep + row0, rt.urank + row0, n_clusters + h1, lane);
+    } else if (n_total <= CL_BIG_N && pc.max_cluster <= 32) {
+        // too many rows for this block's share of shared memory: queued for k_cluster_big (rows are already written)
+        if (lane == 0) big_list[atomicAdd(big_count, 1)] = h1;
     } else {
         cluster_warp_global(n_total, pc, rt.xc + row0, rt.yc + row0, rt.th + row0, rt.thn + row0, rt.orient + row0, rt.label + row0,
                             rt.h2orig + row0, rt.xbar + row0, rt.ybar + row0, rt.thbar + row0, rt.h2rep + row0, rt.urank + row0,
                             n_clusters + h1, lane);
+    }
+}
+// Clustering of the view-1 edges whose hypothesis group has CL_N < n <= CL_BIG_N rows: same warp algorithm, one warp per
+// block with the whole adjacency matrix in shared memory, blocks stride over the queue k_form<true> filled.
+__global__ void __launch_bounds__(32) k_cluster_big(const __grid_constant__ PassConst pc, const int32_t* __restrict__ big_list,
+                                                    const int32_t* __restrict__ big_count, const int32_t* __restrict__ n_of,
+                                                    const int64_t* __restrict__ row_off, RowTable rt, int32_t* n_clusters) {
+    extern __shared__ __align__(16) unsigned char big_smem[];
+    ClusterSm<CL_BIG_N>& s = *reinterpret_cast<ClusterSm<CL_BIG_N>*>(big_smem);
+    const int cnt = *big_count;
+    for (int b = blockIdx.x; b < cnt; b += gridDim.x) {
+        const int h1 = big_list[b];
+        const int64_t row0 = row_off[h1];
+        cluster_warp_sm<CL_BIG_N>(n_of[h1], pc, s, rt.xc + row0, rt.yc + row0, rt.th + row0, rt.h2orig + row0, rt.xbar + row0, rt.ybar + row0,
+                                  rt.thbar + row0, rt.label + row0, rt.h2rep + row0, rt.urank + row0, n_clusters + h1, threadIdx.x);
+        __syncwarp();
     }
 }
 void launch_form_count(const PassConst& pc, const double* x1, const double* y1, int h1_begin, int h1_end, const double2* wedge_h1,
@@ -879,18 +920,22 @@ void launch_form_count(const PassConst& pc, const double* x1, const double* y1, 
     if (n <= 0) return;
     RowTable rt = {};
     k_form<false><<<(n + FORM_WARPS - 1) / FORM_WARPS, FORM_WARPS * 32, 0, st>>>(pc, x1, y1, h1_begin, h1_end, wedge_h1, x2, y2, th2, ang2, E2, ix,
-                                                                                m_out, n_out, nullptr, rt, nullptr);
+                                                                                m_out, n_out, nullptr, rt, nullptr, nullptr, nullptr);
 }
 void launch_form_fill(const PassConst& pc, const double* x1, const double* y1, int h1_begin, int h1_end, const double2* wedge_h1,
                       const double* x2, const double* y2, const double* th2, const double* ang2, int E2, AngleIndex ix, const int32_t* m_of,
-                      const int32_t* n_of, const int64_t* row_off, RowTable rt, int32_t* n_clusters, cudaStream_t st) {
+                      const int32_t* n_of, const int64_t* row_off, RowTable rt, int32_t* n_clusters, int32_t* big_list, int32_t* big_count,
+                      cudaStream_t st) {
     const int n = h1_end - h1_begin;
     if (n <= 0) return;
     const size_t smem = FORM_WARPS * sizeof(ClusterSm<CL_N>);
     cudaFuncSetAttribute(k_form<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));   // per device, cheap
     k_form<true><<<(n + FORM_WARPS - 1) / FORM_WARPS, FORM_WARPS * 32, smem, st>>>(pc, x1, y1, h1_begin, h1_end, wedge_h1, x2, y2, th2, ang2, E2, ix,
                                                                                   const_cast<int32_t*>(m_of), const_cast<int32_t*>(n_of), row_off, rt,
-                                                                                  n_clusters);
+                                                                                  n_clusters, big_list, big_count);
+    const size_t big = sizeof(ClusterSm<CL_BIG_N>);
+    cudaFuncSetAttribute(k_cluster_big, cudaFuncAttributeMaxDynamicSharedMemorySize, int(big));
+    k_cluster_big<<<std::min(n, 148 * 4), 32, big, st>>>(pc, big_list, big_count, n_of, row_off, rt, n_clusters);
 }
 
 // ----------------------------------------------------------------------------- unique-hypothesis table

@@ -67,6 +67,8 @@ struct UniqTable {
 
 
 void launch_edge_trig(const double* th, double* cs, double* sn, int64_t n, cudaStream_t st);
+void launch_ingest_views(const double* sx, const double* sy, const double* st_, const int64_t* tab, int n_views, int64_t max_n, EdgeArena ea,
+                         cudaStream_t st);
 
 int pick_cell_stride(int64_t max_edges);   // CS: cell budget per view (~16 cells per edge of the largest view) + 1
 // scratch of the segmented cell scan: 2 * n_vali * scan_tiles(CS) ints
@@ -103,7 +105,8 @@ void launch_form_count(const PassConst& pc, const double* x1, const double* y1, 
                        int32_t* n_out, cudaStream_t st);
 void launch_form_fill(const PassConst& pc, const double* x1, const double* y1, int h1_begin, int h1_end, const double2* wedge_h1,
                       const double* x2, const double* y2, const double* th2, const double* ang2, int E2, AngleIndex ix, const int32_t* m_of,
-                      const int32_t* n_of, const int64_t* row_off, RowTable rt, int32_t* n_clusters, cudaStream_t st);
+                      const int32_t* n_of, const int64_t* row_off, RowTable rt, int32_t* n_clusters, int32_t* big_list, int32_t* big_count,
+                      cudaStream_t st);
 // unique-hypothesis table from the clustered rows (+ view-independent reprojection terms)
 void launch_uniq_fill(const PassConst& pc, const double* x1, const double* y1, const double* th1, RowTable rt, int64_t H,
                       const int64_t* row_off, const int64_t* u_off, UniqTable ut, cudaStream_t st);

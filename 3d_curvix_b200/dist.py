@@ -28,7 +28,7 @@ class _DevArray:
     """Exposes a raw device pointer of the C-ABI (cvx_get_device_results) through __cuda_array_interface__."""
 
     def __init__(self, ptr, shape, typestr):
-        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": typestr, "data": (int(ptr), True), "version": 3, "strides": None}
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": typestr, "data": (int(ptr), False), "version": 3, "strides": None}
 
 
 def device_tensor(ptr, shape, dtype):
@@ -61,10 +61,42 @@ def gather_varlen(t, group=None, dst=0):
 
 
 def gather_results(local, group=None, dst=0):
-    """local: dict name -> tensor with a common ragged first dimension (pairs).  Returns the concatenated dict on dst."""
+    """local: dict name -> tensor with a common ragged first dimension (accepted pairs).  Returns (dict concatenated in rank
+    order on dst | None elsewhere, per-rank row counts).  Two collectives in total: the row counts, then ONE all_gather of a
+    byte buffer into which every field is packed (fields back to back, padded to the largest rank) -- the payload is KB-MB,
+    so the exchange is latency-bound and the number of collectives is what matters."""
+    world = dist.get_world_size(group)
+    rank = dist.get_rank(group)
+    keys = sorted(local)
+    first = local[keys[0]]
+    dev = first.device
+    n = torch.tensor([first.shape[0]], dtype=torch.int64, device=dev)
+    cl = [torch.zeros_like(n) for _ in range(world)]
+    dist.all_gather(cl, n, group=group)
+    counts = [int(c) for c in torch.cat(cl).tolist()]
+    row_bytes = {k: int(np.prod(local[k].shape[1:], dtype=np.int64)) * local[k].element_size() for k in keys}
+    per_row = sum(row_bytes.values())
+    mx = max(max(counts), 1)
+    # field k of a rank with c rows occupies bytes [c * prefix_k, c * prefix_k + c * row_bytes_k): 8-byte aligned when every
+    # wider-than-4-byte field comes first
+    order = sorted(keys, key=lambda k: (-local[k].element_size(), k))
+    buf = torch.empty(mx * per_row, dtype=torch.uint8, device=dev)
+    off = 0
+    for k in order:
+        nb = first.shape[0] * row_bytes[k]
+        if nb:
+            buf[off:off + nb] = local[k].contiguous().view(-1).view(torch.uint8)
+        off += nb
+    bufs = [torch.empty_like(buf) for _ in range(world)]
+    dist.all_gather(bufs, buf, group=group)
+    if rank != dst:
+        return None, counts
     out = {}
-    counts = None
-    for k in sorted(local):
-        g, counts = gather_varlen(local[k], group, dst)
-        out[k] = g
-    return (out if dist.get_rank(group) == dst else None), counts
+    for k in keys:
+        parts = []
+        for r in range(world):
+            c = counts[r]
+            o = sum(c * row_bytes[q] for q in order[:order.index(k)])
+            parts.append(bufs[r][o:o + c * row_bytes[k]].view(local[k].dtype).view((c,) + tuple(local[k].shape[1:])))
+        out[k] = torch.cat(parts, 0)
+    return out, counts

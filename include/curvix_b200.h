@@ -90,6 +90,12 @@ int cvx_set_cameras(cvx_ctx* ctx, int n, const double* R, const double* T, const
 int cvx_set_view_edges(cvx_ctx* ctx, int view, int n, const double* x, const double* y, const double* theta,
                        const double* strength);
 
+/* Same, all views in one call (what Read_Edgels_Data does: it loads every view, EdgeSketch_Core.hpp:87-90).
+ * x, y, theta are the per-view columns concatenated in view order (view v starts at n[0] + ... + n[v-1]); n_views must equal
+ * cfg.n_views.  Three host->device copies and one kernel instead of 3 copies + 1 kernel per view; pinned host memory streams at
+ * link speed. */
+int cvx_set_all_view_edges(cvx_ctx* ctx, int n_views, const int32_t* n, const double* x, const double* y, const double* theta);
+
 /* replaces Set_Hypothesis_Views_Camera + Set_Hypothesis_Views_Edgels EdgeSketch_Core.cpp:115-166
  * Computes the per-pass constants (R21,T21,F21, per-view F/epipoles), the epipolar angles of the view-2 edges
  * (getOreList), the wedges of the view-1 edges (getOreListBar) and stages every validation view
@@ -195,6 +201,10 @@ int cvx_support_problem_create(cvx_ctx* ctx, int n_groups, const int64_t* group_
                                const double* wedge31, const double* wedge32, const double* tgt, double cos_thresh,
                                double parallel_deg, cvx_support_problem** out);
 int cvx_support_problem_run(cvx_support_problem* p, float* kernel_ms);
+/* Counted re-run (untimed): wedge-intersection members (the n of SURVEY.md 8d "52 + 16 n" bytes per validation), grid entries
+ * visited, supported and parallel-wedge validations, summed over the whole problem.  Any pointer may be NULL. */
+int cvx_support_problem_stats(cvx_support_problem* p, int64_t* n_inliers, int64_t* n_visited, int64_t* n_supported,
+                              int64_t* n_parallel);
 int cvx_support_problem_result(cvx_support_problem* p, int32_t* support);
 int cvx_support_problem_destroy(cvx_support_problem* p);
 

@@ -40,6 +40,25 @@ def test_tiny_scene_full_parity(oracle_mod, tiny_scene):
         assert rep["counts_gpu"]["n_hypotheses"] > 0
 
 
+def test_large_hypothesis_groups_parity(oracle_mod, data_mod):
+    """Dense views: hypothesis groups of 128 < n <= 512 rows are clustered by k_cluster_big, n > 512 by the global-memory
+    fallback; both must reproduce the oracle's greedy merge order exactly.  Also exercises the packed all-view upload."""
+    scene = data_mod.make_synthetic_scene(n_views=6, edges_per_view=40000, rows=800, cols=800, seed=11, n_curves=12)
+    o = make_oracle(oracle_mod, scene, max_support_views=2)
+    api = pkg("api")
+    g = api.EdgeSketch(api.default_config(n_views=6, img_rows=800, img_cols=800, max_support_views=2), 0)
+    g.keep_intermediates(True)
+    g.set_cameras(scene.R, scene.T, scene.K)
+    g.set_all_view_edges(scene.edges)
+    o.set_pair(0, 1); g.set_pair(0, 1)
+    n = g.run(0, 1500).h1_table()["n"]
+    assert ((n > 128) & (n <= 512)).sum() > 50, "scene no longer produces medium-size groups"
+    o.run(0, 1500, mode=1, keep=True)
+    rep = compare(o, g, check_intermediates=True)
+    _report("large_groups_0_1", rep)
+    assert rep["counts_gpu"]["n_hypotheses"] > 100000
+
+
 def test_abc_nef_first_pass_parity(oracle_mod, abc_scene):
     """BASELINE.json config 1: ABC-NEF 00000006, configs/3D_Curvix_ABC_NEF.yaml parameters, initial pair (47, 42)."""
     o = make_oracle(oracle_mod, abc_scene)
