@@ -1013,6 +1013,11 @@ struct SupportAcc {
     int bj;        // position (in the walked layout) of the best entry so far, -1 = none
     unsigned n_in, n_vis;
 };
+__device__ __forceinline__ double4 ld_rec(const double4* p) {   // one 256-bit load (LDG.E.ENL2.256) instead of two 128-bit ones:
+    double4 r;                                                  // half the L1 tag lookups of the walk, which is L1-lookup bound
+    asm volatile("ld.global.nc.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(r.x), "=d"(r.y), "=d"(r.z), "=d"(r.w) : "l"(p));
+    return r;
+}
 // One candidate entry.  The edge index is only needed to break exact ties (equal |t . t^|: the reference keeps the first in
 // ascending index order), so it is not loaded on the common path: the walk carries the POSITION of the best entry.
 __device__ __forceinline__ void support_visit(SupportAcc& s, const double4 e, int j, const double2 w1, const double2 w2, const double2 tg,
@@ -1118,7 +1123,7 @@ __global__ void __launch_bounds__(VAL_THREADS, VAL_MIN_BLOCKS) k_validate(const 
                     j[t] = kk < l0 ? beg[0] + kk : kk < l1 ? beg[1] + (kk - l0) : kk < l2 ? beg[2] + (kk - l1) : beg[3] + (kk - l2);
                 }
 #pragma unroll
-                for (int t = 0; t < VAL_BATCH; t++) e[t] = rec[j[t]];
+                for (int t = 0; t < VAL_BATCH; t++) e[t] = ld_rec(rec + j[t]);
 #pragma unroll
                 for (int t = 0; t < VAL_BATCH; t++)
                     if (t == 0 || k + t < work) support_visit(acc, e[t], j[t], w1, w2, tg, a.cos_thresh, idx_);
@@ -1128,7 +1133,7 @@ __global__ void __launch_bounds__(VAL_THREADS, VAL_MIN_BLOCKS) k_validate(const 
             for (int b = r0; b <= r1; b++) {
                 const int cc = b * G + c0;
                 const int jb = cc ? ce[cc - 1] : 0, je = ce[b * G + c1];
-                for (int j = jb; j < je; j++) support_visit(acc, rec[j], j, w1, w2, tg, a.cos_thresh, idx_);
+                for (int j = jb; j < je; j++) support_visit(acc, ld_rec(rec + j), j, w1, w2, tg, a.cos_thresh, idx_);
             }
         }
     }
@@ -1154,13 +1159,13 @@ __global__ void __launch_bounds__(VAL_THREADS, VAL_MIN_BLOCKS) k_validate(const 
             for (int b = sr0 + lane; b <= sr1; b += 32) {
                 const int cc = b * sG + sc0;
                 const int jb = cc ? ce[cc - 1] : 0, je = ce[b * sG + sc1];
-                for (int j = jb; j < je; j++) support_visit(ca, rec[j], j, sw1, sw2, stg, a.cos_thresh, idx_);
+                for (int j = jb; j < je; j++) support_visit(ca, ld_rec(rec + j), j, sw1, sw2, stg, a.cos_thresh, idx_);
             }
         } else {                                        // few long rows: the lanes stride over the entries
             for (int b = sr0; b <= sr1; b++) {
                 const int cc = b * sG + sc0;
                 const int jb = cc ? ce[cc - 1] : 0, je = ce[b * sG + sc1];
-                for (int j = jb + lane; j < je; j += 32) support_visit(ca, rec[j], j, sw1, sw2, stg, a.cos_thresh, idx_);
+                for (int j = jb + lane; j < je; j += 32) support_visit(ca, ld_rec(rec + j), j, sw1, sw2, stg, a.cos_thresh, idx_);
             }
         }
         int ci = ca.bj >= 0 ? idx_[ca.bj] : -2;         // edge index of the lane's best
