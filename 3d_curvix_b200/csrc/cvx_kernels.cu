@@ -498,41 +498,35 @@ struct ClusterSm {
     double x[N], y[N], thn[N], orient[N];   // corrected location, normalised orientation, per-label average orientation
     double tmpd[32], tmpw[32];
     uint32_t adj[N * (N / 32)];
-    int16_t label[N], size[N], rank[N], mem[32];
+    uint32_t dirty[N / 32], canw[N / 32];   // rows whose merge decision must be re-evaluated / rows that can merge (bit per row)
+    int16_t label[N], size[N], rank[N], mem[32];   // rank doubles as the cached merge partner during the merge phase
 };
 #define CL_N 128          // rows handled by the shared-memory path inside k_form
 #define CL_BIG_N 512      // rows handled by k_cluster_big (one warp per block, 52 KB of shared memory); beyond: global-memory fallback
 #define FORM_WARPS 4
 
-// Gaussian-weighted average over the members s.mem[0..cnt) (ascending index): EdgeClusterer.cpp:60-125.  All sums run
-// in member order on every lane (bit-identical to the sequential code); sqrt / exp of the members are lane-parallel.
+// Gaussian-weighted average over the members s.mem[0..cnt) (ascending index): EdgeClusterer.cpp:60-125.  Lane k holds member k;
+// every sum runs in member order on every lane through shuffles (bit-identical to the sequential code: the products are formed
+// per member first, the additions are the reference's left-to-right chain); sqrt / exp of the members are lane-parallel.
+__device__ __forceinline__ double shfl_d(double v, int src) { return __shfl_sync(FULL, v, src); }
 template <int N>
-__device__ __forceinline__ void gauss_avg_list(ClusterSm<N>& s, int cnt, double sigma, int lane, double* gx, double* gy, double* gth) {
+__device__ __noinline__ void gauss_avg_list(ClusterSm<N>& s, int cnt, double sigma, int lane, double* gx, double* gy, double* gth) {
+    double xi = 0, yi = 0, ti = 0;
+    if (lane < cnt) { const int i = s.mem[lane]; xi = s.x[i]; yi = s.y[i]; ti = s.thn[i]; }
     double sx = 0, sy = 0;
-    for (int k = 0; k < cnt; k++) { const int i = s.mem[k]; sx += s.x[i]; sy += s.y[i]; }
+    for (int k = 0; k < cnt; k++) { sx += shfl_d(xi, k); sy += shfl_d(yi, k); }
     const double cx = sx / cnt, cy = sy / cnt;
-    if (lane < cnt) {
-        const int i = s.mem[lane];
-        const double dx = s.x[i] - cx, dy = s.y[i] - cy;
-        s.tmpd[lane] = sqrt(dx * dx + dy * dy);
-    }
-    __syncwarp();
+    const double dx = xi - cx, dy = yi - cy;
+    const double di = sqrt(dx * dx + dy * dy);
     double tot = 0.0;
-    for (int k = 0; k < cnt; k++) tot += s.tmpd[k];
+    for (int k = 0; k < cnt; k++) tot += shfl_d(di, k);
     const double mean_shift = tot / cnt;
-    if (lane < cnt) {
-        const double q = (s.tmpd[lane] - mean_shift) / sigma;
-        s.tmpw[lane] = exp(-0.5 * (q * q));
-    }
-    __syncwarp();
+    const double q = (di - mean_shift) / sigma;
+    const double w = exp(-0.5 * (q * q));
+    const double wx = w * xi, wy = w * yi, wo = w * ti;
     double swx = 0, swy = 0, swo = 0, tw = 0;
-    for (int k = 0; k < cnt; k++) {
-        const int i = s.mem[k];
-        const double w = s.tmpw[k];
-        swx += w * s.x[i]; swy += w * s.y[i]; swo += w * s.thn[i]; tw += w;
-    }
+    for (int k = 0; k < cnt; k++) { swx += shfl_d(wx, k); swy += shfl_d(wy, k); swo += shfl_d(wo, k); tw += shfl_d(w, k); }
     *gx = swx / tw; *gy = swy / tw; *gth = swo / tw;
-    __syncwarp();
 }
 // members with label la or lb, ascending, into s.mem; returns the count (<= 32 by construction)
 template <int N>
@@ -575,22 +569,29 @@ __device__ void cluster_warp_sm(int n, const PassConst& pc, ClusterSm<N>& s, con
         }
     }
     __syncwarp();
-    while (true) {                                                        // :139-189
-        int mi = -1, mj = -1;
-        for (int base = 0; base < n; base += 32) {
-            const int i = base + lane;
+    // :139-189.  The reference restarts its scan after every merge and takes the first row that can merge.  A row's decision
+    // depends only on its own cluster and on the clusters of its neighbours (adjacency), so after a merge only the members of
+    // the merged cluster and the rows adjacent to them are re-evaluated; every other row keeps its cached decision and partner.
+    // The first set bit of the "can merge" mask is exactly the row the restarted scan would reach first.
+    for (int w = lane; w < nw; w += 32) { const int rem = n - w * 32; s.dirty[w] = rem >= 32 ? 0xffffffffu : ((1u << rem) - 1u); s.canw[w] = 0u; }
+    __syncwarp();
+    while (true) {
+        for (int w = 0; w < nw; w++) {
+            const uint32_t dw = s.dirty[w];
+            if (!dw) continue;
+            const int i = w * 32 + lane;
             bool found = false;
-            int bj = -1;
-            if (i < n) {
+            if ((dw >> lane) & 1u) {
                 const int li = s.label[i];
                 const double oi = s.orient[li], xi = s.x[i], yi = s.y[i];
                 double bd = DBL_MAX;
-                for (int w = 0; w < nw; w++) {
-                    uint32_t bits = s.adj[i * NW + w];
+                int bj = -1;
+                for (int ww = 0; ww < nw; ww++) {
+                    uint32_t bits = s.adj[i * NW + ww];
                     while (bits) {
                         const int b = __ffs(bits) - 1;
                         bits &= bits - 1;
-                        const int j = w * 32 + b;
+                        const int j = ww * 32 + b;
                         const int lj = s.label[j];
                         if (lj != li && fabs(oi - s.orient[lj]) < pc.cl_orient_rad) {          // :147-154
                             const double ddx = xi - s.x[j], ddy = yi - s.y[j];
@@ -599,23 +600,28 @@ __device__ void cluster_warp_sm(int n, const PassConst& pc, ClusterSm<N>& s, con
                         }
                     }
                 }
-                if (bj >= 0 && int(s.size[s.label[bj]]) + int(s.size[li]) <= pc.max_cluster) found = true;   // :166
+                found = bj >= 0 && int(s.size[s.label[bj]]) + int(s.size[li]) <= pc.max_cluster;   // :166
+                s.rank[i] = int16_t(found ? bj : -1);
             }
             const unsigned m = __ballot_sync(FULL, found);
-            if (m) {
-                const int src = __ffs(m) - 1;
-                mi = base + src;
-                mj = __shfl_sync(FULL, bj, src);
-                break;
-            }
+            if (lane == 0) { s.canw[w] = (s.canw[w] & ~dw) | m; s.dirty[w] = 0u; }
         }
+        __syncwarp();
+        int mi = -1;
+        for (int w = 0; w < nw; w++) { const uint32_t cw = s.canw[w]; if (cw) { mi = w * 32 + __ffs(cw) - 1; break; } }
         if (mi < 0) break;
+        const int mj = s.rank[mi];
         const int old_l = s.label[mj], new_l = s.label[mi];
         const int cnt = member_list(s, n, old_l, new_l, lane, lt);
         double gx, gy, gth;
         gauss_avg_list(s, cnt, pc.cl_sigma, lane, &gx, &gy, &gth);       // :168
         if (lane == 0) { s.orient[new_l] = normalize_orientation(gth, pc.cl_wrap_deg); s.size[new_l] = int16_t(cnt); }   // :175-176
         for (int k = lane; k < n; k += 32) if (s.label[k] == old_l) s.label[k] = int16_t(new_l);   // :179-183
+        for (int w = lane; w < nw; w += 32) {                            // members + everything adjacent to a member
+            uint32_t d = 0u;
+            for (int k = 0; k < cnt; k++) { const int mrow = s.mem[k]; d |= s.adj[mrow * NW + w]; if ((mrow >> 5) == w) d |= 1u << (mrow & 31); }
+            s.dirty[w] = d;
+        }
         __syncwarp();
     }
     // cluster ranks (clusters in ascending label order = the reference's std::map order); a label in use is the index
@@ -776,7 +782,6 @@ __device__ void cluster_warp_global(int n, const PassConst& pc, const double* xc
 // (ascending view-2 index) by rank-sorting the gathered candidates in shared memory; edges with more candidates than the
 // shared-memory list holds fall back to the ordered linear scan of the whole angle list.
 #define FORM_CAND_CAP 512
-static_assert(2 * FORM_CAND_CAP * sizeof(int32_t) <= sizeof(ClusterSm<CL_N>), "candidate lists alias the clustering storage");
 
 // processes 32 candidates (lane: view-2 edge i, valid when in) of an ordered candidate stream; returns through mbase / nbase
 template <bool FILL>
@@ -810,8 +815,7 @@ __global__ void __launch_bounds__(FORM_WARPS * 32) k_form(const __grid_constant_
                                                           const double2* __restrict__ wedge_h1, const double* __restrict__ x2,
                                                           const double* __restrict__ y2, const double* __restrict__ th2,
                                                           const double* __restrict__ ang2, int E2, const AngleIndex ix, int32_t* m_out,
-                                                          int32_t* n_out, const int64_t* __restrict__ row_off, RowTable rt, int32_t* n_clusters,
-                                                          int32_t* big_list, int32_t* big_count) {
+                                                          int32_t* n_out, const int64_t* __restrict__ row_off, RowTable rt, int32_t* n_clusters) {
     extern __shared__ __align__(16) unsigned char form_smem[];
     const int lane = threadIdx.x & 31;
     const int h1 = h1_begin + blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
@@ -851,7 +855,7 @@ __global__ void __launch_bounds__(FORM_WARPS * 32) k_form(const __grid_constant_
     }
     if (m_total <= FORM_CAND_CAP) {
         // gather (unordered), rank-sort by view-2 index, then the reference's ordered pass over the candidates
-        int32_t* cand = reinterpret_cast<int32_t*>(form_smem + size_t(threadIdx.x >> 5) * sizeof(ClusterSm<CL_N>));
+        int32_t* cand = reinterpret_cast<int32_t*>(form_smem + size_t(threadIdx.x >> 5) * (2 * FORM_CAND_CAP * sizeof(int32_t)));
         int32_t* sorted = cand + FORM_CAND_CAP;
         int m = 0;
         for (int base = beg; base < end; base += 32) {
@@ -883,33 +887,55 @@ __global__ void __launch_bounds__(FORM_WARPS * 32) k_form(const __grid_constant_
             form_chunk<true>(in, i, coef, pc, x2, y2, th2, h1, n_total, row0, rt, lt, mbase, nbase);
         }
     }
-    __syncwarp();
-    if (n_total <= CL_N && pc.max_cluster <= 32) {
-        ClusterSm<CL_N>& s = reinterpret_cast<ClusterSm<CL_N>*>(form_smem)[threadIdx.x >> 5];
-        cluster_warp_sm<CL_N>(n_total, pc, s, rt.xc + row0, rt.yc + row0, rt.th + row0, rt.h2orig + row0, rt.xbar + row0, rt.ybar + row0,
-                              rt.thbar + row0, rt.label + row0, rt.h2rep + row0, rt.urank + row0, n_clusters + h1, lane);
-    } else if (n_total <= CL_BIG_N && pc.max_cluster <= 32) {
-        // too many rows for this block's share of shared memory: queued for k_cluster_big (rows are already written)
-        if (lane == 0) big_list[atomicAdd(big_count, 1)] = h1;
-    } else {
-        cluster_warp_global(n_total, pc, rt.xc + row0, rt.yc + row0, rt.th + row0, rt.thn + row0, rt.orient + row0, rt.label + row0,
-                            rt.h2orig + row0, rt.xbar + row0, rt.ybar + row0, rt.thbar + row0, rt.h2rep + row0, rt.urank + row0,
-                            n_clusters + h1, lane);
+}
+// ---- clustering as its own launches (the formation kernel stays small enough for the instruction cache, and the clustering
+// kernels see the view-1 edges in DESCENDING order of their hypothesis count, so the long sequential merges start first).
+// k_order_by_n: one block; order[] = edges with 1 <= n <= CL_N sorted by n descending, then those with CL_N < n <= CL_BIG_N, then
+// the rest; cnts[0..2] = the three counts.
+#define ORDER_BUCKETS (CL_N + 2)
+__global__ void __launch_bounds__(1024) k_order_by_n(const int32_t* __restrict__ n_of, int h1_begin, int h1_end, int max_cluster,
+                                                     int32_t* __restrict__ order, int32_t* __restrict__ cnts) {
+    __shared__ int hist[ORDER_BUCKETS];
+    for (int k = threadIdx.x; k < ORDER_BUCKETS; k += blockDim.x) hist[k] = 0;
+    __syncthreads();
+    const bool sm_ok = max_cluster <= 32;          // the shared-memory algorithm keeps member lists of at most 32
+    auto key = [&](int n) { return (!sm_ok || n > CL_BIG_N) ? CL_N + 1 : n > CL_N ? CL_N : CL_N - n; };
+    for (int i = h1_begin + threadIdx.x; i < h1_end; i += blockDim.x) { const int n = n_of[i]; if (n > 0) atomicAdd(&hist[key(n)], 1); }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int run = 0, ns = 0;
+        for (int k = 0; k < ORDER_BUCKETS; k++) { const int c = hist[k]; hist[k] = run; run += c; if (k == CL_N - 1) ns = run; }
+        cnts[0] = ns; cnts[1] = hist[CL_N + 1] - ns; cnts[2] = run - hist[CL_N + 1];
+    }
+    __syncthreads();
+    for (int i = h1_begin + threadIdx.x; i < h1_end; i += blockDim.x) { const int n = n_of[i]; if (n > 0) order[atomicAdd(&hist[key(n)], 1)] = i; }
+}
+template <int N, int WARPS>
+__global__ void __launch_bounds__(WARPS * 32) k_cluster(const __grid_constant__ PassConst pc, const int32_t* __restrict__ order,
+                                                        const int32_t* __restrict__ cnts, int which, const int32_t* __restrict__ n_of,
+                                                        const int64_t* __restrict__ row_off, RowTable rt, int32_t* n_clusters) {
+    extern __shared__ __align__(16) unsigned char cl_smem[];
+    ClusterSm<N>& s = reinterpret_cast<ClusterSm<N>*>(cl_smem)[threadIdx.x >> 5];
+    const int lane = threadIdx.x & 31;
+    const int base = which ? cnts[0] : 0, cnt = cnts[which];
+    for (int b = blockIdx.x * WARPS + (threadIdx.x >> 5); b < cnt; b += gridDim.x * WARPS) {
+        const int h1 = order[base + b];
+        const int64_t row0 = row_off[h1];
+        cluster_warp_sm<N>(n_of[h1], pc, s, rt.xc + row0, rt.yc + row0, rt.th + row0, rt.h2orig + row0, rt.xbar + row0, rt.ybar + row0,
+                           rt.thbar + row0, rt.label + row0, rt.h2rep + row0, rt.urank + row0, n_clusters + h1, lane);
+        __syncwarp();
     }
 }
-// Clustering of the view-1 edges whose hypothesis group has CL_N < n <= CL_BIG_N rows: same warp algorithm, one warp per
-// block with the whole adjacency matrix in shared memory, blocks stride over the queue k_form<true> filled.
-__global__ void __launch_bounds__(32) k_cluster_big(const __grid_constant__ PassConst pc, const int32_t* __restrict__ big_list,
-                                                    const int32_t* __restrict__ big_count, const int32_t* __restrict__ n_of,
-                                                    const int64_t* __restrict__ row_off, RowTable rt, int32_t* n_clusters) {
-    extern __shared__ __align__(16) unsigned char big_smem[];
-    ClusterSm<CL_BIG_N>& s = *reinterpret_cast<ClusterSm<CL_BIG_N>*>(big_smem);
-    const int cnt = *big_count;
+__global__ void __launch_bounds__(32) k_cluster_huge(const __grid_constant__ PassConst pc, const int32_t* __restrict__ order,
+                                                     const int32_t* __restrict__ cnts, const int32_t* __restrict__ n_of,
+                                                     const int64_t* __restrict__ row_off, RowTable rt, int32_t* n_clusters) {
+    const int base = cnts[0] + cnts[1], cnt = cnts[2];
     for (int b = blockIdx.x; b < cnt; b += gridDim.x) {
-        const int h1 = big_list[b];
+        const int h1 = order[base + b];
         const int64_t row0 = row_off[h1];
-        cluster_warp_sm<CL_BIG_N>(n_of[h1], pc, s, rt.xc + row0, rt.yc + row0, rt.th + row0, rt.h2orig + row0, rt.xbar + row0, rt.ybar + row0,
-                                  rt.thbar + row0, rt.label + row0, rt.h2rep + row0, rt.urank + row0, n_clusters + h1, threadIdx.x);
+        cluster_warp_global(n_of[h1], pc, rt.xc + row0, rt.yc + row0, rt.th + row0, rt.thn + row0, rt.orient + row0, rt.label + row0,
+                            rt.h2orig + row0, rt.xbar + row0, rt.ybar + row0, rt.thbar + row0, rt.h2rep + row0, rt.urank + row0,
+                            n_clusters + h1, threadIdx.x);
         __syncwarp();
     }
 }
@@ -920,7 +946,7 @@ void launch_form_count(const PassConst& pc, const double* x1, const double* y1, 
     if (n <= 0) return;
     RowTable rt = {};
     k_form<false><<<(n + FORM_WARPS - 1) / FORM_WARPS, FORM_WARPS * 32, 0, st>>>(pc, x1, y1, h1_begin, h1_end, wedge_h1, x2, y2, th2, ang2, E2, ix,
-                                                                                m_out, n_out, nullptr, rt, nullptr, nullptr, nullptr);
+                                                                                m_out, n_out, nullptr, rt, nullptr);
 }
 void launch_form_fill(const PassConst& pc, const double* x1, const double* y1, int h1_begin, int h1_end, const double2* wedge_h1,
                       const double* x2, const double* y2, const double* th2, const double* ang2, int E2, AngleIndex ix, const int32_t* m_of,
@@ -928,14 +954,19 @@ void launch_form_fill(const PassConst& pc, const double* x1, const double* y1, i
                       cudaStream_t st) {
     const int n = h1_end - h1_begin;
     if (n <= 0) return;
-    const size_t smem = FORM_WARPS * sizeof(ClusterSm<CL_N>);
-    cudaFuncSetAttribute(k_form<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));   // per device, cheap
+    const size_t smem = FORM_WARPS * 2 * FORM_CAND_CAP * sizeof(int32_t);
     k_form<true><<<(n + FORM_WARPS - 1) / FORM_WARPS, FORM_WARPS * 32, smem, st>>>(pc, x1, y1, h1_begin, h1_end, wedge_h1, x2, y2, th2, ang2, E2, ix,
                                                                                   const_cast<int32_t*>(m_of), const_cast<int32_t*>(n_of), row_off, rt,
-                                                                                  n_clusters, big_list, big_count);
-    const size_t big = sizeof(ClusterSm<CL_BIG_N>);
-    cudaFuncSetAttribute(k_cluster_big, cudaFuncAttributeMaxDynamicSharedMemorySize, int(big));
-    k_cluster_big<<<std::min(n, 148 * 4), 32, big, st>>>(pc, big_list, big_count, n_of, row_off, rt, n_clusters);
+                                                                                  n_clusters);
+    // clustering: order by hypothesis count, then one launch per size class (blocks past the class's count exit at once)
+    int32_t* order = big_list;
+    int32_t* cnts = big_count;
+    k_order_by_n<<<1, 1024, 0, st>>>(n_of, h1_begin, h1_end, pc.max_cluster, order, cnts);
+    const size_t sm_small = FORM_WARPS * sizeof(ClusterSm<CL_N>), sm_big = sizeof(ClusterSm<CL_BIG_N>);
+    cudaFuncSetAttribute(k_cluster<CL_BIG_N, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sm_big));   // per device, cheap
+    k_cluster<CL_N, FORM_WARPS><<<(n + FORM_WARPS - 1) / FORM_WARPS, FORM_WARPS * 32, sm_small, st>>>(pc, order, cnts, 0, n_of, row_off, rt, n_clusters);
+    k_cluster<CL_BIG_N, 1><<<std::min(n, 148 * 4), 32, sm_big, st>>>(pc, order, cnts, 1, n_of, row_off, rt, n_clusters);
+    k_cluster_huge<<<std::min(n, 148 * 4), 32, 0, st>>>(pc, order, cnts, n_of, row_off, rt, n_clusters);
 }
 
 // ----------------------------------------------------------------------------- unique-hypothesis table
