@@ -420,6 +420,14 @@ int cvx_set_hypothesis_pair(cvx_ctx* ctx, int h1, int h2) {
     pc.parallel_deg = cfg.parallel_angle_deg;
     pc.loc_pert = cfg.location_perturbation; pc.tang_thresh = cfg.epip_tangency_displ_thresh; pc.orient_pert = cfg.orient_perturbation;
     pc.cl_dist = cfg.cluster_dist_thresh;
+    {   // exact critical value of the squared distance (IEEE sqrt is correctly rounded and monotone; a few ulp steps from cl_dist^2)
+        double sq = pc.cl_dist * pc.cl_dist;
+        if (pc.cl_dist > 0) {
+            while (std::sqrt(sq) >= pc.cl_dist) sq = std::nextafter(sq, 0.0);
+            while (std::sqrt(sq) < pc.cl_dist) sq = std::nextafter(sq, INFINITY);
+        } else sq = 0.0;   // sqrt(s) < non-positive threshold never holds for s >= 0 (s < 0 cannot occur)
+        pc.cl_dist_sq = sq;
+    }
     pc.cl_orient_rad = cfg.cluster_orient_thresh_deg * (M_PI / 180.0);                // util.hpp deg_to_rad
     pc.cl_wrap_deg = -90.0 + (cfg.cluster_orient_thresh_deg / 2.0);                   // EdgeClusterer.cpp:41
     pc.cl_sigma = cfg.cluster_gauss_sigma; pc.lowes_ratio = cfg.lowes_ratio;

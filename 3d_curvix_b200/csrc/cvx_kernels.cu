@@ -509,7 +509,7 @@ struct ClusterSm {
 // every sum runs in member order on every lane through shuffles (bit-identical to the sequential code: the products are formed
 // per member first, the additions are the reference's left-to-right chain); sqrt / exp of the members are lane-parallel.
 __device__ __forceinline__ double shfl_d(double v, int src) { return __shfl_sync(FULL, v, src); }
-template <int N>
+template <int N, bool ORIENT_ONLY>   // ORIENT_ONLY: the merge step needs the averaged orientation alone (EdgeClusterer.cpp:168-176)
 __device__ __noinline__ void gauss_avg_list(ClusterSm<N>& s, int cnt, double sigma, int lane, double* gx, double* gy, double* gth) {
     double xi = 0, yi = 0, ti = 0;
     if (lane < cnt) { const int i = s.mem[lane]; xi = s.x[i]; yi = s.y[i]; ti = s.thn[i]; }
@@ -523,10 +523,17 @@ __device__ __noinline__ void gauss_avg_list(ClusterSm<N>& s, int cnt, double sig
     const double mean_shift = tot / cnt;
     const double q = (di - mean_shift) / sigma;
     const double w = exp(-0.5 * (q * q));
-    const double wx = w * xi, wy = w * yi, wo = w * ti;
-    double swx = 0, swy = 0, swo = 0, tw = 0;
-    for (int k = 0; k < cnt; k++) { swx += shfl_d(wx, k); swy += shfl_d(wy, k); swo += shfl_d(wo, k); tw += shfl_d(w, k); }
-    *gx = swx / tw; *gy = swy / tw; *gth = swo / tw;
+    const double wo = w * ti;
+    double swo = 0, tw = 0;
+    if (ORIENT_ONLY) {
+        for (int k = 0; k < cnt; k++) { swo += shfl_d(wo, k); tw += shfl_d(w, k); }
+    } else {
+        const double wx = w * xi, wy = w * yi;
+        double swx = 0, swy = 0;
+        for (int k = 0; k < cnt; k++) { swx += shfl_d(wx, k); swy += shfl_d(wy, k); swo += shfl_d(wo, k); tw += shfl_d(w, k); }
+        *gx = swx / tw; *gy = swy / tw;
+    }
+    *gth = swo / tw;
 }
 // members with label la or lb, ascending, into s.mem; returns the count (<= 32 by construction)
 template <int N>
@@ -563,7 +570,7 @@ __device__ void cluster_warp_sm(int n, const PassConst& pc, ClusterSm<N>& s, con
             for (int b = 0; b < jend; b++) {
                 const int j = w * 32 + b;
                 const double ddx = xi - s.x[j], ddy = yi - s.y[j];
-                if (sqrt(ddx * ddx + ddy * ddy) < pc.cl_dist && j != i) bits |= (1u << b);
+                if (ddx * ddx + ddy * ddy < pc.cl_dist_sq && j != i) bits |= (1u << b);   // == sqrt(.) < cl_dist, see cl_dist_sq
             }
             s.adj[i * NW + w] = bits;
         }
@@ -614,7 +621,7 @@ __device__ void cluster_warp_sm(int n, const PassConst& pc, ClusterSm<N>& s, con
         const int old_l = s.label[mj], new_l = s.label[mi];
         const int cnt = member_list(s, n, old_l, new_l, lane, lt);
         double gx, gy, gth;
-        gauss_avg_list(s, cnt, pc.cl_sigma, lane, &gx, &gy, &gth);       // :168
+        gauss_avg_list<N, true>(s, cnt, pc.cl_sigma, lane, &gx, &gy, &gth);       // :168
         if (lane == 0) { s.orient[new_l] = normalize_orientation(gth, pc.cl_wrap_deg); s.size[new_l] = int16_t(cnt); }   // :175-176
         for (int k = lane; k < n; k += 32) if (s.label[k] == old_l) s.label[k] = int16_t(new_l);   // :179-183
         for (int w = lane; w < nw; w += 32) {                            // members + everything adjacent to a member
@@ -635,31 +642,39 @@ __device__ void cluster_warp_sm(int n, const PassConst& pc, ClusterSm<N>& s, con
         nroots += __popc(m);
     }
     __syncwarp();
-    // :250-290 per cluster: Gaussian-weighted average written to every member, representative = member closest to it
-    for (int i = 0; i < n; i++) {
-        if (s.label[i] != i) continue;
-        const int cnt = member_list(s, n, i, i, lane, lt);
-        double gx, gy, gth;
-        gauss_avg_list(s, cnt, pc.cl_sigma, lane, &gx, &gy, &gth);
-        double d = DBL_MAX;
-        int pos = lane;
-        if (lane < cnt) {
-            const int j = s.mem[lane];
-            const double ddx = s.x[j] - gx, ddy = s.y[j] - gy;
-            d = sqrt(ddx * ddx + ddy * ddy);
-        }
+    // :250-290 per cluster: Gaussian-weighted average written to every member, representative = member closest to it.
+    // A one-member cluster averages to its member exactly (weight exp(-0) = 1, x / 1 = x): written directly, lane-parallel.
+    for (int k = lane; k < n; k += 32)
+        if (s.label[k] == k && s.size[k] == 1) { xbar[k] = s.x[k]; ybar[k] = s.y[k]; thbar[k] = s.thn[k]; h2rep[k] = h2orig[k]; }
+    for (int base = 0; base < n; base += 32) {
+        const int kk = base + lane;
+        unsigned roots = __ballot_sync(FULL, kk < n && s.label[kk] == kk && s.size[kk] > 1);
+        while (roots) {
+            const int i = base + __ffs(roots) - 1;
+            roots &= roots - 1;
+            const int cnt = member_list(s, n, i, i, lane, lt);
+            double gx, gy, gth;
+            gauss_avg_list<N, false>(s, cnt, pc.cl_sigma, lane, &gx, &gy, &gth);
+            double d = DBL_MAX;
+            int pos = lane;
+            if (lane < cnt) {
+                const int j = s.mem[lane];
+                const double ddx = s.x[j] - gx, ddy = s.y[j] - gy;
+                d = sqrt(ddx * ddx + ddy * ddy);
+            }
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {                                // first minimum in member order (:270)
-            const double od = __shfl_xor_sync(FULL, d, o);
-            const int op = __shfl_xor_sync(FULL, pos, o);
-            if (od < d || (od == d && op < pos)) { d = od; pos = op; }
+            for (int o = 16; o > 0; o >>= 1) {                            // first minimum in member order (:270)
+                const double od = __shfl_xor_sync(FULL, d, o);
+                const int op = __shfl_xor_sync(FULL, pos, o);
+                if (od < d || (od == d && op < pos)) { d = od; pos = op; }
+            }
+            const int rep = h2orig[s.mem[pos]];                           // corrected(closest, 8), :282
+            if (lane < cnt) {
+                const int j = s.mem[lane];
+                xbar[j] = gx; ybar[j] = gy; thbar[j] = gth; h2rep[j] = rep;
+            }
+            __syncwarp();
         }
-        const int rep = h2orig[s.mem[pos]];                               // corrected(closest, 8), :282
-        if (lane < cnt) {
-            const int j = s.mem[lane];
-            xbar[j] = gx; ybar[j] = gy; thbar[j] = gth; h2rep[j] = rep;
-        }
-        __syncwarp();
     }
     for (int k = lane; k < n; k += 32) { const int l = s.label[k]; label_out[k] = l; urank[k] = s.rank[l]; }
     if (lane == 0) *n_clusters = nroots;
