@@ -30,7 +30,7 @@ class CvxConfig(C.Structure):
         ("cluster_dist_thresh", C.c_double), ("cluster_orient_thresh_deg", C.c_double),
         ("cluster_gauss_sigma", C.c_double), ("pi_truncated", C.c_double),
         ("n_views", C.c_int32), ("img_rows", C.c_int32), ("img_cols", C.c_int32),
-        ("max_support_views", C.c_int32), ("max_cluster_size", C.c_int32), ("reserved", C.c_int32),
+        ("max_support_views", C.c_int32), ("max_cluster_size", C.c_int32), ("strict_libm_order", C.c_int32),
     ]
 
 

@@ -563,7 +563,7 @@ int cvx_run_edge_sketch(cvx_ctx* ctx, int h1_begin, int h1_end) {
     std::memset(&a, 0, sizeof(a));
     a.ut = ut; a.U = U; a.x1 = x1; a.y1 = y1; a.w31 = ctx->d_w31.p; a.w31_stride = E1; a.vc = ctx->d_vc.p;
     a.vali_view = ctx->d_vali.p; a.edge_off = ctx->d_edge_off.p; a.gi = ctx->ea.gi;
-    a.cos_thresh = pc.cos_thresh; a.parallel_deg = pc.parallel_deg; a.delta = pc.delta; a.rows = pc.rows; a.cols = pc.cols; a.n_vali = V;
+    a.cos_thresh = pc.cos_thresh; a.parallel_deg = pc.parallel_deg; a.delta = pc.delta; a.rows = pc.rows; a.cols = pc.cols; a.n_vali = V; a.strict = ctx->cfg.strict_libm_order;
     a.support = ctx->d_support.p; a.sup_stride = int64_t(Ua); a.ctr = ctx->d_ctr.p;
     if (ctx->keep_inter) { a.w32_out = ctx->d_w32.p; a.tgt_out = ctx->d_tgt.p; }
     launch_validate(pc, a, false, st);

@@ -1079,7 +1079,7 @@ __device__ __forceinline__ void support_visit(SupportAcc& s, const double4 e, in
     }
 }
 // GIVEN: wedge32 / tangent are inputs (stand-alone support test on pre-formed hypotheses).
-template <bool GIVEN>
+template <bool GIVEN, bool STRICT>
 __global__ void __launch_bounds__(VAL_THREADS, VAL_MIN_BLOCKS) k_validate(const __grid_constant__ PassConst pc, const __grid_constant__ ValidateArgs a) {
     const int64_t u = blockIdx.x * int64_t(VAL_THREADS) + threadIdx.x;
     const int v = blockIdx.y;
@@ -1102,7 +1102,8 @@ __global__ void __launch_bounds__(VAL_THREADS, VAL_MIN_BLOCKS) k_validate(const 
             mat_vec(pc.K1inv, a.x1[h1], a.y1[h1], 1.0, g.G1);
             g.rho1 = ge.x; g.Tv1[0] = ge.y; g.Tv1[1] = ge.z; g.Tv1[2] = ge.w;
             reproject_tangent(g, c.R31, c.T31, &tg.x, &tg.y);
-            wedge_row(xy.x, xy.y, c.F32, c.e1_32[0], c.e1_32[1], c.e2_32[0], c.e2_32[1], a.delta, a.rows, a.cols, &w2.x, &w2.y);
+            if (STRICT) wedge_row(xy.x, xy.y, c.F32, c.e1_32[0], c.e1_32[1], c.e2_32[0], c.e2_32[1], a.delta, a.rows, a.cols, &w2.x, &w2.y);
+            else wedge_row_fast(xy.x, xy.y, c.F32, c.e1_32[0], c.e1_32[1], c.e2_32[0], c.e2_32[1], a.delta, a.rows, a.cols, &w2.x, &w2.y);
             if (a.w32_out) { a.w32_out[int64_t(v) * a.U + u] = w2; a.tgt_out[int64_t(v) * a.U + u] = tg; }
         }
         const bool w1_bad = (w1.x != w1.x), w2_bad = (w2.x != w2.x);
@@ -1251,8 +1252,9 @@ __global__ void __launch_bounds__(VAL_THREADS, VAL_MIN_BLOCKS) k_validate(const 
 void launch_validate(const PassConst& pc, const ValidateArgs& a, bool given, cudaStream_t st) {
     if (a.U <= 0 || a.n_vali <= 0) return;
     dim3 grid(unsigned((a.U + VAL_THREADS - 1) / VAL_THREADS), a.n_vali);
-    if (given) k_validate<true><<<grid, VAL_THREADS, 0, st>>>(pc, a);
-    else k_validate<false><<<grid, VAL_THREADS, 0, st>>>(pc, a);
+    if (given) k_validate<true, false><<<grid, VAL_THREADS, 0, st>>>(pc, a);
+    else if (a.strict) k_validate<false, true><<<grid, VAL_THREADS, 0, st>>>(pc, a);
+    else k_validate<false, false><<<grid, VAL_THREADS, 0, st>>>(pc, a);
 }
 
 // ----------------------------------------------------------------------------- vote + ratio test

@@ -130,6 +130,7 @@ struct ValidateArgs {
     GridIndex gi;
     double cos_thresh, parallel_deg, delta;
     int rows, cols, n_vali;
+    int strict;                               // reference libm call order for the view-2 wedge (cvx_config.strict_libm_order)
     // outputs
     int32_t* support; int64_t sup_stride;     // [V][sup_stride] indexed by unique hypothesis
     double2* w32_out; double2* tgt_out;       // optional (parity intermediates), [V][U]

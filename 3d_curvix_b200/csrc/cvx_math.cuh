@@ -178,6 +178,68 @@ CVX_HD int wedge_row(double x, double y, const double* F, double e1x, double e1y
     return 0;
 }
 
+// ---- the same wedge with the libm round trips removed (validation kernel: one call per unique hypothesis x view).
+// getOreListBar goes angle -> (asin, atan) -> sincos -> point and slope -> atan -> cos; algebraically
+//   cos(atan(t)) = 1/sqrt(1+t^2),  (cos,sin)(atan(dy/dx)) = (|dx|, sgn(dy/dx)|dy|)/r,  (sin,cos)(asin(u)) = (u, sqrt(1-u^2)),
+// and the MIN/MAX ordering of the two epipolar-line angles follows from their slopes (atan is monotone).  What remains of libm
+// are the four atan that produce the wedge bounds themselves, in the reference's expression.  The bounds agree with wedge_row to
+// a few ulp (the same order as the glibc / libdevice difference of the libm chain, ~1e-13 degrees); the degenerate cases (NaN,
+// != 2 border crossings) are the same expressions.  cvx_config.strict_libm_order = 1 selects wedge_row in the kernel instead.
+CVX_HD bool ore_less(double t1, double t2) {   // ore(t) = atan(t) in [0,90) for t >= 0, atan(t) + 180 in (90,180) for t < 0
+    const bool n1 = t1 < 0, n2 = t2 < 0;
+    return (n1 == n2) ? (t1 < t2) : n2;
+}
+CVX_HD void wedge_border_slopes_fast(double px, double py, double dlt, double e2x, double e2y, int cols, double* sp, double* sn) {
+    double slope_p, slope_n;
+    if (px == 0 || px == double(cols)) {                          // :246 vertical border: shift in y
+        const double fdx = px - e2x;
+        slope_p = (py - e2y - dlt) / fdx;
+        slope_n = (py - e2y + dlt) / fdx;
+    } else {                                                      // shift in x
+        const double fdy = py - e2y;
+        slope_p = fdy / (px - e2x - dlt);
+        slope_n = fdy / (px - e2x + dlt);
+    }
+    *sp = cvx_atan(slope_p) / M_PI * 180;
+    *sn = cvx_atan(slope_n) / M_PI * 180;
+}
+CVX_HD int wedge_row_fast(double x, double y, const double* F, double e1x, double e1y, double e2x, double e2y, double delta, int rows,
+                          int cols, double* lo, double* hi) {
+    const double dy = y - e1y, dx = x - e1x;                      // :54-55
+    const double r2 = dy * dy + dx * dx;
+    const double d12 = sqrt(r2 - delta * delta);                  // :58-60 (NaN when the edge is inside the disc)
+    const double st = delta / d12, ct = sqrt((d12 - delta) * (d12 + delta)) / d12;   // sin / cos of asin(delta / d12) (NaN when delta > d12)
+    const double ir = 1.0 / sqrt(r2);
+    const double ca = fabs(dx) * ir;                              // cos / sin of atan(dy / dx)
+    const double sa = ((dy < 0) != (dx < 0)) ? -(fabs(dy) * ir) : fabs(dy) * ir;
+    const double c1 = ca * ct - sa * st, s1 = sa * ct + ca * st;  // ang + th
+    const double c2 = ca * ct + sa * st, s2 = sa * ct - ca * st;  // ang - th
+    double dx1 = fabs(c1 * d12), dy1 = fabs(s1 * d12), dx2 = fabs(c2 * d12), dy2 = fabs(s2 * d12);
+    if (dx < 0) { dx1 = -dx1; dx2 = -dx2; }                       // :87
+    if (dy < 0) { dy1 = -dy1; dy2 = -dy2; }                       // :92
+    const double p1x = dx1 + e1x, p1y = dy1 + e1y, p2x = dx2 + e1x, p2y = dy2 + e1y;   // :102-106
+    const double A1 = (F[0] * p1x + F[1] * p1y) + F[2], B1 = (F[3] * p1x + F[4] * p1y) + F[5], C1 = (F[6] * p1x + F[7] * p1y) + F[8];  // :109
+    const double A2 = (F[0] * p2x + F[1] * p2y) + F[2], B2 = (F[3] * p2x + F[4] * p2y) + F[5], C2 = (F[6] * p2x + F[7] * p2y) + F[8];  // :115
+    const double t1 = B1 / A1, t2 = B2 / A2;                      // slopes whose atan the reference orders (:121-139)
+    const double k1 = delta / sqrt(1.0 + t1 * t1), k2 = delta / sqrt(1.0 + t2 * t2);   // |cos(atan t)| * delta (:243)
+    const bool first_lo = ore_less(t1, t2);
+    const double dlt_lo = first_lo ? k1 : k2, dlt_hi = first_lo ? k2 : k1;
+    double q1x, q1y, q2x, q2y;
+    int flag = 0;
+    if (!wedge_border_point(A1, B1, C1, rows, cols, e2x, e2y, &q1x, &q1y)) flag |= 1;
+    if (!wedge_border_point(A2, B2, C2, rows, cols, e2x, e2y, &q2x, &q2y)) flag |= 2;
+    const double qnan = nan("");
+    if (flag) { *lo = qnan; *hi = qnan; return flag; }
+    double s[4];
+    wedge_border_slopes_fast(q1x, q1y, dlt_lo, e2x, e2y, cols, &s[0], &s[1]);   // line 1 is shifted with the MIN angle (:243)
+    wedge_border_slopes_fast(q2x, q2y, dlt_hi, e2x, e2y, cols, &s[2], &s[3]);   // line 2 with the MAX angle (:309)
+    for (int k = 0; k < 4; k++) if (s[k] < 0) s[k] = s[k] + 180;  // :337-348
+    if (s[0] != s[0] || s[1] != s[1] || s[2] != s[2] || s[3] != s[3]) { *lo = qnan; *hi = qnan; return 4; }
+    *lo = fmin(fmin(s[0], s[1]), fmin(s[2], s[3]));               // :349
+    *hi = fmax(fmax(s[0], s[1]), fmax(s[2], s[3]));               // :350
+    return 0;
+}
+
 // ---- epipolar correction of one view-2 candidate: PairEdgeHypo.cpp:225-293, util.cpp:68-106
 CVX_HD void epip_line_coeffs(const double* F, double x1, double y1, double* c) {   // util.cpp:68-78
     const double l0 = (F[0] * x1 + F[1] * y1) + F[2], l1 = (F[3] * x1 + F[4] * y1) + F[5], l2 = (F[6] * x1 + F[7] * y1) + F[8];

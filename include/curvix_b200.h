@@ -49,7 +49,8 @@ typedef struct cvx_config {
     int32_t img_cols;                  /* YAML Image_Cols */
     int32_t max_support_views;         /* YAML Max_Num_Of_Support_Views (must be >= 1) */
     int32_t max_cluster_size;          /* MAX_CLUSTER_SIZE (10)                       definitions.h:25 */
-    int32_t reserved;
+    int32_t strict_libm_order;   /* 0 (default): the validation kernel evaluates the view-2 wedge with the libm round trips
+                                  * removed (wedge_row_fast, bounds equal to a few ulp); 1: the reference's libm call order */
 } cvx_config;
 
 /* Sizes of the variable-length outputs of the last cvx_run_edge_sketch + run statistics. */

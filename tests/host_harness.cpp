@@ -12,6 +12,10 @@ int hh_wedge_row(double x, double y, const double* F, const double* e1, const do
                  double* hi) {
     return wedge_row(x, y, F, e1[0], e1[1], e2[0], e2[1], delta, rows, cols, lo, hi);
 }
+int hh_wedge_row_fast(double x, double y, const double* F, const double* e1, const double* e2, double delta, int rows, int cols, double* lo,
+                      double* hi) {
+    return wedge_row_fast(x, y, F, e1[0], e1[1], e2[0], e2[1], delta, rows, cols, lo, hi);
+}
 double hh_ore_angle(double x, double y, double ex, double ey) { return ore_angle(x, y, ex, ey); }
 int hh_correct_one(const double* F21, double x1, double y1, double x2, double y2, double th2, double loc, double tang, double orient,
                    double* cx, double* cy) {

@@ -48,6 +48,37 @@ def test_wedge_and_angle_bit_exact(oracle_mod, host_harness, tiny_scene):
     assert n_flag < 750   # not everything degenerate
 
 
+def test_fast_wedge_agrees_with_reference_order(oracle_mod, host_harness, tiny_scene, abc_scene):
+    """wedge_row_fast (libm round trips removed; the validation kernel's default) against the reference-order wedge_row:
+    same degenerate set, bounds equal to libm-noise level (well inside parity.ABS_ANGLE = 1e-10 degrees)."""
+    host_harness.hh_wedge_row.argtypes = [D, D, PD, PD, PD, D, C.c_int, C.c_int, PD, PD]
+    host_harness.hh_wedge_row_fast.argtypes = [D, D, PD, PD, PD, D, C.c_int, C.c_int, PD, PD]
+    worst, n_ok, n_flag, worst_at, worst_far = 0.0, 0, 0, None, 0.0
+    rng = np.random.default_rng(3)
+    for scene, pairs in ((tiny_scene[0], [(0, 1), (0, 3), (1, 5), (2, 7), (6, 0)]), (abc_scene, [(47, 42), (42, 14), (28, 48), (0, 40), (9, 39)])):
+        for (a, b) in pairs:
+            _, _, F, e1, e2 = _geom(oracle_mod, scene, a, b)
+            pts = [tuple(e[:2]) for e in scene.edges[a][:400]]
+            pts += [(e1[0] + dx, e1[1] + dy) for dx, dy in rng.normal(0, 1.0, (40, 2))]        # around / inside the disc about the epipole
+            pts += [(float(x), float(y)) for x, y in rng.uniform(0, scene.cols, (200, 2))]
+            for x, y in pts:
+                lo = D(); hi = D(); lo2 = D(); hi2 = D()
+                f1 = host_harness.hh_wedge_row(x, y, _p(F), _p(e1), _p(e2), 0.4, scene.rows, scene.cols, C.byref(lo), C.byref(hi))
+                f2 = host_harness.hh_wedge_row_fast(x, y, _p(F), _p(e1), _p(e2), 0.4, scene.rows, scene.cols, C.byref(lo2), C.byref(hi2))
+                assert f1 == f2, (x, y, f1, f2)
+                n_flag += bool(f1)
+                if not f1:
+                    d = max(abs(lo.value - lo2.value), abs(hi.value - hi2.value))
+                    if d > worst:
+                        worst, worst_at = d, (x, y, float(np.hypot(x - e1[0], y - e1[1])), lo.value, hi.value)
+                    if np.hypot(x - e1[0], y - e1[1]) > 5.0:
+                        worst_far = max(worst_far, d)
+                    n_ok += 1
+    # within a few pixels of the epipole the wedge is tens of degrees wide and both formulations are ill-conditioned
+    assert worst_far < 2e-12, worst_far
+    assert n_ok > 2000 and worst < 1e-10, (n_ok, n_flag, worst, worst_at)
+
+
 def test_correction_reprojection_bit_exact(oracle_mod, host_harness, tiny_scene):
     scene, _ = tiny_scene
     olib = oracle_mod.load()

@@ -75,6 +75,23 @@ def test_abc_nef_first_pass_parity(oracle_mod, abc_scene):
     assert rep["n_pairs_compared"] >= 0.97 * rep["n_pairs_oracle"]
 
 
+def test_strict_libm_order_switch(oracle_mod, abc_scene):
+    """cvx_config.strict_libm_order = 1: the validation kernel evaluates the view-2 wedge in the reference's libm call order
+    (wedge_row) instead of wedge_row_fast; both must satisfy the parity rule, and they select the same pairs on this pass."""
+    o = make_oracle(oracle_mod, abc_scene)
+    o.set_pair(47, 42); o.run(mode=1, keep=True)
+    sel = []
+    for strict in (1, 0):
+        g = _gpu(abc_scene, strict_libm_order=strict)
+        g.set_pair(47, 42); g.run()
+        rep = compare(o, g, check_intermediates=True)
+        _report(f"abc_47_42_strict{strict}", rep)
+        p = g.pairs()
+        sel.append(np.stack([p["h1"], p["h2rep"]], 1))
+        g.close()
+    assert np.array_equal(sel[0], sel[1])
+
+
 def test_abc_nef_other_pairs(oracle_mod, abc_scene):
     o = make_oracle(oracle_mod, abc_scene)
     g = _gpu(abc_scene)
