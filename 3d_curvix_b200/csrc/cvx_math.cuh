@@ -190,18 +190,19 @@ CVX_HD bool ore_less(double t1, double t2) {   // ore(t) = atan(t) in [0,90) for
     return (n1 == n2) ? (t1 < t2) : n2;
 }
 CVX_HD void wedge_border_slopes_fast(double px, double py, double dlt, double e2x, double e2y, int cols, double* sp, double* sn) {
-    double slope_p, slope_n;
     if (px == 0 || px == double(cols)) {                          // :246 vertical border: shift in y
         const double fdx = px - e2x;
-        slope_p = (py - e2y - dlt) / fdx;
-        slope_n = (py - e2y + dlt) / fdx;
+        *sp = (py - e2y - dlt) / fdx;
+        *sn = (py - e2y + dlt) / fdx;
     } else {                                                      // shift in x
         const double fdy = py - e2y;
-        slope_p = fdy / (px - e2x - dlt);
-        slope_n = fdy / (px - e2x + dlt);
+        *sp = fdy / (px - e2x - dlt);
+        *sn = fdy / (px - e2x + dlt);
     }
-    *sp = cvx_atan(slope_p) / M_PI * 180;
-    *sn = cvx_atan(slope_n) / M_PI * 180;
+}
+CVX_HD double ore_of_slope(double t) {                            // :337-348: atan / M_PI * 180, + 180 if negative
+    const double a = cvx_atan(t) / M_PI * 180;
+    return a < 0 ? a + 180 : a;
 }
 CVX_HD int wedge_row_fast(double x, double y, const double* F, double e1x, double e1y, double e2x, double e2y, double delta, int rows,
                           int cols, double* lo, double* hi) {
@@ -230,13 +231,15 @@ CVX_HD int wedge_row_fast(double x, double y, const double* F, double e1x, doubl
     if (!wedge_border_point(A2, B2, C2, rows, cols, e2x, e2y, &q2x, &q2y)) flag |= 2;
     const double qnan = nan("");
     if (flag) { *lo = qnan; *hi = qnan; return flag; }
-    double s[4];
-    wedge_border_slopes_fast(q1x, q1y, dlt_lo, e2x, e2y, cols, &s[0], &s[1]);   // line 1 is shifted with the MIN angle (:243)
-    wedge_border_slopes_fast(q2x, q2y, dlt_hi, e2x, e2y, cols, &s[2], &s[3]);   // line 2 with the MAX angle (:309)
-    for (int k = 0; k < 4; k++) if (s[k] < 0) s[k] = s[k] + 180;  // :337-348
-    if (s[0] != s[0] || s[1] != s[1] || s[2] != s[2] || s[3] != s[3]) { *lo = qnan; *hi = qnan; return 4; }
-    *lo = fmin(fmin(s[0], s[1]), fmin(s[2], s[3]));               // :349
-    *hi = fmax(fmax(s[0], s[1]), fmax(s[2], s[3]));               // :350
+    double m0, m1, m2, m3;                                        // the four slopes whose angles bound the wedge
+    wedge_border_slopes_fast(q1x, q1y, dlt_lo, e2x, e2y, cols, &m0, &m1);   // line 1 is shifted with the MIN angle (:243)
+    wedge_border_slopes_fast(q2x, q2y, dlt_hi, e2x, e2y, cols, &m2, &m3);   // line 2 with the MAX angle (:309)
+    if (m0 != m0 || m1 != m1 || m2 != m2 || m3 != m3) { *lo = qnan; *hi = qnan; return 4; }
+    // min / max of the four angles (:349-350) = angles of the extreme slopes in the ore order: two atan instead of four
+    const double a = ore_less(m1, m0) ? m1 : m0, b = ore_less(m3, m2) ? m3 : m2;
+    const double c = ore_less(m0, m1) ? m1 : m0, d = ore_less(m2, m3) ? m3 : m2;
+    *lo = ore_of_slope(ore_less(b, a) ? b : a);
+    *hi = ore_of_slope(ore_less(c, d) ? d : c);
     return 0;
 }
 
