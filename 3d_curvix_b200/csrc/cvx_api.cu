@@ -517,7 +517,7 @@ int cvx_run_edge_sketch(cvx_ctx* ctx, int h1_begin, int h1_end) {
     CU(cudaMemsetAsync(ctx->d_m.p, 0, E1a * 4, st)); CU(cudaMemsetAsync(ctx->d_n.p, 0, E1a * 4, st)); CU(cudaMemsetAsync(ctx->d_ncl.p, 0, E1a * 4, st));
     CU(cudaMemsetAsync(ctx->d_nvalid.p, 0, E1a * 4, st)); CU(cudaMemsetAsync(ctx->d_nsel.p, 0, E1a * 4, st));
     CU(cudaMemsetAsync(ctx->d_ctr.p, 0, sizeof(DevCounters), st));
-    CU(ctx->d_big_list.reserve(size_t(E1a) + 4));                     // clustering order of the view-1 edges + the 3 class counts
+    CU(ctx->d_big_list.reserve(size_t(E1a) + 8));                     // clustering order of the view-1 edges + the 5 class counts
     cudaEventRecord(ctx->ev[0], st);
     // ---- hypothesis formation
     launch_form_count(pc, x1, y1, h1_begin, h1_end, ctx->d_wedge_h1.p, x2, y2, th2, ctx->d_ang2.p, E2, ctx->h2ix, ctx->d_m.p, ctx->d_n.p, st);
@@ -536,9 +536,9 @@ int cvx_run_edge_sketch(cvx_ctx* ctx, int h1_begin, int h1_end) {
     for (auto* b : db) CU(b->reserve(Ha));
     RowTable rt = row_table(ctx);
     launch_form_fill(pc, x1, y1, h1_begin, h1_end, ctx->d_wedge_h1.p, x2, y2, th2, ctx->d_ang2.p, E2, ctx->h2ix, ctx->d_m.p, ctx->d_n.p, ctx->d_row_off.p, rt,
-                     ctx->d_ncl.p, ctx->d_big_list.p, ctx->d_big_list.p + E1a, st);
+                     ctx->d_ncl.p, ctx->d_big_list.p, ctx->d_big_list.p + E1a, st);   // order[E1], cnts[5]
     launch_scan_i32_i64(ctx->d_ncl.p, ctx->d_u_off.p, E1, st);
-    ctx->tm.kernel_launches += 6;
+    ctx->tm.kernel_launches += 8;
     cudaEventRecord(ctx->ev[1], st);
     int64_t U = 0;
     CU(cudaMemcpyAsync(&U, ctx->d_u_off.p + E1, 8, cudaMemcpyDeviceToHost, st));

@@ -502,7 +502,9 @@ struct ClusterSm {
     int16_t label[N], size[N], rank[N], mem[32];   // rank doubles as the cached merge partner during the merge phase
 };
 #define CL_N 128          // rows handled by the shared-memory path inside k_form
-#define CL_BIG_N 512      // rows handled by k_cluster_big (one warp per block, 52 KB of shared memory); beyond: global-memory fallback
+#define CL_MID_N 256      // size classes of the clustering launches: <= CL_N (4 warps per block), <= CL_MID_N (18 KB per warp),
+#define CL_BIG_N 512      // <= CL_BIG_N (one warp per block, 53 KB of shared memory), <= CL_HUGE_N (one warp per block, 171 KB: one block
+#define CL_HUGE_N 1024    // per SM); beyond: global-memory fallback
 #define FORM_WARPS 4
 
 // Gaussian-weighted average over the members s.mem[0..cnt) (ascending index): EdgeClusterer.cpp:60-125.  Lane k holds member k;
@@ -774,7 +776,7 @@ __device__ void cluster_warp_global(int n, const PassConst& pc, const double* xc
         gauss_avg_warp(n, xc, yc, thn, label, i, i, pc.cl_sigma, &gx, &gy, &gth);
         double md = DBL_MAX;
         int closest = -1;
-        for (int j = i; j < n; j++) {
+        for (int j = 0; j < n; j++) {                    // a cluster keeps the label of the row that absorbed it: members may precede the root
             if (label[j] == i) {
                 const double ddx = xc[j] - gx, ddy = yc[j] - gy;
                 const double dist = sqrt(ddx * ddx + ddy * ddy);
@@ -782,7 +784,7 @@ __device__ void cluster_warp_global(int n, const PassConst& pc, const double* xc
             }
         }
         const int rep = h2orig[closest];
-        for (int j = i + lane; j < n; j += 32)
+        for (int j = lane; j < n; j += 32)
             if (label[j] == i) { xbar[j] = gx; ybar[j] = gy; thbar[j] = gth; h2rep[j] = rep; }
     }
     __syncwarp();
@@ -906,21 +908,22 @@ __global__ void __launch_bounds__(FORM_WARPS * 32) k_form(const __grid_constant_
 // ---- clustering as its own launches (the formation kernel stays small enough for the instruction cache, and the clustering
 // kernels see the view-1 edges in DESCENDING order of their hypothesis count, so the long sequential merges start first).
 // k_order_by_n: one block; order[] = edges with 1 <= n <= CL_N sorted by n descending, then those with CL_N < n <= CL_BIG_N, then
-// the rest; cnts[0..2] = the three counts.
-#define ORDER_BUCKETS (CL_N + 2)
+// then CL_MID_N < n <= CL_BIG_N, then CL_BIG_N < n <= CL_HUGE_N, then the rest; cnts[0..4] = the five counts.
+#define ORDER_BUCKETS (CL_N + 4)
 __global__ void __launch_bounds__(1024) k_order_by_n(const int32_t* __restrict__ n_of, int h1_begin, int h1_end, int max_cluster,
                                                      int32_t* __restrict__ order, int32_t* __restrict__ cnts) {
     __shared__ int hist[ORDER_BUCKETS];
     for (int k = threadIdx.x; k < ORDER_BUCKETS; k += blockDim.x) hist[k] = 0;
     __syncthreads();
     const bool sm_ok = max_cluster <= 32;          // the shared-memory algorithm keeps member lists of at most 32
-    auto key = [&](int n) { return (!sm_ok || n > CL_BIG_N) ? CL_N + 1 : n > CL_N ? CL_N : CL_N - n; };
+    auto key = [&](int n) { return (!sm_ok || n > CL_HUGE_N) ? CL_N + 3 : n > CL_BIG_N ? CL_N + 2 : n > CL_MID_N ? CL_N + 1 : n > CL_N ? CL_N : CL_N - n; };
     for (int i = h1_begin + threadIdx.x; i < h1_end; i += blockDim.x) { const int n = n_of[i]; if (n > 0) atomicAdd(&hist[key(n)], 1); }
     __syncthreads();
     if (threadIdx.x == 0) {
         int run = 0, ns = 0;
         for (int k = 0; k < ORDER_BUCKETS; k++) { const int c = hist[k]; hist[k] = run; run += c; if (k == CL_N - 1) ns = run; }
-        cnts[0] = ns; cnts[1] = hist[CL_N + 1] - ns; cnts[2] = run - hist[CL_N + 1];
+        cnts[0] = ns; cnts[1] = hist[CL_N + 1] - ns; cnts[2] = hist[CL_N + 2] - hist[CL_N + 1];
+        cnts[3] = hist[CL_N + 3] - hist[CL_N + 2]; cnts[4] = run - hist[CL_N + 3];
     }
     __syncthreads();
     for (int i = h1_begin + threadIdx.x; i < h1_end; i += blockDim.x) { const int n = n_of[i]; if (n > 0) order[atomicAdd(&hist[key(n)], 1)] = i; }
@@ -932,7 +935,9 @@ __global__ void __launch_bounds__(WARPS * 32) k_cluster(const __grid_constant__ 
     extern __shared__ __align__(16) unsigned char cl_smem[];
     ClusterSm<N>& s = reinterpret_cast<ClusterSm<N>*>(cl_smem)[threadIdx.x >> 5];
     const int lane = threadIdx.x & 31;
-    const int base = which ? cnts[0] : 0, cnt = cnts[which];
+    int base = 0;
+    for (int k = 0; k < which; k++) base += cnts[k];
+    const int cnt = cnts[which];
     for (int b = blockIdx.x * WARPS + (threadIdx.x >> 5); b < cnt; b += gridDim.x * WARPS) {
         const int h1 = order[base + b];
         const int64_t row0 = row_off[h1];
@@ -944,7 +949,7 @@ __global__ void __launch_bounds__(WARPS * 32) k_cluster(const __grid_constant__ 
 __global__ void __launch_bounds__(32) k_cluster_huge(const __grid_constant__ PassConst pc, const int32_t* __restrict__ order,
                                                      const int32_t* __restrict__ cnts, const int32_t* __restrict__ n_of,
                                                      const int64_t* __restrict__ row_off, RowTable rt, int32_t* n_clusters) {
-    const int base = cnts[0] + cnts[1], cnt = cnts[2];
+    const int base = cnts[0] + cnts[1] + cnts[2] + cnts[3], cnt = cnts[4];
     for (int b = blockIdx.x; b < cnt; b += gridDim.x) {
         const int h1 = order[base + b];
         const int64_t row0 = row_off[h1];
@@ -977,10 +982,14 @@ void launch_form_fill(const PassConst& pc, const double* x1, const double* y1, i
     int32_t* order = big_list;
     int32_t* cnts = big_count;
     k_order_by_n<<<1, 1024, 0, st>>>(n_of, h1_begin, h1_end, pc.max_cluster, order, cnts);
-    const size_t sm_small = FORM_WARPS * sizeof(ClusterSm<CL_N>), sm_big = sizeof(ClusterSm<CL_BIG_N>);
+    const size_t sm_small = FORM_WARPS * sizeof(ClusterSm<CL_N>), sm_mid = 2 * sizeof(ClusterSm<CL_MID_N>), sm_big = sizeof(ClusterSm<CL_BIG_N>);
     cudaFuncSetAttribute(k_cluster<CL_BIG_N, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sm_big));   // per device, cheap
     k_cluster<CL_N, FORM_WARPS><<<(n + FORM_WARPS - 1) / FORM_WARPS, FORM_WARPS * 32, sm_small, st>>>(pc, order, cnts, 0, n_of, row_off, rt, n_clusters);
-    k_cluster<CL_BIG_N, 1><<<std::min(n, 148 * 4), 32, sm_big, st>>>(pc, order, cnts, 1, n_of, row_off, rt, n_clusters);
+    k_cluster<CL_MID_N, 2><<<std::min((n + 1) / 2, 148 * 6), 64, sm_mid, st>>>(pc, order, cnts, 1, n_of, row_off, rt, n_clusters);
+    k_cluster<CL_BIG_N, 1><<<std::min(n, 148 * 4), 32, sm_big, st>>>(pc, order, cnts, 2, n_of, row_off, rt, n_clusters);
+    const size_t sm_huge = sizeof(ClusterSm<CL_HUGE_N>);
+    cudaFuncSetAttribute(k_cluster<CL_HUGE_N, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sm_huge));
+    k_cluster<CL_HUGE_N, 1><<<std::min(n, 148), 32, sm_huge, st>>>(pc, order, cnts, 3, n_of, row_off, rt, n_clusters);
     k_cluster_huge<<<std::min(n, 148 * 4), 32, 0, st>>>(pc, order, cnts, n_of, row_off, rt, n_clusters);
 }
 

@@ -201,3 +201,61 @@ def test_abc_against_committed_goldens(abc_scene):
     assert np.max(np.abs(a - b) / np.maximum(np.linalg.norm(b, axis=1, keepdims=True), 1e-12)) <= 1e-6
     a, b = f["tangent_world"][idx_s], g["tangent_world"][idx_g]
     assert np.max(np.abs(a - b)) <= 1e-6
+
+
+def test_full_size_properties_cfg4(oracle_mod, data_mod):
+    """BASELINE.json config 4 at full size (100 views x 50k edges/view, one pair): the oracle cannot finish this in seconds, so
+    the size-independent properties are checked instead -- determinism (two runs identical), exact view-1-range sharding,
+    vote consistency of every accepted pair, finite unit tangents -- and a bounded view-1 range is compared with the oracle."""
+    w = data_mod.workload("cfg4")
+    scene = data_mod.make_synthetic_scene(**w["scene"])
+    api = pkg("api")
+    cfg = api.default_config(n_views=scene.n_views, img_rows=scene.rows, img_cols=scene.cols, max_support_views=w["max_support_views"])
+    g = api.EdgeSketch(cfg, 0)
+    g.set_cameras(scene.R, scene.T, scene.K)
+    g.set_all_view_edges(scene.edges)
+    g.set_pair(0, 1)
+    E1 = g.n_edges[0]
+    g.run(); c = g.counts(); full = g.pairs(); fin = g.finalize()
+    assert c["n_validations"] == c["n_hypotheses"] * (scene.n_views - 2) and c["n_hypotheses"] > 10_000_000
+    g.run(); again = g.pairs(); fin2 = g.finalize()
+    for k in ("h1", "h2rep", "count", "supports"):
+        assert np.array_equal(full[k], again[k]), k
+    assert np.array_equal(fin["gamma_world"], fin2["gamma_world"], equal_nan=True)
+    parts = []
+    for (a, b) in [(0, E1 // 2), (E1 // 2, E1)]:
+        g.run(a, b); parts.append((g.pairs(), g.finalize()))
+    for k in ("h1", "h2rep", "count", "supports"):
+        assert np.array_equal(np.concatenate([p[0][k] for p in parts]), full[k]), k
+    assert np.array_equal(np.concatenate([p[1]["tangent_world"] for p in parts]), fin["tangent_world"], equal_nan=True)
+    # vote consistency: count = number of supporting views >= N_support; support indices address real edges of their view
+    sup = full["supports"]
+    assert np.array_equal((sup != -2).sum(1), full["count"]) and (full["count"] >= w["max_support_views"]).all()
+    vali = [v for v in range(scene.n_views) if v not in (0, 1)]
+    for j, v in enumerate(vali[:8]):
+        s = sup[:, j]
+        assert ((s == -2) | ((s >= 0) & (s < len(scene.edges[v])))).all()
+    ok = fin["nan_flag"] == 0
+    tn = np.linalg.norm(fin["tangent_world"][ok], axis=1)
+    assert ok.mean() > 0.99 and np.allclose(tn, 1.0, atol=1e-9)
+    # bounded oracle comparison on the same full-size scene
+    o = make_oracle(oracle_mod, scene, max_support_views=w["max_support_views"])
+    o.set_pair(0, 1); o.run(0, 24, mode=1, keep=True)
+    g.keep_intermediates(True)
+    g.run(0, 24)
+    rep = compare(o, g, check_intermediates=True)
+    _report("cfg4_0_1_h1_0_24", rep)
+    g.close()
+
+
+def test_global_memory_clustering_fallback(oracle_mod, tiny_scene):
+    """MAX_CLUSTER_SIZE > 32 (member lists no longer fit a warp) routes every hypothesis group to the global-memory clustering
+    fallback -- the same path groups of more than 1024 rows take; it must reproduce the oracle's merge order as well."""
+    scene, w = tiny_scene
+    o = make_oracle(oracle_mod, scene, max_support_views=w["max_support_views"], max_cluster_size=40)
+    g = _gpu(scene, max_support_views=w["max_support_views"], max_cluster_size=40)
+    o.set_pair(0, 1); o.run(mode=1, keep=True)
+    g.set_pair(0, 1); g.run()
+    rep = compare(o, g, check_intermediates=True)
+    _report("tiny_0_1_maxcluster40", rep)
+    assert rep["counts_gpu"]["n_hypotheses"] > 0
