@@ -334,7 +334,13 @@ CVX_HD void smallest_eigvec4(double a[4][4], double* out) {
         double off = 0;
         for (int p = 0; p < 4; p++) for (int q = p + 1; q < 4; q++) off += a[p][q] * a[p][q];
         if (off == 0.0) break;
+#if defined(__CUDA_ARCH__)
+#pragma unroll   // static (p, q): the two 4x4 matrices stay in registers instead of local memory
+#endif
         for (int p = 0; p < 3; p++)
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
             for (int q = p + 1; q < 4; q++) {
                 if (a[p][q] == 0.0) continue;
                 const double theta = (a[q][q] - a[p][p]) / (2.0 * a[p][q]);
@@ -345,9 +351,12 @@ CVX_HD void smallest_eigvec4(double a[4][4], double* out) {
                 for (int k = 0; k < 4; k++) { const double x = v[k][p], y = v[k][q]; v[k][p] = c * x - s * y; v[k][q] = s * x + c * y; }
             }
     }
-    int best = 0;
-    for (int k = 1; k < 4; k++) if (a[k][k] < a[best][best]) best = k;
-    for (int k = 0; k < 4; k++) out[k] = v[k][best];
+    int best = 0;                                   // smallest diagonal entry, first minimum; static indexing only (registers)
+    double bv = a[0][0];
+    if (a[1][1] < bv) { bv = a[1][1]; best = 1; }
+    if (a[2][2] < bv) { bv = a[2][2]; best = 2; }
+    if (a[3][3] < bv) { bv = a[3][3]; best = 3; }
+    for (int k = 0; k < 4; k++) out[k] = best == 0 ? v[k][0] : best == 1 ? v[k][1] : best == 2 ? v[k][2] : v[k][3];
 }
 CVX_HD void triangulate2(double x1, double y1, double x2, double y2, const double* R21, const double* T21, const double* Kinv, double* G) {
     double g1[3], g2[3];

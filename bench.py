@@ -527,7 +527,7 @@ def run_support_stress(args, rank, world, local_rank):
                     "ms_per_step": 1e3 * e2e_s, "timer": "host wall clock around create (pageable host arrays -> device, staging) + run + result, one step"},
             "gpu_launches": args.steps, "wall_s_timed_region": wall,
             "roofline": {"bound": "hbm", "kernel": "k_validate<true>", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-                         "traffic": traffic("k_validate<true>"), "peak_source": peak_src, "kernel_ms": ms_per_step, "algorithmic_bytes": abytes,
+                         "traffic": traffic("k_validate<true>", V), "peak_source": peak_src, "kernel_ms": ms_per_step, "algorithmic_bytes": abytes,
                          "bytes_formula": "validations x 52 + 16 x wedge-intersection members + 32 x staged edges (SURVEY.md 8d)",
                          "mean_intersection": n_bar, "entries_visited_per_validation": stats["n_visited"] / vals},
             "counts_rank0": dict(stats, n_validations=vals, n_rows=H, n_edges=int(prob["view_off"][-1])), "create_s": create_s}
@@ -558,12 +558,15 @@ def run_support_stress(args, rank, world, local_rank):
         tdist.destroy_process_group()
 
 
-def traffic(kernel):
+def traffic(kernel, views=0):
     """dram__bytes_read.sum + dram__bytes_write.sum of one launch of `kernel`, from the committed ncu --set full capture
     (profiles/traffic.json, written by scripts/ncu_summary.py from the .ncu-rep of the same bench command), else None."""
     p = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(p):
-        return json.load(open(p)).get(kernel, {}).get("bytes")
+        e = json.load(open(p)).get(kernel, {})
+        if "bytes_per_view" in e and views:
+            return e["bytes_per_view"] * views
+        return e.get("bytes")
     return None
 
 
