@@ -95,6 +95,8 @@ struct cvx_ctx {
     cvx_config cfg;
     int device = 0;
     cudaStream_t stream = nullptr;
+    cudaStream_t stream2 = nullptr;             // side stream: the clustering launches of the larger size classes run beside the small one
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     std::string err;
     // cameras (host)
     int n_views = 0;
@@ -281,6 +283,8 @@ int cvx_create(const cvx_config* cfg, int device, cvx_ctx** out) {
         return CVX_ERR_CUDA;
     }
     for (auto& e : ctx->ev) cudaEventCreate(&e);
+    cudaStreamCreateWithFlags(&ctx->stream2, cudaStreamNonBlocking);
+    cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming); cudaEventCreateWithFlags(&ctx->ev_join, cudaEventDisableTiming);
     if (ctx->d_ctr.reserve(1) != cudaSuccess) { delete ctx; return CVX_ERR_NOMEM; }
     *out = ctx;
     return CVX_OK;
@@ -310,6 +314,9 @@ int cvx_destroy(cvx_ctx* ctx) {
     ctx->d_claim_cnt.release(); ctx->d_claim_mask.release();
     for (auto& e : ctx->ev) cudaEventDestroy(e);
     cudaStreamDestroy(ctx->stream);
+    if (ctx->stream2) cudaStreamDestroy(ctx->stream2);
+    if (ctx->ev_fork) cudaEventDestroy(ctx->ev_fork);
+    if (ctx->ev_join) cudaEventDestroy(ctx->ev_join);
     delete ctx;
     return CVX_OK;
 }
@@ -536,7 +543,7 @@ int cvx_run_edge_sketch(cvx_ctx* ctx, int h1_begin, int h1_end) {
     for (auto* b : db) CU(b->reserve(Ha));
     RowTable rt = row_table(ctx);
     launch_form_fill(pc, x1, y1, h1_begin, h1_end, ctx->d_wedge_h1.p, x2, y2, th2, ctx->d_ang2.p, E2, ctx->h2ix, ctx->d_m.p, ctx->d_n.p, ctx->d_row_off.p, rt,
-                     ctx->d_ncl.p, ctx->d_big_list.p, ctx->d_big_list.p + E1a, st);   // order[E1], cnts[5]
+                     ctx->d_ncl.p, ctx->d_big_list.p, ctx->d_big_list.p + E1a, st, ctx->stream2, ctx->ev_fork, ctx->ev_join);   // order[E1], cnts[5]
     launch_scan_i32_i64(ctx->d_ncl.p, ctx->d_u_off.p, E1, st);
     ctx->tm.kernel_launches += 8;
     cudaEventRecord(ctx->ev[1], st);

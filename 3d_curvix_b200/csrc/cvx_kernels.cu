@@ -971,7 +971,7 @@ void launch_form_count(const PassConst& pc, const double* x1, const double* y1, 
 void launch_form_fill(const PassConst& pc, const double* x1, const double* y1, int h1_begin, int h1_end, const double2* wedge_h1,
                       const double* x2, const double* y2, const double* th2, const double* ang2, int E2, AngleIndex ix, const int32_t* m_of,
                       const int32_t* n_of, const int64_t* row_off, RowTable rt, int32_t* n_clusters, int32_t* big_list, int32_t* big_count,
-                      cudaStream_t st) {
+                      cudaStream_t st, cudaStream_t side, cudaEvent_t ev_fork, cudaEvent_t ev_join) {
     const int n = h1_end - h1_begin;
     if (n <= 0) return;
     const size_t smem = FORM_WARPS * 2 * FORM_CAND_CAP * sizeof(int32_t);
@@ -984,13 +984,18 @@ void launch_form_fill(const PassConst& pc, const double* x1, const double* y1, i
     k_order_by_n<<<1, 1024, 0, st>>>(n_of, h1_begin, h1_end, pc.max_cluster, order, cnts);
     const size_t sm_small = FORM_WARPS * sizeof(ClusterSm<CL_N>), sm_mid = 2 * sizeof(ClusterSm<CL_MID_N>), sm_big = sizeof(ClusterSm<CL_BIG_N>);
     cudaFuncSetAttribute(k_cluster<CL_BIG_N, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sm_big));   // per device, cheap
-    k_cluster<CL_N, FORM_WARPS><<<(n + FORM_WARPS - 1) / FORM_WARPS, FORM_WARPS * 32, sm_small, st>>>(pc, order, cnts, 0, n_of, row_off, rt, n_clusters);
-    k_cluster<CL_MID_N, 2><<<std::min((n + 1) / 2, 148 * 6), 64, sm_mid, st>>>(pc, order, cnts, 1, n_of, row_off, rt, n_clusters);
-    k_cluster<CL_BIG_N, 1><<<std::min(n, 148 * 4), 32, sm_big, st>>>(pc, order, cnts, 2, n_of, row_off, rt, n_clusters);
     const size_t sm_huge = sizeof(ClusterSm<CL_HUGE_N>);
     cudaFuncSetAttribute(k_cluster<CL_HUGE_N, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sm_huge));
-    k_cluster<CL_HUGE_N, 1><<<std::min(n, 148), 32, sm_huge, st>>>(pc, order, cnts, 3, n_of, row_off, rt, n_clusters);
-    k_cluster_huge<<<std::min(n, 148 * 4), 32, 0, st>>>(pc, order, cnts, n_of, row_off, rt, n_clusters);
+    // the few long-running edges of the larger classes go to a side stream and run beside the many small ones (fork / join)
+    cudaStream_t big = side ? side : st;
+    if (side) { cudaEventRecord(ev_fork, st); cudaStreamWaitEvent(side, ev_fork, 0); }
+    k_cluster<CL_HUGE_N, 1><<<std::min(n, 148), 32, sm_huge, big>>>(pc, order, cnts, 3, n_of, row_off, rt, n_clusters);
+    k_cluster<CL_BIG_N, 1><<<std::min(n, 148 * 4), 32, sm_big, big>>>(pc, order, cnts, 2, n_of, row_off, rt, n_clusters);
+    k_cluster<CL_MID_N, 2><<<std::min((n + 1) / 2, 148 * 6), 64, sm_mid, big>>>(pc, order, cnts, 1, n_of, row_off, rt, n_clusters);
+    k_cluster_huge<<<std::min(n, 148 * 4), 32, 0, big>>>(pc, order, cnts, n_of, row_off, rt, n_clusters);
+    if (side) cudaEventRecord(ev_join, side);
+    k_cluster<CL_N, FORM_WARPS><<<(n + FORM_WARPS - 1) / FORM_WARPS, FORM_WARPS * 32, sm_small, st>>>(pc, order, cnts, 0, n_of, row_off, rt, n_clusters);
+    if (side) cudaStreamWaitEvent(st, ev_join, 0);
 }
 
 // ----------------------------------------------------------------------------- unique-hypothesis table

@@ -106,7 +106,7 @@ void launch_form_count(const PassConst& pc, const double* x1, const double* y1, 
 void launch_form_fill(const PassConst& pc, const double* x1, const double* y1, int h1_begin, int h1_end, const double2* wedge_h1,
                       const double* x2, const double* y2, const double* th2, const double* ang2, int E2, AngleIndex ix, const int32_t* m_of,
                       const int32_t* n_of, const int64_t* row_off, RowTable rt, int32_t* n_clusters, int32_t* big_list, int32_t* big_count,
-                      cudaStream_t st);
+                      cudaStream_t st, cudaStream_t side, cudaEvent_t ev_fork, cudaEvent_t ev_join);
 // unique-hypothesis table from the clustered rows (+ view-independent reprojection terms)
 void launch_uniq_fill(const PassConst& pc, const double* x1, const double* y1, const double* th1, RowTable rt, int64_t H,
                       const int64_t* row_off, const int64_t* u_off, UniqTable ut, cudaStream_t st);
