@@ -423,22 +423,42 @@ __global__ void k_h2_hist(const double* __restrict__ ang, int n, AngleIndex ix, 
     bin_of[i] = b;
     atomicAdd(&ix.bin_end[b], 1);
 }
-__global__ void __launch_bounds__(1024) k_scan_bins1(int32_t* b, int n) {   // in-place exclusive scan, one block
-    __shared__ int part[1024];
-    const int per = (n + 1023) / 1024;
+// exclusive scan of the 1024 per-thread partial sums of a block: two levels of warp shuffles, two barriers
+template <typename T>
+__device__ __forceinline__ T block_excl_scan_1024(T mine, T* sh /* 32 */) {
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    T inc = mine;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const T t = __shfl_up_sync(FULL, inc, o); if (lane >= o) inc += t; }
+    if (lane == 31) sh[wid] = inc;
+    __syncthreads();
+    if (wid == 0) {
+        const T w = sh[lane];
+        T winc = w;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const T t = __shfl_up_sync(FULL, winc, o); if (lane >= o) winc += t; }
+        sh[lane] = winc - w;
+    }
+    __syncthreads();
+    return sh[wid] + inc - mine;
+}
+__global__ void __launch_bounds__(1024) k_scan_bins1(int32_t* b, int n) {   // in-place exclusive scan, one block, int4 traffic
+    __shared__ int sh[32];
+    const int per = (((n + 1023) / 1024) + 3) & ~3;                          // multiple of 4: every thread's run is 16-byte aligned
     const int lo = min(int(threadIdx.x) * per, n), hi = min(lo + per, n);
     int s = 0;
-    for (int i = lo; i < hi; i++) s += b[i];
-    part[threadIdx.x] = s;
-    __syncthreads();
-    for (int d = 1; d < 1024; d <<= 1) {
-        const int t = (threadIdx.x >= d) ? part[threadIdx.x - d] : 0;
-        __syncthreads();
-        part[threadIdx.x] += t;
-        __syncthreads();
+    int i = lo;
+    for (; i + 3 < hi; i += 4) { const int4 q = *reinterpret_cast<const int4*>(b + i); s += (q.x + q.y) + (q.z + q.w); }
+    for (; i < hi; i++) s += b[i];
+    int run = block_excl_scan_1024<int>(s, sh);
+    i = lo;
+    for (; i + 3 < hi; i += 4) {
+        const int4 q = *reinterpret_cast<const int4*>(b + i);
+        int4 o;
+        o.x = run; o.y = o.x + q.x; o.z = o.y + q.y; o.w = o.z + q.z; run = o.w + q.w;
+        *reinterpret_cast<int4*>(b + i) = o;
     }
-    int run = part[threadIdx.x] - s;
-    for (int i = lo; i < hi; i++) { const int c = b[i]; b[i] = run; run += c; }
+    for (; i < hi; i++) { const int c = b[i]; b[i] = run; run += c; }
 }
 __global__ void k_h2_scatter(const double* __restrict__ ang, int n, AngleIndex ix, const int32_t* __restrict__ bin_of) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -469,22 +489,14 @@ void launch_h1_wedges(const PassConst& pc, const double* x1, const double* y1, i
 
 // ----------------------------------------------------------------------------- scan
 __global__ void __launch_bounds__(1024) k_scan_i32_i64(const int32_t* __restrict__ in, int64_t* __restrict__ out, int n) {
-    __shared__ long long part[1024];
+    __shared__ long long sh[32];
     const int per = (n + 1023) / 1024;
     const int lo = min(int(threadIdx.x) * per, n), hi = min(lo + per, n);
     long long s = 0;
     for (int i = lo; i < hi; i++) s += in[i];
-    part[threadIdx.x] = s;
-    __syncthreads();
-    for (int d = 1; d < 1024; d <<= 1) {
-        long long t = (threadIdx.x >= d) ? part[threadIdx.x - d] : 0;
-        __syncthreads();
-        part[threadIdx.x] += t;
-        __syncthreads();
-    }
-    long long run = part[threadIdx.x] - s;
+    long long run = block_excl_scan_1024<long long>(s, sh);
     for (int i = lo; i < hi; i++) { out[i] = run; run += in[i]; }
-    if (threadIdx.x == 1023) out[n] = part[1023];
+    if (threadIdx.x == 1023) out[n] = run;
 }
 void launch_scan_i32_i64(const int32_t* in, int64_t* out, int n, cudaStream_t st) { k_scan_i32_i64<<<1, 1024, 0, st>>>(in, out, n); }
 
