@@ -333,7 +333,8 @@ CVX_HD void smallest_eigvec4(double a[4][4], double* out) {
     for (int sweep = 0; sweep < 60; sweep++) {
         double off = 0;
         for (int p = 0; p < 4; p++) for (int q = p + 1; q < 4; q++) off += a[p][q] * a[p][q];
-        if (off == 0.0) break;
+        const double dg = (a[0][0] * a[0][0] + a[1][1] * a[1][1]) + (a[2][2] * a[2][2] + a[3][3] * a[3][3]);
+        if (off <= 1e-40 * dg) break;   // off-diagonal norm below 1e-20 of the diagonal: converged far below 1 ulp (JacobiSVD itself stops at 2 eps)
 #if defined(__CUDA_ARCH__)
 #pragma unroll   // static (p, q): the two 4x4 matrices stay in registers instead of local memory
 #endif
