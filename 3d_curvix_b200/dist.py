@@ -100,3 +100,59 @@ def gather_results(local, group=None, dst=0):
             parts.append(bufs[r][o:o + c * row_bytes[k]].view(local[k].dtype).view((c,) + tuple(local[k].shape[1:])))
         out[k] = torch.cat(parts, 0)
     return out, counts
+
+
+class PackedGather:
+    """Steady-state form of gather_results for a known row capacity: ONE collective per call and no host synchronisation on the
+    sending ranks.  Every rank packs [int64 row count | fields back to back, widest element type first] into a fixed-size byte
+    buffer (capacity `cap_rows`, agreed once, e.g. from an all_reduce MAX over a warm-up pass); one all_gather_into_tensor moves
+    the buffers; rank `dst` reads the counts (its only synchronisation) and returns per-rank views in rank order = ascending
+    pair / view-1 order.  A rank with more rows than the capacity raises (grow the capacity collectively and retry)."""
+
+    HEADER = 16
+
+    def __init__(self, fields, cap_rows, device, group=None, dst=0):
+        """fields: dict name -> (row_shape tuple, torch dtype)."""
+        self.group, self.dst, self.cap = group, dst, int(cap_rows)
+        self.world = dist.get_world_size(group)
+        self.rank = dist.get_rank(group)
+        esz = lambda dt: torch.empty((), dtype=dt).element_size()
+        self.order = sorted(fields, key=lambda k: (-esz(fields[k][1]), k))
+        self.fields = {k: (tuple(fields[k][0]), fields[k][1], int(np.prod(fields[k][0], dtype=np.int64)) * esz(fields[k][1])) for k in fields}
+        per_row = sum(v[2] for v in self.fields.values())
+        self.nbytes = self.HEADER + ((self.cap * per_row + 15) // 16) * 16
+        self.send = torch.zeros(self.nbytes, dtype=torch.uint8, device=device)
+        self.recv = torch.empty(self.world * self.nbytes, dtype=torch.uint8, device=device)
+        self.hdr = torch.zeros(1, dtype=torch.int64, device=device)
+
+    def run(self, local, concat=False):
+        P = int(local[self.order[0]].shape[0])
+        if P > self.cap:
+            raise RuntimeError(f"PackedGather: {P} rows exceed the agreed capacity {self.cap}")
+        self.hdr.fill_(P)
+        self.send[:8].copy_(self.hdr.view(torch.uint8))
+        off = self.HEADER
+        for k in self.order:
+            nb = P * self.fields[k][2]
+            if nb:
+                self.send[off:off + nb].copy_(local[k].contiguous().view(-1).view(torch.uint8))
+            off += nb
+        if dist.get_backend(self.group) == "gloo":
+            parts = [self.recv[r * self.nbytes:(r + 1) * self.nbytes] for r in range(self.world)]
+            dist.all_gather(parts, self.send, group=self.group)
+        else:
+            dist.all_gather_into_tensor(self.recv, self.send, group=self.group)
+        if self.rank != self.dst:
+            return None, None
+        bufs = self.recv.view(self.world, self.nbytes)
+        counts = [int(c) for c in bufs[:, :8].contiguous().view(torch.int64).view(-1).tolist()]
+        out = {k: [] for k in self.fields}
+        for r, c in enumerate(counts):
+            off = self.HEADER
+            for k in self.order:
+                shape, dt, rb = self.fields[k]
+                out[k].append(bufs[r, off:off + c * rb].view(dt).view((c,) + shape))
+                off += c * rb
+        if concat:
+            out = {k: torch.cat(v, 0) for k, v in out.items()}
+        return out, counts

@@ -303,13 +303,23 @@ def run_b200(args, rank, world, local_rank):
     stream = torch.cuda.ExternalStream(g.stream_ptr(), device=torch.device("cuda", local_rank))
     flush = torch.empty(L2_FLUSH_BYTES // 4, dtype=torch.int32, device="cuda")
 
+    gather_plan = {}
+
     def gather(res):
-        """The path's only exchange: accepted pairs + 3-D edges + tangents to rank 0 (NCCL), rank order = pair order."""
+        """The path's only exchange: accepted pairs + 3-D edges + tangents to rank 0 (NCCL), rank order = pair order.  The first
+        call gathers with exact counts (two collectives) and agrees a row capacity; the following ones use ONE collective."""
         P, Vv = int(res.n_pairs), int(res.n_vali_views)
         loc = {"h1": distm.device_tensor(res.pair_h1, (P,), torch.int32), "h2": distm.device_tensor(res.pair_h2rep, (P,), torch.int32),
                "sup": distm.device_tensor(res.pair_supports, (P, Vv), torch.int32),
                "gw": distm.device_tensor(res.gamma_world, (P, 3), torch.float64), "tw": distm.device_tensor(res.tangent_world, (P, 3), torch.float64)}
-        return distm.gather_results(loc)
+        if "pg" not in gather_plan:
+            out = distm.gather_results(loc)
+            cap = torch.tensor([P], dtype=torch.int64, device="cuda")
+            tdist.all_reduce(cap, op=tdist.ReduceOp.MAX)
+            fields = {k: (tuple(t.shape[1:]), t.dtype) for k, t in loc.items()}
+            gather_plan["pg"] = distm.PackedGather(fields, int(cap.item()) * 5 // 4 + 64, torch.device("cuda", local_rank))
+            return out
+        return gather_plan["pg"].run(loc)
 
     gather_ev = []
 

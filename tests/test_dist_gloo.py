@@ -26,10 +26,18 @@ def _worker(rank, world, port, payloads, out_path):
     dist.init_process_group("gloo", rank=rank, world_size=world)
     local = {k: torch.from_numpy(v) for k, v in payloads[rank].items()}
     got, counts = distm.gather_results(local)
+    # steady-state form: fixed capacity, one collective; must deliver the same rows
+    fields = {k: (tuple(v.shape[1:]), v.dtype) for k, v in local.items()}
+    cap = torch.tensor([local["h1"].shape[0]], dtype=torch.int64)
+    dist.all_reduce(cap, op=dist.ReduceOp.MAX)
+    pg = distm.PackedGather(fields, int(cap.item()) + 3, torch.device("cpu"))
+    for _ in range(2):      # reusable
+        got2, counts2 = pg.run(local, concat=True)
     if rank == 0:
+        assert counts2 == counts and all(torch.equal(got[k], got2[k]) for k in got)
         np.savez(out_path, counts=np.array(counts), **{k: v.numpy() for k, v in got.items()})
     else:
-        assert got is None
+        assert got is None and got2 is None
     dist.barrier()
     dist.destroy_process_group()
 
