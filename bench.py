@@ -423,7 +423,7 @@ def run_b200(args, rank, world, local_rank):
         abytes = 0
     ach = abytes / (ktime[dom] * 1e-3) / 1e9
     roof = {"bound": "hbm", "kernel": kname, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": traffic(kname),
-            "peak_source": peak_src, "kernel_ms": ktime[dom], "algorithmic_bytes": abytes,
+            "peak_source": peak_src, "kernel_ms": ktime[dom], "algorithmic_bytes": abytes, "ncu": ncu_notes(kname),
             "kernel_ms_all": {k: round(v, 4) for k, v in ktime.items()},
             "note": "FP64-transcendental bound, not HBM bound (DESIGN.md): ~1.3k FP64 flop-equivalents per validation vs a few bytes"}
     val_ms = parts["validate_ms"] / args.steps
@@ -539,7 +539,7 @@ def run_support_stress(args, rank, world, local_rank):
             "roofline": {"bound": "hbm", "kernel": "k_validate<true>", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
                          "traffic": traffic("k_validate<true>", V), "peak_source": peak_src, "kernel_ms": ms_per_step, "algorithmic_bytes": abytes,
                          "bytes_formula": "validations x 52 + 16 x wedge-intersection members + 32 x staged edges (SURVEY.md 8d)",
-                         "mean_intersection": n_bar, "entries_visited_per_validation": stats["n_visited"] / vals},
+                         "mean_intersection": n_bar, "entries_visited_per_validation": stats["n_visited"] / vals, "ncu": ncu_notes("k_validate<true>")},
             "counts_rank0": dict(stats, n_validations=vals, n_rows=H, n_edges=int(prob["view_off"][-1])), "create_s": create_s}
     if not args.no_cpu_baseline and world == 1:
         # bounded CPU sample: one view, the first groups; same arrays
@@ -566,6 +566,12 @@ def run_support_stress(args, rank, world, local_rank):
     sp.close(); g.close()
     if use_dist:
         tdist.destroy_process_group()
+
+
+def ncu_notes(kernel):
+    """Pipe / issue utilisation of `kernel` from the committed ncu capture (profiles/traffic.json): what actually bounds it."""
+    p = os.path.join(ROOT, "profiles", "traffic.json")
+    return json.load(open(p)).get(kernel, {}).get("ncu") if os.path.exists(p) else None
 
 
 def traffic(kernel, views=0):
