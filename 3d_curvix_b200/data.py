@@ -109,7 +109,7 @@ def _curves(rng, n_curves):
 
 
 def make_synthetic_scene(n_views, edges_per_view, rows=800, cols=800, seed=20251106, n_curves=24, pair_baseline_deg=25.0,
-                         outlier_frac=0.10, loc_sigma=0.25, ori_sigma_deg=2.0, cam_radius=4.0, name=None):
+                         outlier_frac=0.10, loc_sigma=0.25, ori_sigma_deg=2.0, cam_radius=4.0, name=None, fy_scale=1.0, c_shift=(0.0, 0.0)):
     """Seeded synthetic multiview edge scene.
 
     Views 0 and 1 form a hypothesis pair with `pair_baseline_deg` of baseline; the remaining cameras are
@@ -119,7 +119,9 @@ def make_synthetic_scene(n_views, edges_per_view, rows=800, cols=800, seed=20251
     """
     rng = np.random.default_rng(seed)
     f = 1111.11136542426 * (cols / 800.0)
-    K = np.array([[f, 0, (cols - 1) / 2.0], [0, f, (rows - 1) / 2.0], [0, 0, 1.0]])
+    # fy_scale / c_shift: anisotropic focal length and off-centre principal point (the DTU intrinsics have both)
+    fy = f * fy_scale
+    K = np.array([[f, 0, (cols - 1) / 2.0 + c_shift[0]], [0, fy, (rows - 1) / 2.0 + c_shift[1]], [0, 0, 1.0]])
     curves = _curves(rng, n_curves)
     tot_len = sum(L for _, L in curves)
     # camera centres
@@ -152,10 +154,10 @@ def make_synthetic_scene(n_views, edges_per_view, rows=800, cols=800, seed=20251
             dPc = dP @ R[v].T
             z = Pc[:, 2]
             u = f * Pc[:, 0] / z + K[0, 2]
-            w = f * Pc[:, 1] / z + K[1, 2]
+            w = fy * Pc[:, 1] / z + K[1, 2]
             # image tangent = d/dt of the projection
             du = f * (dPc[:, 0] * z - Pc[:, 0] * dPc[:, 2]) / (z * z)
-            dw = f * (dPc[:, 1] * z - Pc[:, 1] * dPc[:, 2]) / (z * z)
+            dw = fy * (dPc[:, 1] * z - Pc[:, 1] * dPc[:, 2]) / (z * z)
             xs.append(u); ys.append(w); ths.append(np.arctan2(dw, du))
         x = np.concatenate(xs); y = np.concatenate(ys); th = np.concatenate(ths)
         x = x + rng.normal(0, loc_sigma, x.shape); y = y + rng.normal(0, loc_sigma, y.shape)

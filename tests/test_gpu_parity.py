@@ -259,3 +259,23 @@ def test_global_memory_clustering_fallback(oracle_mod, tiny_scene):
     rep = compare(o, g, check_intermediates=True)
     _report("tiny_0_1_maxcluster40", rep)
     assert rep["counts_gpu"]["n_hypotheses"] > 0
+
+
+def test_dtu_shaped_scene_parity(oracle_mod, data_mod):
+    """DTU-shaped inputs (configs/3D_Curvix_DTU.yaml): non-square image, fx != fy, off-centre principal point, N_support = 6;
+    full parity against the oracle on two hypothesis pairs, with the packed all-view upload."""
+    scene = data_mod.make_synthetic_scene(n_views=14, edges_per_view=2500, rows=1200, cols=1600, seed=31, n_curves=16,
+                                          fy_scale=922.616455078125 / 925.546142578125, c_shift=(7.4, -5.9))
+    o = make_oracle(oracle_mod, scene, max_support_views=6)
+    api = pkg("api")
+    g = api.EdgeSketch(api.default_config(n_views=scene.n_views, img_rows=scene.rows, img_cols=scene.cols, max_support_views=6), 0)
+    g.keep_intermediates(True)
+    g.set_cameras(scene.R, scene.T, scene.K)
+    g.set_all_view_edges(scene.edges)
+    for (a, b) in [(0, 1), (6, 7)]:
+        o.set_pair(a, b); o.run(mode=1, keep=True)
+        g.set_pair(a, b); g.run()
+        rep = compare(o, g, check_intermediates=True)
+        _report(f"dtu_shaped_{a}_{b}", rep)
+        assert rep["counts_gpu"]["n_hypotheses"] > 1000
+    g.close()
