@@ -147,7 +147,11 @@ struct cvx_ctx {
     std::vector<int64_t> h_ingest_tab;
     DevBuf<int32_t> v_h1, v_row, v_count, v_sel, p_h1, p_h2rep, p_row, p_count, p_sup, f_nan;
     DevBuf<double> f_gc, f_gw, f_tw, f_h2c;
-    std::vector<int64_t> h_row_off;
+    std::vector<int64_t> h_row_off;             // fetched lazily by cvx_get_h1_table
+    bool h_row_off_valid = false;
+    struct HostPin { int64_t H, U, tot[2]; int32_t cnts[8]; DevCounters hc; };
+    HostPin* pin = nullptr;                     // pinned: the scalars a run reads back arrive by truly asynchronous copies
+    bool timings_pending = false;
     // claimed-edge bitmap over the arena (one bit per edge slot) + per-view popcounts
     uint32_t* d_claim = nullptr;
     size_t claim_words = 0;
@@ -155,7 +159,8 @@ struct cvx_ctx {
     DevBuf<uint8_t> d_claim_mask;
     cvx_counts counts;
     cvx_timings tm;
-    cudaEvent_t ev[8];
+    cudaEvent_t ev[10];                         // run: 0,1,3,4,5; finalize: 6,7; set_pair: 8,9
+    bool final_timing_pending = false;
 };
 
 struct cvx_support_problem {
@@ -283,6 +288,7 @@ int cvx_create(const cvx_config* cfg, int device, cvx_ctx** out) {
         return CVX_ERR_CUDA;
     }
     for (auto& e : ctx->ev) cudaEventCreate(&e);
+    if (cudaMallocHost(reinterpret_cast<void**>(&ctx->pin), sizeof(cvx_ctx::HostPin)) != cudaSuccess) { delete ctx; return CVX_ERR_NOMEM; }
     cudaStreamCreateWithFlags(&ctx->stream2, cudaStreamNonBlocking);
     cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming); cudaEventCreateWithFlags(&ctx->ev_join, cudaEventDisableTiming);
     if (ctx->d_ctr.reserve(1) != cudaSuccess) { delete ctx; return CVX_ERR_NOMEM; }
@@ -314,6 +320,7 @@ int cvx_destroy(cvx_ctx* ctx) {
     ctx->d_claim_cnt.release(); ctx->d_claim_mask.release();
     for (auto& e : ctx->ev) cudaEventDestroy(e);
     cudaStreamDestroy(ctx->stream);
+    if (ctx->pin) cudaFreeHost(ctx->pin);
     if (ctx->stream2) cudaStreamDestroy(ctx->stream2);
     if (ctx->ev_fork) cudaEventDestroy(ctx->ev_fork);
     if (ctx->ev_join) cudaEventDestroy(ctx->ev_join);
@@ -460,7 +467,7 @@ int cvx_set_hypothesis_pair(cvx_ctx* ctx, int h1, int h2) {
     int rc = sync_tables(ctx);
     if (rc) return rc;
     CU(ctx->d_vc.reserve(V)); CU(ctx->d_vali.reserve(V));
-    cudaEventRecord(ctx->ev[0], ctx->stream);
+    cudaEventRecord(ctx->ev[8], ctx->stream);
     CU(cudaMemcpyAsync(ctx->d_vc.p, vc.data(), V * sizeof(ViewConst), cudaMemcpyHostToDevice, ctx->stream));
     CU(cudaMemcpyAsync(ctx->d_vali.p, ctx->vali_views.data(), V * sizeof(int32_t), cudaMemcpyHostToDevice, ctx->stream));
     // ---- stage every validation view into its bin grid (hoisted getOreListVali + cos/sin, EdgeSketch_Core.cpp:315-342)
@@ -492,9 +499,9 @@ int cvx_set_hypothesis_pair(cvx_ctx* ctx, int h1, int h2) {
     }
     launch_h1_wedges(pc, ctx->ea.x + ctx->edge_off[h1], ctx->ea.y + ctx->edge_off[h1], E1, ctx->d_wedge_h1.p, ctx->d_wflag_h1.p, ctx->stream);
     ctx->tm.kernel_launches += 2;
-    cudaEventRecord(ctx->ev[1], ctx->stream);
+    cudaEventRecord(ctx->ev[9], ctx->stream);
     CU(cudaStreamSynchronize(ctx->stream));   // vc (host vector) must outlive the copy
-    cudaEventElapsedTime(&ctx->tm.set_pair_ms, ctx->ev[0], ctx->ev[1]);
+    cudaEventElapsedTime(&ctx->tm.set_pair_ms, ctx->ev[8], ctx->ev[9]);
     CU(cudaGetLastError());
     ctx->have_run = false; ctx->have_final = false;
     return CVX_OK;
@@ -524,16 +531,17 @@ int cvx_run_edge_sketch(cvx_ctx* ctx, int h1_begin, int h1_end) {
     CU(cudaMemsetAsync(ctx->d_m.p, 0, E1a * 4, st)); CU(cudaMemsetAsync(ctx->d_n.p, 0, E1a * 4, st)); CU(cudaMemsetAsync(ctx->d_ncl.p, 0, E1a * 4, st));
     CU(cudaMemsetAsync(ctx->d_nvalid.p, 0, E1a * 4, st)); CU(cudaMemsetAsync(ctx->d_nsel.p, 0, E1a * 4, st));
     CU(cudaMemsetAsync(ctx->d_ctr.p, 0, sizeof(DevCounters), st));
-    CU(ctx->d_big_list.reserve(size_t(E1a) + 8));                     // clustering order of the view-1 edges + the 5 class counts
+    CU(ctx->d_big_list.reserve(size_t(E1a) + 8));                     // clustering order of the view-1 edges + the class counts
+    CU(cudaMemsetAsync(ctx->d_big_list.p + E1a, 0, 8 * 4, st));
     cudaEventRecord(ctx->ev[0], st);
     // ---- hypothesis formation
     launch_form_count(pc, x1, y1, h1_begin, h1_end, ctx->d_wedge_h1.p, x2, y2, th2, ctx->d_ang2.p, E2, ctx->h2ix, ctx->d_m.p, ctx->d_n.p, st);
     launch_scan_i32_i64(ctx->d_n.p, ctx->d_row_off.p, E1, st);
     ctx->tm.kernel_launches += 2;
-    ctx->h_row_off.resize(size_t(E1) + 1);
-    CU(cudaMemcpyAsync(ctx->h_row_off.data(), ctx->d_row_off.p, (size_t(E1) + 1) * 8, cudaMemcpyDeviceToHost, st));
+    ctx->h_row_off_valid = false;
+    CU(cudaMemcpyAsync(&ctx->pin->H, ctx->d_row_off.p + E1, 8, cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
-    const int64_t H = ctx->h_row_off[E1];
+    const int64_t H = ctx->pin->H;
     ctx->H = H;
     const size_t Ha = size_t(std::max<int64_t>(H, 1));
     DevBuf<int32_t>* ib[] = {&ctx->r_h1, &ctx->r_h2orig, &ctx->r_local, &ctx->r_rawat, &ctx->r_label, &ctx->r_h2rep, &ctx->r_count, &ctx->r_flags,
@@ -547,9 +555,9 @@ int cvx_run_edge_sketch(cvx_ctx* ctx, int h1_begin, int h1_end) {
     launch_scan_i32_i64(ctx->d_ncl.p, ctx->d_u_off.p, E1, st);
     ctx->tm.kernel_launches += 8;
     cudaEventRecord(ctx->ev[1], st);
-    int64_t U = 0;
-    CU(cudaMemcpyAsync(&U, ctx->d_u_off.p + E1, 8, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(&ctx->pin->U, ctx->d_u_off.p + E1, 8, cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
+    const int64_t U = ctx->pin->U;
     ctx->U = U;
     // ---- unique hypotheses (one per cluster) + wedge of the view-1 edge in every validation view
     const size_t Ua = size_t(std::max<int64_t>(U, 1));
@@ -582,12 +590,13 @@ int cvx_run_edge_sketch(cvx_ctx* ctx, int h1_begin, int h1_end) {
     launch_scan_i32_i64(ctx->d_nvalid.p, ctx->d_valid_off.p, E1, st);
     launch_scan_i32_i64(ctx->d_nsel.p, ctx->d_pair_off.p, E1, st);
     ctx->tm.kernel_launches += 4;
-    int64_t tot[2] = {0, 0};
+    int64_t* tot = ctx->pin->tot;
     CU(cudaMemcpyAsync(&tot[0], ctx->d_valid_off.p + E1, 8, cudaMemcpyDeviceToHost, st));
     CU(cudaMemcpyAsync(&tot[1], ctx->d_pair_off.p + E1, 8, cudaMemcpyDeviceToHost, st));
     static_assert(sizeof(DevCounters) == 6 * CVX_CTR_SLOTS * 8, "DevCounters layout");
-    DevCounters hc;
-    CU(cudaMemcpyAsync(&hc, ctx->d_ctr.p, sizeof(hc), cudaMemcpyDeviceToHost, st));
+    const DevCounters& hc = ctx->pin->hc;
+    CU(cudaMemcpyAsync(&ctx->pin->hc, ctx->d_ctr.p, sizeof(hc), cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(ctx->pin->cnts, ctx->d_big_list.p + E1a, 8 * 4, cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
     ctx->n_valid = tot[0]; ctx->P = tot[1];
     const size_t NVa = size_t(std::max<int64_t>(ctx->n_valid, 1)), Pa = size_t(std::max<int64_t>(ctx->P, 1));
@@ -599,13 +608,8 @@ int cvx_run_edge_sketch(cvx_ctx* ctx, int h1_begin, int h1_end) {
     launch_gather_supports(ctx->p_row.p, ctx->r_row_u.p, ctx->P, V, ctx->d_support.p, int64_t(Ua), ctx->p_sup.p, st);
     ctx->tm.kernel_launches += 2;
     cudaEventRecord(ctx->ev[3], st);
-    CU(cudaStreamSynchronize(st));
     CU(cudaGetLastError());
-    cudaEventElapsedTime(&ctx->tm.run_ms, ctx->ev[0], ctx->ev[3]);
-    cudaEventElapsedTime(&ctx->tm.form_ms, ctx->ev[0], ctx->ev[1]);
-    cudaEventElapsedTime(&ctx->tm.prep_ms, ctx->ev[1], ctx->ev[4]);
-    cudaEventElapsedTime(&ctx->tm.validate_ms, ctx->ev[4], ctx->ev[5]);
-    cudaEventElapsedTime(&ctx->tm.select_ms, ctx->ev[5], ctx->ev[3]);
+    ctx->timings_pending = true;      // the last two launches are still in flight: phase times are read in cvx_get_timings
     // ---- counts
     cvx_counts& c = ctx->counts;
     std::memset(&c, 0, sizeof(c));
@@ -616,7 +620,7 @@ int cvx_run_edge_sketch(cvx_ctx* ctx, int h1_begin, int h1_end) {
         c.n_parallel += int64_t(hc.n_parallel[k]); c.n_inliers += int64_t(hc.n_inliers[k]);
         c.n_entries_visited += int64_t(hc.n_visited[k]); c.n_heavy_queries += int64_t(hc.n_heavy[k]);
     }
-    for (int i = h1_begin; i < h1_end; i++) if (ctx->h_row_off[i + 1] > ctx->h_row_off[i]) c.n_h1_processed++;
+    c.n_h1_processed = ctx->pin->cnts[5];                             // view-1 edges with at least one hypothesis (k_order_by_n)
     c.n_candidates = -1;   // filled lazily by cvx_get_counts (needs m[])
     ctx->have_run = true; ctx->have_final = false;
     return CVX_OK;
@@ -628,6 +632,7 @@ int cvx_get_counts(cvx_ctx* ctx, cvx_counts* out) {
         CU(cudaSetDevice(ctx->device));
         const int E1 = ctx->edge_n[ctx->h1];
         std::vector<int32_t> m(std::max(E1, 1));
+        CU(cudaStreamSynchronize(ctx->stream));
         CU(cudaMemcpy(m.data(), ctx->d_m.p, size_t(E1) * 4, cudaMemcpyDeviceToHost));
         int64_t s = 0;
         for (int i = 0; i < E1; i++) s += m[i];
@@ -639,8 +644,11 @@ int cvx_get_counts(cvx_ctx* ctx, cvx_counts* out) {
 
 #define D2HA(dst, src, n, T)                                                                                      \
     do { if ((dst) && (n) > 0) CU(cudaMemcpyAsync((dst), (src), size_t(n) * sizeof(T), cudaMemcpyDeviceToHost, ctx->stream)); } while (0)
+// stream-ordered and complete on return: the context stream is non-blocking, so a plain cudaMemcpy would not wait for the
+// launches cvx_run_edge_sketch / run_finalize leave in flight
 #define D2H(dst, src, n, T)                                                                                       \
-    do { if ((dst) && (n) > 0) CU(cudaMemcpy((dst), (src), size_t(n) * sizeof(T), cudaMemcpyDeviceToHost)); } while (0)
+    do { if ((dst) && (n) > 0) { CU(cudaMemcpyAsync((dst), (src), size_t(n) * sizeof(T), cudaMemcpyDeviceToHost, ctx->stream)); \
+                                 CU(cudaStreamSynchronize(ctx->stream)); } } while (0)
 
 int cvx_get_h2_angles(cvx_ctx* ctx, double* out) {
     if (!ctx || ctx->h2 < 0) return fail(ctx, CVX_ERR_INVALID, "no pair");
@@ -661,6 +669,11 @@ int cvx_get_h1_table(cvx_ctx* ctx, int32_t* m, int32_t* n, int64_t* row_off) {
     const int E1 = ctx->edge_n[ctx->h1];
     D2H(m, ctx->d_m.p, E1, int32_t);
     D2H(n, ctx->d_n.p, E1, int32_t);
+    if (row_off && !ctx->h_row_off_valid) {
+        ctx->h_row_off.resize(size_t(E1) + 1);
+        D2H(ctx->h_row_off.data(), ctx->d_row_off.p, E1 + 1, int64_t);
+        ctx->h_row_off_valid = true;
+    }
     if (row_off)
         for (int i = 0; i < E1; i++) row_off[i] = (ctx->h_row_off[i + 1] > ctx->h_row_off[i]) ? ctx->h_row_off[i] : -1;
     return CVX_OK;
@@ -703,6 +716,7 @@ int cvx_get_intermediates(cvx_ctx* ctx, double* wedge31, double* wedge32, double
     const int E1 = ctx->edge_n[ctx->h1], V = ctx->n_vali;
     const int64_t H = ctx->H, U = ctx->U;
     // device layout is view-major over unique hypotheses; the ABI returns [E1][V][2] and [H][V][2]
+    CU(cudaStreamSynchronize(ctx->stream));
     if (wedge31) {
         std::vector<double> t(size_t(V) * E1 * 2);
         CU(cudaMemcpy(t.data(), ctx->d_w31.p, t.size() * 8, cudaMemcpyDeviceToHost));
@@ -774,14 +788,13 @@ static int run_finalize(cvx_ctx* ctx) {
     CU(ctx->f_gc.reserve(Pa * 3)); CU(ctx->f_gw.reserve(Pa * 3)); CU(ctx->f_tw.reserve(Pa * 3)); CU(ctx->f_h2c.reserve(Pa * 2)); CU(ctx->f_nan.reserve(Pa));
     const double *x1 = ctx->ea.x + ctx->edge_off[ctx->h1], *y1 = ctx->ea.y + ctx->edge_off[ctx->h1], *th1 = ctx->ea.th + ctx->edge_off[ctx->h1];
     const double *x2 = ctx->ea.x + ctx->edge_off[ctx->h2], *y2 = ctx->ea.y + ctx->edge_off[ctx->h2], *th2 = ctx->ea.th + ctx->edge_off[ctx->h2];
-    cudaEventRecord(ctx->ev[0], ctx->stream);
+    cudaEventRecord(ctx->ev[6], ctx->stream);
     launch_finalize(ctx->pc, x1, y1, th1, x2, y2, th2, ctx->p_h1.p, ctx->p_h2rep.p, P, ctx->f_gc.p, ctx->f_gw.p, ctx->f_tw.p, ctx->f_h2c.p,
                     ctx->f_nan.p, ctx->stream);
     ctx->tm.kernel_launches++;
-    cudaEventRecord(ctx->ev[1], ctx->stream);
-    CU(cudaStreamSynchronize(ctx->stream));
+    cudaEventRecord(ctx->ev[7], ctx->stream);
     CU(cudaGetLastError());
-    cudaEventElapsedTime(&ctx->tm.finalize_ms, ctx->ev[0], ctx->ev[1]);
+    ctx->final_timing_pending = true;          // asynchronous: results are consumed on the same stream (or by synchronising getters)
     ctx->have_final = true;
     return CVX_OK;
 }
@@ -877,6 +890,22 @@ int cvx_claims_get_mask(cvx_ctx* ctx, int view, uint8_t* out) {
 
 int cvx_get_timings(cvx_ctx* ctx, cvx_timings* out) {
     if (!ctx || !out) return CVX_ERR_INVALID;
+    if (ctx->timings_pending) {
+        CU(cudaSetDevice(ctx->device));
+        CU(cudaEventSynchronize(ctx->ev[3]));
+        cudaEventElapsedTime(&ctx->tm.run_ms, ctx->ev[0], ctx->ev[3]);
+        cudaEventElapsedTime(&ctx->tm.form_ms, ctx->ev[0], ctx->ev[1]);
+        cudaEventElapsedTime(&ctx->tm.prep_ms, ctx->ev[1], ctx->ev[4]);
+        cudaEventElapsedTime(&ctx->tm.validate_ms, ctx->ev[4], ctx->ev[5]);
+        cudaEventElapsedTime(&ctx->tm.select_ms, ctx->ev[5], ctx->ev[3]);
+        ctx->timings_pending = false;
+    }
+    if (ctx->final_timing_pending) {
+        CU(cudaSetDevice(ctx->device));
+        CU(cudaEventSynchronize(ctx->ev[7]));
+        cudaEventElapsedTime(&ctx->tm.finalize_ms, ctx->ev[6], ctx->ev[7]);
+        ctx->final_timing_pending = false;
+    }
     *out = ctx->tm;
     return CVX_OK;
 }

@@ -936,6 +936,7 @@ __global__ void __launch_bounds__(1024) k_order_by_n(const int32_t* __restrict__
         for (int k = 0; k < ORDER_BUCKETS; k++) { const int c = hist[k]; hist[k] = run; run += c; if (k == CL_N - 1) ns = run; }
         cnts[0] = ns; cnts[1] = hist[CL_N + 1] - ns; cnts[2] = hist[CL_N + 2] - hist[CL_N + 1];
         cnts[3] = hist[CL_N + 3] - hist[CL_N + 2]; cnts[4] = run - hist[CL_N + 3];
+        cnts[5] = run;                             // view-1 edges with at least one hypothesis
     }
     __syncthreads();
     for (int i = h1_begin + threadIdx.x; i < h1_end; i += blockDim.x) { const int n = n_of[i]; if (n > 0) order[atomicAdd(&hist[key(n)], 1)] = i; }
