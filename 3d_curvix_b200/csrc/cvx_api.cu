@@ -553,7 +553,7 @@ int cvx_run_edge_sketch(cvx_ctx* ctx, int h1_begin, int h1_end) {
     launch_form_fill(pc, x1, y1, h1_begin, h1_end, ctx->d_wedge_h1.p, x2, y2, th2, ctx->d_ang2.p, E2, ctx->h2ix, ctx->d_m.p, ctx->d_n.p, ctx->d_row_off.p, rt,
                      ctx->d_ncl.p, ctx->d_big_list.p, ctx->d_big_list.p + E1a, st, ctx->stream2, ctx->ev_fork, ctx->ev_join);   // order[E1], cnts[5]
     launch_scan_i32_i64(ctx->d_ncl.p, ctx->d_u_off.p, E1, st);
-    ctx->tm.kernel_launches += 8;
+    ctx->tm.kernel_launches += 5;
     cudaEventRecord(ctx->ev[1], st);
     CU(cudaMemcpyAsync(&ctx->pin->U, ctx->d_u_off.p + E1, 8, cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));

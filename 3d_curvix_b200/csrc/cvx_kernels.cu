@@ -21,6 +21,7 @@
 
 #include <float.h>
 #include <stdlib.h>
+#include <stdio.h>
 
 #include <algorithm>
 
@@ -508,7 +509,6 @@ void launch_scan_i32_i64(const int32_t* in, int64_t* out, int n, cudaStream_t st
 template <int N>
 struct ClusterSm {
     double x[N], y[N], thn[N], orient[N];   // corrected location, normalised orientation, per-label average orientation
-    double tmpd[32], tmpw[32];
     uint32_t adj[N * (N / 32)];
     uint32_t dirty[N / 32], canw[N / 32];   // rows whose merge decision must be re-evaluated / rows that can merge (bit per row)
     int16_t label[N], size[N], rank[N], mem[32];   // rank doubles as the cached merge partner during the merge phase
@@ -518,15 +518,21 @@ struct ClusterSm {
 #define CL_BIG_N 512      // <= CL_BIG_N (one warp per block, 53 KB of shared memory), <= CL_HUGE_N (one warp per block, 171 KB: one block
 #define CL_HUGE_N 1024    // per SM); beyond: global-memory fallback
 #define FORM_WARPS 4
+// The <= 128 / 256 / 512-row classes share one launch (k_cluster_classes): every block has the same shared-memory size and holds
+// one 512-row edge (8 warps), two 256-row edges (4 warps each) or eight <= 128-row edges (a warp each).
+#define CL_SMEM_QUANTUM (56 * 1024)   // 4 blocks per SM
+#define CL_SMALL_WARPS 8             // warps per block; a <= 128-row edge per warp
+#define CL_MID_WARPS 4               // warps that share one <= 256-row edge
+#define CL_MID_EDGES (CL_SMALL_WARPS / CL_MID_WARPS)
 
 // Gaussian-weighted average over the members s.mem[0..cnt) (ascending index): EdgeClusterer.cpp:60-125.  Lane k holds member k;
 // every sum runs in member order on every lane through shuffles (bit-identical to the sequential code: the products are formed
 // per member first, the additions are the reference's left-to-right chain); sqrt / exp of the members are lane-parallel.
 __device__ __forceinline__ double shfl_d(double v, int src) { return __shfl_sync(FULL, v, src); }
 template <int N, bool ORIENT_ONLY>   // ORIENT_ONLY: the merge step needs the averaged orientation alone (EdgeClusterer.cpp:168-176)
-__device__ __noinline__ void gauss_avg_list(ClusterSm<N>& s, int cnt, double sigma, int lane, double* gx, double* gy, double* gth) {
+__device__ __noinline__ void gauss_avg_list(ClusterSm<N>& s, const int16_t* mem, int cnt, double sigma, int lane, double* gx, double* gy, double* gth) {
     double xi = 0, yi = 0, ti = 0;
-    if (lane < cnt) { const int i = s.mem[lane]; xi = s.x[i]; yi = s.y[i]; ti = s.thn[i]; }
+    if (lane < cnt) { const int i = mem[lane]; xi = s.x[i]; yi = s.y[i]; ti = s.thn[i]; }
     double sx = 0, sy = 0;
     for (int k = 0; k < cnt; k++) { sx += shfl_d(xi, k); sy += shfl_d(yi, k); }
     const double cx = sx / cnt, cy = sy / cnt;
@@ -551,17 +557,46 @@ __device__ __noinline__ void gauss_avg_list(ClusterSm<N>& s, int cnt, double sig
 }
 // members with label la or lb, ascending, into s.mem; returns the count (<= 32 by construction)
 template <int N>
-__device__ __forceinline__ int member_list(ClusterSm<N>& s, int n, int la, int lb, int lane, unsigned lt) {
+__device__ __forceinline__ int member_list(ClusterSm<N>& s, int16_t* mem, int n, int la, int lb, int lane, unsigned lt) {
     int cnt = 0;
     for (int base = 0; base < n; base += 32) {
         const int k = base + lane;
         const bool in = k < n && (s.label[k] == la || s.label[k] == lb);
         const unsigned m = __ballot_sync(FULL, in);
-        if (in) { const int p = cnt + __popc(m & lt); if (p < 32) s.mem[p] = int16_t(k); }
+        if (in) { const int p = cnt + __popc(m & lt); if (p < 32) mem[p] = int16_t(k); }
         cnt += __popc(m);
     }
     __syncwarp();
     return cnt < 32 ? cnt : 32;
+}
+
+// Would row i merge now?  Nearest row of another cluster within the distance threshold whose cluster orientation is within the
+// orientation threshold (first minimum, j ascending), and the two clusters together within the size limit
+// (EdgeClusterer.cpp:143-166).  The partner is cached in s.rank[i].
+template <int N>
+__device__ __forceinline__ bool merge_candidate(ClusterSm<N>& s, int i, int nw, const PassConst& pc) {
+    constexpr int NW = N / 32;
+    const int li = s.label[i];
+    const double oi = s.orient[li], xi = s.x[i], yi = s.y[i];
+    double bd = DBL_MAX;
+    int bj = -1;
+    for (int ww = 0; ww < nw; ww++) {
+        uint32_t bits = s.adj[i * NW + ww];
+        while (bits) {
+            const int b = __ffs(bits) - 1;
+            bits &= bits - 1;
+            const int j = ww * 32 + b;
+            const int lj = s.label[j];
+            if (lj != li && fabs(oi - s.orient[lj]) < pc.cl_orient_rad) {          // :147-154
+                const double ddx = xi - s.x[j], ddy = yi - s.y[j];
+                const double d = sqrt(ddx * ddx + ddy * ddy);
+                if (d < bd) { bd = d; bj = j; }                                     // first minimum (j ascending)
+            }
+        }
+    }
+    const bool found = bj >= 0 && int(s.size[s.label[bj]]) + int(s.size[li]) <= pc.max_cluster;   // :166
+    s.rank[i] = int16_t(found ? bj : -1);
+    return found;
 }
 
 template <int N>
@@ -601,29 +636,7 @@ __device__ void cluster_warp_sm(int n, const PassConst& pc, ClusterSm<N>& s, con
             const uint32_t dw = s.dirty[w];
             if (!dw) continue;
             const int i = w * 32 + lane;
-            bool found = false;
-            if ((dw >> lane) & 1u) {
-                const int li = s.label[i];
-                const double oi = s.orient[li], xi = s.x[i], yi = s.y[i];
-                double bd = DBL_MAX;
-                int bj = -1;
-                for (int ww = 0; ww < nw; ww++) {
-                    uint32_t bits = s.adj[i * NW + ww];
-                    while (bits) {
-                        const int b = __ffs(bits) - 1;
-                        bits &= bits - 1;
-                        const int j = ww * 32 + b;
-                        const int lj = s.label[j];
-                        if (lj != li && fabs(oi - s.orient[lj]) < pc.cl_orient_rad) {          // :147-154
-                            const double ddx = xi - s.x[j], ddy = yi - s.y[j];
-                            const double d = sqrt(ddx * ddx + ddy * ddy);
-                            if (d < bd) { bd = d; bj = j; }                                     // first minimum (j ascending)
-                        }
-                    }
-                }
-                found = bj >= 0 && int(s.size[s.label[bj]]) + int(s.size[li]) <= pc.max_cluster;   // :166
-                s.rank[i] = int16_t(found ? bj : -1);
-            }
+            const bool found = ((dw >> lane) & 1u) && merge_candidate<N>(s, i, nw, pc);
             const unsigned m = __ballot_sync(FULL, found);
             if (lane == 0) { s.canw[w] = (s.canw[w] & ~dw) | m; s.dirty[w] = 0u; }
         }
@@ -633,9 +646,9 @@ __device__ void cluster_warp_sm(int n, const PassConst& pc, ClusterSm<N>& s, con
         if (mi < 0) break;
         const int mj = s.rank[mi];
         const int old_l = s.label[mj], new_l = s.label[mi];
-        const int cnt = member_list(s, n, old_l, new_l, lane, lt);
+        const int cnt = member_list(s, s.mem, n, old_l, new_l, lane, lt);
         double gx, gy, gth;
-        gauss_avg_list<N, true>(s, cnt, pc.cl_sigma, lane, &gx, &gy, &gth);       // :168
+        gauss_avg_list<N, true>(s, s.mem, cnt, pc.cl_sigma, lane, &gx, &gy, &gth);       // :168
         if (lane == 0) { s.orient[new_l] = normalize_orientation(gth, pc.cl_wrap_deg); s.size[new_l] = int16_t(cnt); }   // :175-176
         for (int k = lane; k < n; k += 32) if (s.label[k] == old_l) s.label[k] = int16_t(new_l);   // :179-183
         for (int w = lane; w < nw; w += 32) {                            // members + everything adjacent to a member
@@ -666,9 +679,9 @@ __device__ void cluster_warp_sm(int n, const PassConst& pc, ClusterSm<N>& s, con
         while (roots) {
             const int i = base + __ffs(roots) - 1;
             roots &= roots - 1;
-            const int cnt = member_list(s, n, i, i, lane, lt);
+            const int cnt = member_list(s, s.mem, n, i, i, lane, lt);
             double gx, gy, gth;
-            gauss_avg_list<N, false>(s, cnt, pc.cl_sigma, lane, &gx, &gy, &gth);
+            gauss_avg_list<N, false>(s, s.mem, cnt, pc.cl_sigma, lane, &gx, &gy, &gth);
             double d = DBL_MAX;
             int pos = lane;
             if (lane < cnt) {
@@ -692,6 +705,167 @@ __device__ void cluster_warp_sm(int n, const PassConst& pc, ClusterSm<N>& s, con
     }
     for (int k = lane; k < n; k += 32) { const int l = s.label[k]; label_out[k] = l; urank[k] = s.rank[l]; }
     if (lane == 0) *n_clusters = nroots;
+}
+
+// ---- the same clustering by W warps per view-1 edge (the > 128-row classes).  The merge sequence is inherently serial, but every
+// merge is made of data-parallel pieces: re-evaluating the dirty rows (words of 32 rows strided over the warps), collecting the
+// member mask, relabelling, and the dirty-set update; the Gaussian average stays on one warp and runs beside the relabel (other
+// warps) and the dirty-set update (warp 1).  Three named barriers per merge.  Results are identical to cluster_warp_sm: the same
+// decisions in the same order, the same arithmetic per member in the same order.
+template <int N>
+struct ClusterSmB {
+    ClusterSm<N> s;
+    uint32_t wmask[N / 32];       // member mask of the merge in flight / root mask in the final phase
+    int16_t memw[8][32];          // per-warp member lists of the final per-cluster averages
+};
+static_assert(CL_SMALL_WARPS * sizeof(ClusterSm<CL_N>) <= CL_SMEM_QUANTUM && CL_MID_EDGES * sizeof(ClusterSmB<CL_MID_N>) <= CL_SMEM_QUANTUM &&
+              sizeof(ClusterSmB<CL_BIG_N>) <= CL_SMEM_QUANTUM, "clustering classes must fit the common shared-memory size");
+__device__ __forceinline__ void bar_sync(int id, int nthreads) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory"); }
+template <int N, int W>
+__device__ void cluster_block_sm(int n, const PassConst& pc, ClusterSmB<N>& sb, const double* __restrict__ xc, const double* __restrict__ yc,
+                                 const double* __restrict__ th, const int32_t* __restrict__ h2orig, double* xbar, double* ybar, double* thbar,
+                                 int32_t* label_out, int32_t* h2rep, int32_t* urank, int32_t* n_clusters, int gw, int lane, int bar_id) {
+    static_assert(W >= 4 && W <= 8 && N / 32 <= 32, "cluster_block_sm: 4..8 warps, at most 32 row words");
+    constexpr int NW = N / 32, T = W * 32;
+    ClusterSm<N>& s = sb.s;
+    const unsigned lt = lanemask_lt();
+    const int t = gw * 32 + lane;
+    const int nw = (n + 31) >> 5;
+    for (int k = t; k < n; k += T) {
+        const double o = normalize_orientation(th[k], pc.cl_wrap_deg);   // :131-135
+        s.x[k] = xc[k]; s.y[k] = yc[k]; s.thn[k] = o; s.orient[k] = o; s.label[k] = int16_t(k); s.size[k] = 1;
+    }
+    if (t < nw) { const int rem = n - t * 32; s.dirty[t] = rem >= 32 ? 0xffffffffu : ((1u << rem) - 1u); s.canw[t] = 0u; }
+    bar_sync(bar_id, T);
+    for (int i = t; i < n; i += T) {                                      // adjacency: dist(i, j) < CLUSTER_DIST_THRESH
+        const double xi = s.x[i], yi = s.y[i];
+        for (int w = 0; w < nw; w++) {
+            uint32_t bits = 0;
+            const int jend = min(32, n - w * 32);
+            for (int b = 0; b < jend; b++) {
+                const int j = w * 32 + b;
+                const double ddx = xi - s.x[j], ddy = yi - s.y[j];
+                if (ddx * ddx + ddy * ddy < pc.cl_dist_sq && j != i) bits |= (1u << b);
+            }
+            s.adj[i * NW + w] = bits;
+        }
+    }
+    bar_sync(bar_id, T);
+    while (true) {
+        for (int w = gw; w < nw; w += W) {                                // dirty rows, a word of 32 rows per warp step
+            const uint32_t dw = s.dirty[w];
+            if (!dw) continue;
+            const int i = w * 32 + lane;
+            const bool found = ((dw >> lane) & 1u) && merge_candidate<N>(s, i, nw, pc);
+            const unsigned m = __ballot_sync(FULL, found);
+            if (lane == 0) { s.canw[w] = (s.canw[w] & ~dw) | m; s.dirty[w] = 0u; }
+        }
+        bar_sync(bar_id, T);
+        // first row that can merge (every warp finds the same one)
+        const uint32_t cw = lane < nw ? s.canw[lane] : 0u;
+        const unsigned nz = __ballot_sync(FULL, cw != 0u);
+        if (!nz) break;
+        const int fw = __ffs(nz) - 1;
+        const int mi = fw * 32 + __ffs(__shfl_sync(FULL, cw, fw)) - 1;
+        const int mj = s.rank[mi];
+        const int old_l = s.label[mj], new_l = s.label[mi];
+        for (int w = gw; w < nw; w += W) {                                // members of the two clusters, a mask word per warp step
+            const int k = w * 32 + lane;
+            const int l = k < n ? int(s.label[k]) : -1;
+            const unsigned m = __ballot_sync(FULL, l == old_l || l == new_l);
+            if (lane == 0) sb.wmask[w] = m;
+        }
+        bar_sync(bar_id, T);
+        if (gw == 0) {                                                    // ascending member list, Gaussian average (:168-176)
+            const uint32_t wm = lane < nw ? sb.wmask[lane] : 0u;
+            int incl = __popc(wm);
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) { const int v = __shfl_up_sync(FULL, incl, o); if (lane >= o) incl += v; }
+            int pos = incl - __popc(wm);
+            uint32_t bits = wm;
+            while (bits) {
+                const int b = __ffs(bits) - 1;
+                bits &= bits - 1;
+                if (pos < 32) s.mem[pos] = int16_t(lane * 32 + b);
+                pos++;
+            }
+            const int cnt = min(32, __shfl_sync(FULL, incl, 31));
+            __syncwarp();
+            double gx, gy, gth;
+            gauss_avg_list<N, true>(s, s.mem, cnt, pc.cl_sigma, lane, &gx, &gy, &gth);
+            if (lane == 0) { s.orient[new_l] = normalize_orientation(gth, pc.cl_wrap_deg); s.size[new_l] = int16_t(cnt); }
+        } else if (gw == 1) {                                             // dirty set: the members and every row adjacent to one
+            uint32_t d = lane < nw ? sb.wmask[lane] : 0u;
+            for (int ww = 0; ww < nw; ww++) {
+                uint32_t bits = sb.wmask[ww];
+                while (bits) {
+                    const int mrow = ww * 32 + __ffs(bits) - 1;
+                    bits &= bits - 1;
+                    if (lane < nw) d |= s.adj[mrow * NW + lane];
+                }
+            }
+            if (lane < nw) s.dirty[lane] = d;
+        } else {                                                          // relabel (:179-183)
+            for (int w = gw - 2; w < nw; w += W - 2)
+                if ((sb.wmask[w] >> lane) & 1u) s.label[w * 32 + lane] = int16_t(new_l);
+        }
+        bar_sync(bar_id, T);
+    }
+    // ranks of the cluster roots (label[k] == k) in ascending label order
+    for (int w = gw; w < nw; w += W) {
+        const int k = w * 32 + lane;
+        const unsigned m = __ballot_sync(FULL, k < n && s.label[k] == k);
+        if (lane == 0) sb.wmask[w] = m;
+    }
+    bar_sync(bar_id, T);
+    const uint32_t rm = lane < nw ? sb.wmask[lane] : 0u;
+    int rincl = __popc(rm);
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const int v = __shfl_up_sync(FULL, rincl, o); if (lane >= o) rincl += v; }
+    const int nroots = __shfl_sync(FULL, rincl, 31);
+    const int rexcl = rincl - __popc(rm);
+    for (int w = gw; w < nw; w += W) {
+        const int base = __shfl_sync(FULL, rexcl, w);
+        const uint32_t m = __shfl_sync(FULL, rm, w);
+        if ((m >> lane) & 1u) s.rank[w * 32 + lane] = int16_t(base + __popc(m & lt));
+    }
+    // :250-290 per cluster (see cluster_warp_sm): one-member clusters directly, the others a warp each
+    for (int k = t; k < n; k += T)
+        if (s.label[k] == k && s.size[k] == 1) { xbar[k] = s.x[k]; ybar[k] = s.y[k]; thbar[k] = s.thn[k]; h2rep[k] = h2orig[k]; }
+    int16_t* mem = sb.memw[gw];
+    for (int w = gw; w < nw; w += W) {
+        const int kk = w * 32 + lane;
+        unsigned roots = __ballot_sync(FULL, kk < n && s.label[kk] == kk && s.size[kk] > 1);
+        while (roots) {
+            const int i = w * 32 + __ffs(roots) - 1;
+            roots &= roots - 1;
+            const int cnt = member_list(s, mem, n, i, i, lane, lt);
+            double gx, gy, gth;
+            gauss_avg_list<N, false>(s, mem, cnt, pc.cl_sigma, lane, &gx, &gy, &gth);
+            double d = DBL_MAX;
+            int pos = lane;
+            if (lane < cnt) {
+                const int j = mem[lane];
+                const double ddx = s.x[j] - gx, ddy = s.y[j] - gy;
+                d = sqrt(ddx * ddx + ddy * ddy);
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {                            // first minimum in member order (:270)
+                const double od = __shfl_xor_sync(FULL, d, o);
+                const int op = __shfl_xor_sync(FULL, pos, o);
+                if (od < d || (od == d && op < pos)) { d = od; pos = op; }
+            }
+            const int rep = h2orig[mem[pos]];                             // corrected(closest, 8), :282
+            if (lane < cnt) {
+                const int j = mem[lane];
+                xbar[j] = gx; ybar[j] = gy; thbar[j] = gth; h2rep[j] = rep;
+            }
+            __syncwarp();
+        }
+    }
+    bar_sync(bar_id, T);                                                  // ranks complete
+    for (int k = t; k < n; k += T) { const int l = s.label[k]; label_out[k] = l; urank[k] = s.rank[l]; }
+    if (t == 0) *n_clusters = nroots;
 }
 
 // ---- global-memory fallback for groups larger than CL_N rows (same semantics, the plain sequential scan order)
@@ -959,6 +1133,51 @@ __global__ void __launch_bounds__(WARPS * 32) k_cluster(const __grid_constant__ 
         __syncwarp();
     }
 }
+// The <= 128 / 256 / 512-row classes in ONE launch.  A block is a "unit" of one shared-memory size (CL_SMEM_QUANTUM): one 512-row edge
+// (all 8 warps), two 256-row edges (4 warps each) or eight <= 128-row edges (a warp each); units are numbered longest class first, so the hardware
+// hands out the long sequential chains before the many short ones.  (As separate launches on side streams the long classes
+// starved: the block scheduler finishes handing out the blocks of the grid that arrived first -- the small class, a few
+// microseconds ahead -- before it starts the next grid, so the longest chains began 0.3 - 0.9 ms late on cfg2.)
+template <int N>
+__device__ __forceinline__ void cluster_edge(int h1, const PassConst& pc, ClusterSm<N>& s, const int32_t* __restrict__ n_of,
+                                             const int64_t* __restrict__ row_off, const RowTable& rt, int32_t* n_clusters, int lane) {
+    const int64_t row0 = row_off[h1];
+    cluster_warp_sm<N>(n_of[h1], pc, s, rt.xc + row0, rt.yc + row0, rt.th + row0, rt.h2orig + row0, rt.xbar + row0, rt.ybar + row0,
+                       rt.thbar + row0, rt.label + row0, rt.h2rep + row0, rt.urank + row0, n_clusters + h1, lane);
+}
+template <int N, int W>
+__device__ __forceinline__ void cluster_edge_block(int h1, const PassConst& pc, ClusterSmB<N>& sb, const int32_t* __restrict__ n_of,
+                                                   const int64_t* __restrict__ row_off, const RowTable& rt, int32_t* n_clusters, int gw, int lane,
+                                                   int bar_id) {
+    const int64_t row0 = row_off[h1];
+    cluster_block_sm<N, W>(n_of[h1], pc, sb, rt.xc + row0, rt.yc + row0, rt.th + row0, rt.h2orig + row0, rt.xbar + row0, rt.ybar + row0,
+                           rt.thbar + row0, rt.label + row0, rt.h2rep + row0, rt.urank + row0, n_clusters + h1, gw, lane, bar_id);
+}
+__global__ void __launch_bounds__(CL_SMALL_WARPS * 32, 4) k_cluster_classes(const __grid_constant__ PassConst pc, const int32_t* __restrict__ order,
+                                                                         const int32_t* __restrict__ cnts, const int32_t* __restrict__ n_of,
+                                                                         const int64_t* __restrict__ row_off, RowTable rt, int32_t* n_clusters) {
+    extern __shared__ __align__(16) unsigned char cl_smem[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int n_small = cnts[0], n_mid = cnts[1], n_big = cnts[2];
+    const int u_big = n_big, u_mid = (n_mid + CL_MID_EDGES - 1) / CL_MID_EDGES, u_small = (n_small + CL_SMALL_WARPS - 1) / CL_SMALL_WARPS;
+    const int units = u_big + u_mid + u_small;
+    for (int unit = blockIdx.x; unit < units; unit += gridDim.x) {
+        if (unit < u_big) {                                               // one edge, the whole block
+            cluster_edge_block<CL_BIG_N, CL_SMALL_WARPS>(order[n_small + n_mid + unit], pc, *reinterpret_cast<ClusterSmB<CL_BIG_N>*>(cl_smem), n_of, row_off,
+                                                         rt, n_clusters, warp, lane, 1);
+        } else if (unit < u_big + u_mid) {                                // CL_MID_EDGES edges, CL_MID_WARPS warps each
+            const int g = warp / CL_MID_WARPS;
+            const int e = (unit - u_big) * CL_MID_EDGES + g;
+            if (e < n_mid)
+                cluster_edge_block<CL_MID_N, CL_MID_WARPS>(order[n_small + e], pc, reinterpret_cast<ClusterSmB<CL_MID_N>*>(cl_smem)[g], n_of, row_off, rt,
+                                                           n_clusters, warp - g * CL_MID_WARPS, lane, 1 + g);
+        } else {                                                          // one <= 128-row edge per warp
+            const int e = (unit - u_big - u_mid) * CL_SMALL_WARPS + warp;
+            if (e < n_small) cluster_edge<CL_N>(order[e], pc, reinterpret_cast<ClusterSm<CL_N>*>(cl_smem)[warp], n_of, row_off, rt, n_clusters, lane);
+        }
+        if (unit + int(gridDim.x) < units) __syncthreads();   // the next unit may lay the shared memory out differently
+    }
+}
 __global__ void __launch_bounds__(32) k_cluster_huge(const __grid_constant__ PassConst pc, const int32_t* __restrict__ order,
                                                      const int32_t* __restrict__ cnts, const int32_t* __restrict__ n_of,
                                                      const int64_t* __restrict__ row_off, RowTable rt, int32_t* n_clusters) {
@@ -995,19 +1214,32 @@ void launch_form_fill(const PassConst& pc, const double* x1, const double* y1, i
     int32_t* order = big_list;
     int32_t* cnts = big_count;
     k_order_by_n<<<1, 1024, 0, st>>>(n_of, h1_begin, h1_end, pc.max_cluster, order, cnts);
-    const size_t sm_small = FORM_WARPS * sizeof(ClusterSm<CL_N>), sm_mid = 2 * sizeof(ClusterSm<CL_MID_N>), sm_big = sizeof(ClusterSm<CL_BIG_N>);
-    cudaFuncSetAttribute(k_cluster<CL_BIG_N, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sm_big));   // per device, cheap
-    const size_t sm_huge = sizeof(ClusterSm<CL_HUGE_N>);
+    const size_t sm_q = CL_SMEM_QUANTUM, sm_huge = sizeof(ClusterSm<CL_HUGE_N>);
+    cudaFuncSetAttribute(k_cluster_classes, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sm_q));   // per device, cheap
     cudaFuncSetAttribute(k_cluster<CL_HUGE_N, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sm_huge));
-    // the few long-running edges of the larger classes go to a side stream and run beside the many small ones (fork / join)
-    cudaStream_t big = side ? side : st;
+    // the rare > 512-row edges (one 171 KB block per SM, or the global-memory fallback) run beside the rest on a side stream
+    cudaStream_t s_huge = side ? side : st;
+    // CVX_FORM_DEBUG=1: per-launch start / end times (stderr); a diagnostic, it synchronises the device
+    static const bool dbg = getenv("CVX_FORM_DEBUG") != nullptr;
+    cudaEvent_t de[4];
+    if (dbg) for (auto& e : de) cudaEventCreate(&e);
     if (side) { cudaEventRecord(ev_fork, st); cudaStreamWaitEvent(side, ev_fork, 0); }
-    k_cluster<CL_HUGE_N, 1><<<std::min(n, 148), 32, sm_huge, big>>>(pc, order, cnts, 3, n_of, row_off, rt, n_clusters);
-    k_cluster<CL_BIG_N, 1><<<std::min(n, 148 * 4), 32, sm_big, big>>>(pc, order, cnts, 2, n_of, row_off, rt, n_clusters);
-    k_cluster<CL_MID_N, 2><<<std::min((n + 1) / 2, 148 * 6), 64, sm_mid, big>>>(pc, order, cnts, 1, n_of, row_off, rt, n_clusters);
-    k_cluster_huge<<<std::min(n, 148 * 4), 32, 0, big>>>(pc, order, cnts, n_of, row_off, rt, n_clusters);
+    if (dbg) cudaEventRecord(de[0], s_huge);
+    k_cluster<CL_HUGE_N, 1><<<std::min(n, 148), 32, sm_huge, s_huge>>>(pc, order, cnts, 3, n_of, row_off, rt, n_clusters);
+    k_cluster_huge<<<std::min(n, 148 * 4), 32, 0, s_huge>>>(pc, order, cnts, n_of, row_off, rt, n_clusters);
+    if (dbg) { cudaEventRecord(de[1], s_huge); cudaEventRecord(de[2], st); }
     if (side) cudaEventRecord(ev_join, side);
-    k_cluster<CL_N, FORM_WARPS><<<(n + FORM_WARPS - 1) / FORM_WARPS, FORM_WARPS * 32, sm_small, st>>>(pc, order, cnts, 0, n_of, row_off, rt, n_clusters);
+    // one block per unit in the common case (units ~ n / 8 plus the few long edges); beyond that the blocks stride
+    const int grid = std::min(n, (n + CL_SMALL_WARPS - 1) / CL_SMALL_WARPS + 148 * 4);
+    k_cluster_classes<<<grid, CL_SMALL_WARPS * 32, sm_q, st>>>(pc, order, cnts, n_of, row_off, rt, n_clusters);
+    if (dbg) {
+        cudaEventRecord(de[3], st);
+        cudaDeviceSynchronize();
+        float t[4];
+        for (int i = 0; i < 4; i++) cudaEventElapsedTime(&t[i], de[2], de[i]);
+        fprintf(stderr, "[form] relative to the k_cluster_classes launch: > 512-row classes %.3f..%.3f, <= 512-row classes 0..%.3f ms\n", t[0], t[1], t[3]);
+        for (auto& e : de) cudaEventDestroy(e);
+    }
     if (side) cudaStreamWaitEvent(st, ev_join, 0);
 }
 

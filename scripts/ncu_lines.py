@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Per-source-line hot spots of one kernel from an .ncu-rep captured with --import-source on (needs -lineinfo).
 
-    python scripts/ncu_lines.py gpurun_out/prof.ncu-rep k_validate [top_n]
+    python scripts/ncu_lines.py gpurun_out/prof.ncu-rep k_validate [top_n [launch_index]]
 
 Aggregates the 'cuda,sass' source page: warp-stall samples and executed warp instructions per (file, line), plus the
 dominant stall reasons of each line.
@@ -15,6 +15,7 @@ import sys
 def main():
     rep, kern = sys.argv[1], sys.argv[2]
     top = int(sys.argv[3]) if len(sys.argv) > 3 else 40
+    which = int(sys.argv[4]) + 1 if len(sys.argv) > 4 else 1    # n-th captured launch that matches (0-based on the command line)
     out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--print-source", "cuda,sass", "--csv", "--kernel-name", "regex:" + kern],
                          capture_output=True, text=True).stdout
     rows = list(csv.reader(out.splitlines()))
@@ -26,8 +27,10 @@ def main():
             continue
         if r[0] == "Kernel Name":
             kernels_seen += 1
-            if kernels_seen > 1:
-                break           # first captured launch only
+            if kernels_seen > which:
+                break           # one captured launch only
+            continue
+        if kernels_seen != which:
             continue
         if r[0] == "File Name":
             fname = (r[1] or "?").split("/")[-1]
@@ -50,7 +53,7 @@ def main():
                 a["stalls"][k[6:]] += int(v)
     ts = sum(a["samples"] for a in agg.values()) or 1
     ti = sum(a["inst"] for a in agg.values()) or 1
-    print(f"# {rep} kernel~{kern}: {ts} samples, {ti} warp instructions (first captured launch)")
+    print(f"# {rep} kernel~{kern}: {ts} samples, {ti} warp instructions (captured launch {which - 1} of the match)")
     print(f"{'file:line':28s} {'samp%':>6s} {'inst%':>6s}  top stalls | source")
     for (f, ln), a in sorted(agg.items(), key=lambda x: -x[1]["samples"])[:top]:
         st = " ".join(f"{k}:{v}" for k, v in a["stalls"].most_common(3))
