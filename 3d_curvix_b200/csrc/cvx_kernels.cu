@@ -513,10 +513,10 @@ struct ClusterSm {
     uint32_t dirty[N / 32], canw[N / 32];   // rows whose merge decision must be re-evaluated / rows that can merge (bit per row)
     int16_t label[N], size[N], rank[N], mem[32];   // rank doubles as the cached merge partner during the merge phase
 };
-#define CL_N 128          // rows handled by the shared-memory path inside k_form
-#define CL_MID_N 256      // size classes of the clustering launches: <= CL_N (4 warps per block), <= CL_MID_N (18 KB per warp),
-#define CL_BIG_N 512      // <= CL_BIG_N (one warp per block, 53 KB of shared memory), <= CL_HUGE_N (one warp per block, 171 KB: one block
-#define CL_HUGE_N 1024    // per SM); beyond: global-memory fallback
+#define CL_N 128           // size classes: <= CL_N rows (a warp per edge), <= CL_MID_N (4 warps per edge), <= CL_BIG_N (8 warps per edge) --
+#define CL_MID_N 256       // these three share one launch, k_cluster_classes; <= CL_HUGE_N (8 warps per edge, 171 KB of shared memory: one
+#define CL_BIG_N 512       // block per SM, k_cluster_coop); beyond that, or MAX_CLUSTER_SIZE > 32: global-memory fallback (k_cluster_huge)
+#define CL_HUGE_N 1024
 #define FORM_WARPS 4
 // The <= 128 / 256 / 512-row classes share one launch (k_cluster_classes): every block has the same shared-memory size and holds
 // one 512-row edge (8 warps), two 256-row edges (4 warps each) or eight <= 128-row edges (a warp each).
@@ -1096,13 +1096,13 @@ __global__ void __launch_bounds__(FORM_WARPS * 32) k_form(const __grid_constant_
 // k_order_by_n: one block; order[] = edges with 1 <= n <= CL_N sorted by n descending, then those with CL_N < n <= CL_BIG_N, then
 // then CL_MID_N < n <= CL_BIG_N, then CL_BIG_N < n <= CL_HUGE_N, then the rest; cnts[0..4] = the five counts.
 #define ORDER_BUCKETS (CL_N + 4)
-__global__ void __launch_bounds__(1024) k_order_by_n(const int32_t* __restrict__ n_of, int h1_begin, int h1_end, int max_cluster,
+__global__ void __launch_bounds__(1024) k_order_by_n(const int32_t* __restrict__ n_of, int h1_begin, int h1_end, int max_cluster, int small_max,
                                                      int32_t* __restrict__ order, int32_t* __restrict__ cnts) {
     __shared__ int hist[ORDER_BUCKETS];
     for (int k = threadIdx.x; k < ORDER_BUCKETS; k += blockDim.x) hist[k] = 0;
     __syncthreads();
     const bool sm_ok = max_cluster <= 32;          // the shared-memory algorithm keeps member lists of at most 32
-    auto key = [&](int n) { return (!sm_ok || n > CL_HUGE_N) ? CL_N + 3 : n > CL_BIG_N ? CL_N + 2 : n > CL_MID_N ? CL_N + 1 : n > CL_N ? CL_N : CL_N - n; };
+    auto key = [&](int n) { return (!sm_ok || n > CL_HUGE_N) ? CL_N + 3 : n > CL_BIG_N ? CL_N + 2 : n > CL_MID_N ? CL_N + 1 : n > small_max ? CL_N : CL_N - n; };
     for (int i = h1_begin + threadIdx.x; i < h1_end; i += blockDim.x) { const int n = n_of[i]; if (n > 0) atomicAdd(&hist[key(n)], 1); }
     __syncthreads();
     if (threadIdx.x == 0) {
@@ -1114,24 +1114,6 @@ __global__ void __launch_bounds__(1024) k_order_by_n(const int32_t* __restrict__
     }
     __syncthreads();
     for (int i = h1_begin + threadIdx.x; i < h1_end; i += blockDim.x) { const int n = n_of[i]; if (n > 0) order[atomicAdd(&hist[key(n)], 1)] = i; }
-}
-template <int N, int WARPS>
-__global__ void __launch_bounds__(WARPS * 32) k_cluster(const __grid_constant__ PassConst pc, const int32_t* __restrict__ order,
-                                                        const int32_t* __restrict__ cnts, int which, const int32_t* __restrict__ n_of,
-                                                        const int64_t* __restrict__ row_off, RowTable rt, int32_t* n_clusters) {
-    extern __shared__ __align__(16) unsigned char cl_smem[];
-    ClusterSm<N>& s = reinterpret_cast<ClusterSm<N>*>(cl_smem)[threadIdx.x >> 5];
-    const int lane = threadIdx.x & 31;
-    int base = 0;
-    for (int k = 0; k < which; k++) base += cnts[k];
-    const int cnt = cnts[which];
-    for (int b = blockIdx.x * WARPS + (threadIdx.x >> 5); b < cnt; b += gridDim.x * WARPS) {
-        const int h1 = order[base + b];
-        const int64_t row0 = row_off[h1];
-        cluster_warp_sm<N>(n_of[h1], pc, s, rt.xc + row0, rt.yc + row0, rt.th + row0, rt.h2orig + row0, rt.xbar + row0, rt.ybar + row0,
-                           rt.thbar + row0, rt.label + row0, rt.h2rep + row0, rt.urank + row0, n_clusters + h1, lane);
-        __syncwarp();
-    }
 }
 // The <= 128 / 256 / 512-row classes in ONE launch.  A block is a "unit" of one shared-memory size (CL_SMEM_QUANTUM): one 512-row edge
 // (all 8 warps), two 256-row edges (4 warps each) or eight <= 128-row edges (a warp each); units are numbered longest class first, so the hardware
@@ -1178,6 +1160,21 @@ __global__ void __launch_bounds__(CL_SMALL_WARPS * 32, 4) k_cluster_classes(cons
         if (unit + int(gridDim.x) < units) __syncthreads();   // the next unit may lay the shared memory out differently
     }
 }
+// the 513..1024-row class: one edge per block of W warps, one block per SM (171 KB of shared memory)
+template <int N, int W>
+__global__ void __launch_bounds__(W * 32) k_cluster_coop(const __grid_constant__ PassConst pc, const int32_t* __restrict__ order,
+                                                         const int32_t* __restrict__ cnts, int which, const int32_t* __restrict__ n_of,
+                                                         const int64_t* __restrict__ row_off, RowTable rt, int32_t* n_clusters) {
+    extern __shared__ __align__(16) unsigned char cl_smem[];
+    int base = 0;
+    for (int k = 0; k < which; k++) base += cnts[k];
+    const int cnt = cnts[which];
+    for (int b = blockIdx.x; b < cnt; b += gridDim.x) {
+        cluster_edge_block<N, W>(order[base + b], pc, *reinterpret_cast<ClusterSmB<N>*>(cl_smem), n_of, row_off, rt, n_clusters, threadIdx.x >> 5,
+                                 threadIdx.x & 31, 1);
+        __syncthreads();
+    }
+}
 __global__ void __launch_bounds__(32) k_cluster_huge(const __grid_constant__ PassConst pc, const int32_t* __restrict__ order,
                                                      const int32_t* __restrict__ cnts, const int32_t* __restrict__ n_of,
                                                      const int64_t* __restrict__ row_off, RowTable rt, int32_t* n_clusters) {
@@ -1210,13 +1207,14 @@ void launch_form_fill(const PassConst& pc, const double* x1, const double* y1, i
     k_form<true><<<(n + FORM_WARPS - 1) / FORM_WARPS, FORM_WARPS * 32, smem, st>>>(pc, x1, y1, h1_begin, h1_end, wedge_h1, x2, y2, th2, ang2, E2, ix,
                                                                                   const_cast<int32_t*>(m_of), const_cast<int32_t*>(n_of), row_off, rt,
                                                                                   n_clusters);
-    // clustering: order by hypothesis count, then one launch per size class (blocks past the class's count exit at once)
+    // clustering: order by hypothesis count, then the shared-memory classes (one launch) beside the rare larger groups
     int32_t* order = big_list;
     int32_t* cnts = big_count;
-    k_order_by_n<<<1, 1024, 0, st>>>(n_of, h1_begin, h1_end, pc.max_cluster, order, cnts);
-    const size_t sm_q = CL_SMEM_QUANTUM, sm_huge = sizeof(ClusterSm<CL_HUGE_N>);
+    static const int small_max = getenv("CVX_CL_SMALL_MAX") ? std::min(CL_N, std::max(1, atoi(getenv("CVX_CL_SMALL_MAX")))) : CL_N;
+    k_order_by_n<<<1, 1024, 0, st>>>(n_of, h1_begin, h1_end, pc.max_cluster, small_max, order, cnts);
+    const size_t sm_q = CL_SMEM_QUANTUM, sm_huge = sizeof(ClusterSmB<CL_HUGE_N>);
     cudaFuncSetAttribute(k_cluster_classes, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sm_q));   // per device, cheap
-    cudaFuncSetAttribute(k_cluster<CL_HUGE_N, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sm_huge));
+    cudaFuncSetAttribute(k_cluster_coop<CL_HUGE_N, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sm_huge));
     // the rare > 512-row edges (one 171 KB block per SM, or the global-memory fallback) run beside the rest on a side stream
     cudaStream_t s_huge = side ? side : st;
     // CVX_FORM_DEBUG=1: per-launch start / end times (stderr); a diagnostic, it synchronises the device
@@ -1225,7 +1223,7 @@ void launch_form_fill(const PassConst& pc, const double* x1, const double* y1, i
     if (dbg) for (auto& e : de) cudaEventCreate(&e);
     if (side) { cudaEventRecord(ev_fork, st); cudaStreamWaitEvent(side, ev_fork, 0); }
     if (dbg) cudaEventRecord(de[0], s_huge);
-    k_cluster<CL_HUGE_N, 1><<<std::min(n, 148), 32, sm_huge, s_huge>>>(pc, order, cnts, 3, n_of, row_off, rt, n_clusters);
+    k_cluster_coop<CL_HUGE_N, 8><<<std::min(n, 148), 256, sm_huge, s_huge>>>(pc, order, cnts, 3, n_of, row_off, rt, n_clusters);
     k_cluster_huge<<<std::min(n, 148 * 4), 32, 0, s_huge>>>(pc, order, cnts, n_of, row_off, rt, n_clusters);
     if (dbg) { cudaEventRecord(de[1], s_huge); cudaEventRecord(de[2], st); }
     if (side) cudaEventRecord(ev_join, side);

@@ -30,7 +30,7 @@ def main():
             if kernels_seen > which:
                 break           # one captured launch only
             continue
-        if kernels_seen != which:
+        if kernels_seen and kernels_seen != which:   # reports without 'Kernel Name' rows aggregate every captured launch
             continue
         if r[0] == "File Name":
             fname = (r[1] or "?").split("/")[-1]

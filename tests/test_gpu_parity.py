@@ -41,8 +41,9 @@ def test_tiny_scene_full_parity(oracle_mod, tiny_scene):
 
 
 def test_large_hypothesis_groups_parity(oracle_mod, data_mod):
-    """Dense views: hypothesis groups of 128 < n <= 512 rows are clustered by k_cluster_big, n > 512 by the global-memory
-    fallback; both must reproduce the oracle's greedy merge order exactly.  Also exercises the packed all-view upload."""
+    """Dense views: hypothesis groups of 129..256 and 257..512 rows are clustered by 4 / 8 warps per edge inside
+    k_cluster_classes, 513..1024 rows by k_cluster_coop (block-cooperative merge, named barriers); all must reproduce the
+    oracle's greedy merge order exactly.  Also exercises the packed all-view upload."""
     scene = data_mod.make_synthetic_scene(n_views=6, edges_per_view=40000, rows=800, cols=800, seed=11, n_curves=12)
     o = make_oracle(oracle_mod, scene, max_support_views=2)
     api = pkg("api")
@@ -52,7 +53,9 @@ def test_large_hypothesis_groups_parity(oracle_mod, data_mod):
     g.set_all_view_edges(scene.edges)
     o.set_pair(0, 1); g.set_pair(0, 1)
     n = g.run(0, 1500).h1_table()["n"]
-    assert ((n > 128) & (n <= 512)).sum() > 50, "scene no longer produces medium-size groups"
+    n = n[:1500]
+    assert ((n > 128) & (n <= 256)).sum() > 50 and ((n > 256) & (n <= 512)).sum() > 50 and ((n > 512) & (n <= 1024)).sum() > 5, \
+        "scene no longer populates every clustering size class"
     o.run(0, 1500, mode=1, keep=True)
     rep = compare(o, g, check_intermediates=True)
     _report("large_groups_0_1", rep)
