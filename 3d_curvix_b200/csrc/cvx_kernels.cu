@@ -1325,7 +1325,6 @@ __device__ __forceinline__ double4 ld_rec(const double4* p) {   // one 256-bit l
 // ascending index order), so it is not loaded on the common path: the walk carries the POSITION of the best entry.
 __device__ __forceinline__ void support_visit(SupportAcc& s, const double4 e, int j, const double2 w1, const double2 w2, const double2 tg,
                                               double thr, const int32_t* __restrict__ idx_) {
-    s.n_vis++;
     if (e.x > w1.x && e.x < w1.y && e.y > w2.x && e.y < w2.y) {          // PairEdgeHypo.cpp:94, both wedges
         s.n_in++;
         const double d = fabs(tg.x * e.z + tg.y * e.w);                   // getSupportedEdgels.cpp:38
@@ -1418,13 +1417,14 @@ __global__ void __launch_bounds__(VAL_THREADS, VAL_MIN_BLOCKS) k_validate(const 
             // the (at most VAL_LIGHT_ROWS) ranges are walked as one flattened list, VAL_BATCH entries per step, so that several
             // independent 32-byte loads are in flight per lane instead of one (the walk is latency bound)
             const int l0 = end[0] - beg[0], l1 = l0 + (end[1] - beg[1]), l2 = l1 + (end[2] - beg[2]);
+            const int g0 = beg[1] - end[0], g1 = beg[2] - end[1], g2 = beg[3] - end[2];   // jumps between consecutive ranges
             for (int k = 0; k < work; k += VAL_BATCH) {
                 int j[VAL_BATCH];
                 double4 e[VAL_BATCH];
 #pragma unroll
                 for (int t = 0; t < VAL_BATCH; t++) {
                     const int kk = min(k + t, work - 1);
-                    j[t] = kk < l0 ? beg[0] + kk : kk < l1 ? beg[1] + (kk - l0) : kk < l2 ? beg[2] + (kk - l1) : beg[3] + (kk - l2);
+                    j[t] = beg[0] + kk + (kk >= l0 ? g0 : 0) + (kk >= l1 ? g1 : 0) + (kk >= l2 ? g2 : 0);
                 }
 #pragma unroll
                 for (int t = 0; t < VAL_BATCH; t++) e[t] = ld_rec(rec + j[t]);
@@ -1432,12 +1432,14 @@ __global__ void __launch_bounds__(VAL_THREADS, VAL_MIN_BLOCKS) k_validate(const 
                 for (int t = 0; t < VAL_BATCH; t++)
                     if (t == 0 || k + t < work) support_visit(acc, e[t], j[t], w1, w2, tg, a.cos_thresh, idx_);
             }
+            acc.n_vis = unsigned(work);                 // entries visited (statistics)
         } else {
             const int32_t* __restrict__ ce = L.cell_end + ce_off;
             for (int b = r0; b <= r1; b++) {
                 const int cc = b * G + c0;
                 const int jb = cc ? ce[cc - 1] : 0, je = ce[b * G + c1];
                 for (int j = jb; j < je; j++) support_visit(acc, ld_rec(rec + j), j, w1, w2, tg, a.cos_thresh, idx_);
+                acc.n_vis += unsigned(je - jb);
             }
         }
     }
@@ -1464,12 +1466,14 @@ __global__ void __launch_bounds__(VAL_THREADS, VAL_MIN_BLOCKS) k_validate(const 
                 const int cc = b * sG + sc0;
                 const int jb = cc ? ce[cc - 1] : 0, je = ce[b * sG + sc1];
                 for (int j = jb; j < je; j++) support_visit(ca, ld_rec(rec + j), j, sw1, sw2, stg, a.cos_thresh, idx_);
+                ca.n_vis += unsigned(je - jb);
             }
         } else {                                        // few long rows: the lanes stride over the entries
             for (int b = sr0; b <= sr1; b++) {
                 const int cc = b * sG + sc0;
                 const int jb = cc ? ce[cc - 1] : 0, je = ce[b * sG + sc1];
                 for (int j = jb + lane; j < je; j += 32) support_visit(ca, ld_rec(rec + j), j, sw1, sw2, stg, a.cos_thresh, idx_);
+                if (je - jb > lane) ca.n_vis += unsigned((je - jb - lane + 31) >> 5);
             }
         }
         int ci = ca.bj >= 0 ? idx_[ca.bj] : -2;         // edge index of the lane's best
