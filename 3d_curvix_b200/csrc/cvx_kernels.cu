@@ -1405,9 +1405,7 @@ __global__ void __launch_bounds__(VAL_THREADS, VAL_MIN_BLOCKS) k_validate(const 
         active = false;
     }
     // a query much heavier than its warp's mean is walked by the whole warp; the rest by their own lane
-    int wsum = work, wcnt = active ? 1 : 0;
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) { wsum += __shfl_xor_sync(FULL, wsum, o); wcnt += __shfl_xor_sync(FULL, wcnt, o); }
+    const int wsum = __reduce_add_sync(FULL, work), wcnt = __popc(__ballot_sync(FULL, active));   // REDUX: one instruction each
     const bool heavy = active && work > VAL_COOP_MIN && work * max(wcnt, 1) > VAL_COOP_RATIO * wsum;
     if (active && !heavy) {
         const GridLayout& L = useB ? a.gi.B : a.gi.A;
@@ -1477,13 +1475,15 @@ __global__ void __launch_bounds__(VAL_THREADS, VAL_MIN_BLOCKS) k_validate(const 
             }
         }
         int ci = ca.bj >= 0 ? idx_[ca.bj] : -2;         // edge index of the lane's best
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {              // maximum, ties to the lowest edge index
-            const double od = __shfl_xor_sync(FULL, ca.best, o);
-            const int oi = __shfl_xor_sync(FULL, ci, o);
-            ca.n_in += __shfl_xor_sync(FULL, ca.n_in, o); ca.n_vis += __shfl_xor_sync(FULL, ca.n_vis, o);
-            if (oi != -2 && (ci == -2 || od > ca.best || (od == ca.best && oi < ci))) { ca.best = od; ci = oi; }
+        {                                               // maximum, ties to the lowest edge index: |t . t^| > 0 orders as its bit
+            const unsigned long long kb = ci != -2 ? (unsigned long long)__double_as_longlong(ca.best) : 0ULL;   // pattern (REDUX x 3)
+            const unsigned hi = unsigned(kb >> 32), lo = unsigned(kb);
+            const unsigned mh = __reduce_max_sync(FULL, hi);
+            const unsigned ml = __reduce_max_sync(FULL, hi == mh ? lo : 0u);
+            const unsigned mi_ = __reduce_min_sync(FULL, (ci != -2 && hi == mh && lo == ml) ? unsigned(ci) : 0xffffffffu);
+            ci = mi_ == 0xffffffffu ? -2 : int(mi_);
         }
+        ca.n_in = __reduce_add_sync(FULL, ca.n_in); ca.n_vis = __reduce_add_sync(FULL, ca.n_vis);
         if (lane == src) { acc = ca; bidx = ci; c_hvy = 1; }
     }
     if (active && !heavy && acc.bj >= 0) bidx = ((useB ? a.gi.B.idx : a.gi.A.idx) + off)[acc.bj];
@@ -1493,13 +1493,13 @@ __global__ void __launch_bounds__(VAL_THREADS, VAL_MIN_BLOCKS) k_validate(const 
         a.support[int64_t(v) * a.sup_stride + u] = bidx;
     }
     if (a.ctr == nullptr) return;
-    // warp-aggregated statistics -> one counter slot per warp (no block barrier: warps retire independently)
+    // warp-aggregated statistics -> one counter slot per warp (no block barrier: warps retire independently).  Per-warp sums of
+    // everything but the weighted inlier count fit 32 bits (at most 32 lanes x edges of a view / rows of a group): one REDUX each.
+    c_sup = __reduce_add_sync(FULL, unsigned(c_sup)); c_par = __reduce_add_sync(FULL, unsigned(c_par));
+    c_deg = __reduce_add_sync(FULL, unsigned(c_deg)); c_vis = __reduce_add_sync(FULL, unsigned(c_vis));
+    c_hvy = __reduce_add_sync(FULL, unsigned(c_hvy));
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-        c_sup += __shfl_xor_sync(FULL, c_sup, o); c_par += __shfl_xor_sync(FULL, c_par, o);
-        c_inl += __shfl_xor_sync(FULL, c_inl, o); c_deg += __shfl_xor_sync(FULL, c_deg, o);
-        c_vis += __shfl_xor_sync(FULL, c_vis, o); c_hvy += __shfl_xor_sync(FULL, c_hvy, o);
-    }
+    for (int o = 16; o > 0; o >>= 1) c_inl += __shfl_xor_sync(FULL, c_inl, o);
     if (lane == 0) {
         const int slot = int((blockIdx.x * (VAL_THREADS / 32) + (threadIdx.x >> 5) + blockIdx.y) & (CVX_CTR_SLOTS - 1));
         if (c_sup) atomicAdd(&a.ctr->n_supported[slot], c_sup);
