@@ -189,11 +189,46 @@ CVX_HD bool ore_less(double t1, double t2) {   // ore(t) = atan(t) in [0,90) for
     const bool n1 = t1 < 0, n2 = t2 < 0;
     return (n1 == n2) ? (t1 < t2) : n2;
 }
+// reciprocal / reciprocal square root of the fast wedge (device: rcp.rn.f64 / rsqrt, a third of the instructions of a division)
+CVX_HD double cvx_rcp(double x) {
+#ifdef __CUDA_ARCH__
+    return __drcp_rn(x);
+#else
+    return 1.0 / x;
+#endif
+}
+CVX_HD double cvx_rsqrt(double x) {
+#ifdef __CUDA_ARCH__
+    return rsqrt(x);
+#else
+    return 1.0 / sqrt(x);
+#endif
+}
+// wedge_border_point with the two reciprocals shared by its four border crossings (1 ulp from the divisions of the reference)
+CVX_HD bool wedge_border_point_fast(double A, double B, double C, double iA, double iB, int rows, int cols, double e2x, double e2y, double* px,
+                                    double* py) {
+    const double fr = double(rows), fc = double(cols);
+    const double yl = (-C) * iB;               // x = 0          :153
+    const double yr = (-(C + A * fc)) * iB;    // x = cols       :154
+    const double xt = (-C) * iA;               // y = 0          :148
+    const double xb = (-(C + B * fr)) * iA;    // y = rows       :149
+    int hits = 0;
+    double sx0 = 0, sy0 = 0, sx1 = 0, sy1 = 0;
+    if (yl >= 0 && yl <= fr) { sx0 = 0.0; sy0 = yl; hits = 1; }
+    if (yr >= 0 && yr <= fr) { if (hits == 0) { sx0 = fc; sy0 = yr; } else { sx1 = fc; sy1 = yr; } hits++; }
+    if (xt >= 0 && xt <= fc) { if (hits == 0) { sx0 = xt; sy0 = 0.0; } else if (hits == 1) { sx1 = xt; sy1 = 0.0; } hits++; }
+    if (xb >= 0 && xb <= fc) { if (hits == 0) { sx0 = xb; sy0 = fr; } else if (hits == 1) { sx1 = xb; sy1 = fr; } hits++; }
+    if (hits != 2) return false;
+    const double ax = sx0 - e2x, ay = sy0 - e2y, bx = sx1 - e2x, by = sy1 - e2y;
+    const double d0 = ax * ax + ay * ay, d1 = bx * bx + by * by;
+    if (d0 < d1) { *px = sx0; *py = sy0; } else { *px = sx1; *py = sy1; }   // :237
+    return true;
+}
 CVX_HD void wedge_border_slopes_fast(double px, double py, double dlt, double e2x, double e2y, int cols, double* sp, double* sn) {
     if (px == 0 || px == double(cols)) {                          // :246 vertical border: shift in y
-        const double fdx = px - e2x;
-        *sp = (py - e2y - dlt) / fdx;
-        *sn = (py - e2y + dlt) / fdx;
+        const double ifdx = cvx_rcp(px - e2x);
+        *sp = (py - e2y - dlt) * ifdx;
+        *sn = (py - e2y + dlt) * ifdx;
     } else {                                                      // shift in x
         const double fdy = py - e2y;
         *sp = fdy / (px - e2x - dlt);
@@ -208,27 +243,29 @@ CVX_HD int wedge_row_fast(double x, double y, const double* F, double e1x, doubl
                           int cols, double* lo, double* hi) {
     const double dy = y - e1y, dx = x - e1x;                      // :54-55
     const double r2 = dy * dy + dx * dx;
-    const double d12 = sqrt(r2 - delta * delta);                  // :58-60 (NaN when the edge is inside the disc)
-    const double st = delta / d12, ct = sqrt((d12 - delta) * (d12 + delta)) / d12;   // sin / cos of asin(delta / d12) (NaN when delta > d12)
-    const double ir = 1.0 / sqrt(r2);
+    // With d12 = sqrt(r2 - delta^2) (:58-60), th = asin(delta / d12) (:62) and ang = atan(dy / dx) (:57), the tangent points are
+    // d12 (cos, sin)(ang +- th) (:66-76).  d12 sin th = delta and d12 cos th = sqrt(d12^2 - delta^2) = sqrt(r2 - 2 delta^2) =: S,
+    // so d12 itself drops out.  S is NaN exactly where the reference's sqrt / asin are (edge within sqrt(2) delta of the epipole).
+    const double S = sqrt(r2 - 2.0 * (delta * delta));
+    const double ir = cvx_rsqrt(r2);
     const double ca = fabs(dx) * ir;                              // cos / sin of atan(dy / dx)
     const double sa = ((dy < 0) != (dx < 0)) ? -(fabs(dy) * ir) : fabs(dy) * ir;
-    const double c1 = ca * ct - sa * st, s1 = sa * ct + ca * st;  // ang + th
-    const double c2 = ca * ct + sa * st, s2 = sa * ct - ca * st;  // ang - th
-    double dx1 = fabs(c1 * d12), dy1 = fabs(s1 * d12), dx2 = fabs(c2 * d12), dy2 = fabs(s2 * d12);
+    double dx1 = fabs(ca * S - sa * delta), dy1 = fabs(sa * S + ca * delta);   // ang + th
+    double dx2 = fabs(ca * S + sa * delta), dy2 = fabs(sa * S - ca * delta);   // ang - th
     if (dx < 0) { dx1 = -dx1; dx2 = -dx2; }                       // :87
     if (dy < 0) { dy1 = -dy1; dy2 = -dy2; }                       // :92
     const double p1x = dx1 + e1x, p1y = dy1 + e1y, p2x = dx2 + e1x, p2y = dy2 + e1y;   // :102-106
     const double A1 = (F[0] * p1x + F[1] * p1y) + F[2], B1 = (F[3] * p1x + F[4] * p1y) + F[5], C1 = (F[6] * p1x + F[7] * p1y) + F[8];  // :109
     const double A2 = (F[0] * p2x + F[1] * p2y) + F[2], B2 = (F[3] * p2x + F[4] * p2y) + F[5], C2 = (F[6] * p2x + F[7] * p2y) + F[8];  // :115
-    const double t1 = B1 / A1, t2 = B2 / A2;                      // slopes whose atan the reference orders (:121-139)
-    const double k1 = delta / sqrt(1.0 + t1 * t1), k2 = delta / sqrt(1.0 + t2 * t2);   // |cos(atan t)| * delta (:243)
+    const double iA1 = cvx_rcp(A1), iB1 = cvx_rcp(B1), iA2 = cvx_rcp(A2), iB2 = cvx_rcp(B2);
+    const double t1 = B1 * iA1, t2 = B2 * iA2;                    // slopes whose atan the reference orders (:121-139)
+    const double k1 = delta * cvx_rsqrt(1.0 + t1 * t1), k2 = delta * cvx_rsqrt(1.0 + t2 * t2);   // |cos(atan t)| * delta (:243)
     const bool first_lo = ore_less(t1, t2);
     const double dlt_lo = first_lo ? k1 : k2, dlt_hi = first_lo ? k2 : k1;
     double q1x, q1y, q2x, q2y;
     int flag = 0;
-    if (!wedge_border_point(A1, B1, C1, rows, cols, e2x, e2y, &q1x, &q1y)) flag |= 1;
-    if (!wedge_border_point(A2, B2, C2, rows, cols, e2x, e2y, &q2x, &q2y)) flag |= 2;
+    if (!wedge_border_point_fast(A1, B1, C1, iA1, iB1, rows, cols, e2x, e2y, &q1x, &q1y)) flag |= 1;
+    if (!wedge_border_point_fast(A2, B2, C2, iA2, iB2, rows, cols, e2x, e2y, &q2x, &q2y)) flag |= 2;
     const double qnan = nan("");
     if (flag) { *lo = qnan; *hi = qnan; return flag; }
     double m0, m1, m2, m3;                                        // the four slopes whose angles bound the wedge
