@@ -231,12 +231,12 @@ CVX_HD void wedge_border_slopes_fast(double px, double py, double dlt, double e2
         *sn = (py - e2y + dlt) * ifdx;
     } else {                                                      // shift in x
         const double fdy = py - e2y;
-        *sp = fdy / (px - e2x - dlt);
-        *sn = fdy / (px - e2x + dlt);
+        *sp = fdy * cvx_rcp(px - e2x - dlt);
+        *sn = fdy * cvx_rcp(px - e2x + dlt);
     }
 }
-CVX_HD double ore_of_slope(double t) {                            // :337-348: atan / M_PI * 180, + 180 if negative
-    const double a = cvx_atan(t) / M_PI * 180;
+CVX_HD double ore_of_slope(double t) {                            // :337-348: atan / M_PI * 180 (one multiplication here), + 180 if negative
+    const double a = cvx_atan(t) * (180.0 / M_PI);
     return a < 0 ? a + 180 : a;
 }
 CVX_HD int wedge_row_fast(double x, double y, const double* F, double e1x, double e1y, double e2x, double e2y, double delta, int rows,
