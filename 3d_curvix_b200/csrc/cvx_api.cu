@@ -445,6 +445,7 @@ int cvx_set_hypothesis_pair(cvx_ctx* ctx, int h1, int h2) {
     pc.cl_orient_rad = cfg.cluster_orient_thresh_deg * (M_PI / 180.0);                // util.hpp deg_to_rad
     pc.cl_wrap_deg = -90.0 + (cfg.cluster_orient_thresh_deg / 2.0);                   // EdgeClusterer.cpp:41
     pc.cl_sigma = cfg.cluster_gauss_sigma; pc.lowes_ratio = cfg.lowes_ratio;
+    { int ex = 0; pc.cl_sigma_inv = (pc.cl_sigma > 0 && std::frexp(pc.cl_sigma, &ex) == 0.5) ? 1.0 / pc.cl_sigma : 0.0; }
     pc.rows = cfg.img_rows; pc.cols = cfg.img_cols; pc.max_support = cfg.max_support_views; pc.max_cluster = cfg.max_cluster_size;
     ctx->vali_views.clear();
     for (int v = 0; v < ctx->n_views; v++) if (v != h1 && v != h2) ctx->vali_views.push_back(v);

@@ -530,18 +530,22 @@ struct ClusterSm {
 // per member first, the additions are the reference's left-to-right chain); sqrt / exp of the members are lane-parallel.
 __device__ __forceinline__ double shfl_d(double v, int src) { return __shfl_sync(FULL, v, src); }
 template <int N, bool ORIENT_ONLY>   // ORIENT_ONLY: the merge step needs the averaged orientation alone (EdgeClusterer.cpp:168-176)
-__device__ __noinline__ void gauss_avg_list(ClusterSm<N>& s, const int16_t* mem, int cnt, double sigma, int lane, double* gx, double* gy, double* gth) {
+__device__ __noinline__ void gauss_avg_list(ClusterSm<N>& s, const int16_t* mem, int cnt, double sigma, double sigma_inv, int lane, double* gx,
+                                            double* gy, double* gth) {
     double xi = 0, yi = 0, ti = 0;
     if (lane < cnt) { const int i = mem[lane]; xi = s.x[i]; yi = s.y[i]; ti = s.thn[i]; }
     double sx = 0, sy = 0;
     for (int k = 0; k < cnt; k++) { sx += shfl_d(xi, k); sy += shfl_d(yi, k); }
-    const double cx = sx / cnt, cy = sy / cnt;
+    // x / cnt: a power-of-two count (2 members is the most frequent merge) divides exactly by a multiplication (warp-uniform branch)
+    const bool p2 = (cnt & (cnt - 1)) == 0;
+    const double ic = __hiloint2double((1023 - (31 - __clz(cnt))) << 20, 0);   // 2^-floor(log2 cnt)
+    const double cx = p2 ? sx * ic : sx / cnt, cy = p2 ? sy * ic : sy / cnt;
     const double dx = xi - cx, dy = yi - cy;
     const double di = sqrt(dx * dx + dy * dy);
     double tot = 0.0;
     for (int k = 0; k < cnt; k++) tot += shfl_d(di, k);
-    const double mean_shift = tot / cnt;
-    const double q = (di - mean_shift) / sigma;
+    const double mean_shift = p2 ? tot * ic : tot / cnt;
+    const double q = sigma_inv != 0.0 ? (di - mean_shift) * sigma_inv : (di - mean_shift) / sigma;   // exact when sigma is a power of two
     const double w = exp(-0.5 * (q * q));
     const double wo = w * ti;
     double swo = 0, tw = 0;
@@ -648,7 +652,7 @@ __device__ void cluster_warp_sm(int n, const PassConst& pc, ClusterSm<N>& s, con
         const int old_l = s.label[mj], new_l = s.label[mi];
         const int cnt = member_list(s, s.mem, n, old_l, new_l, lane, lt);
         double gx, gy, gth;
-        gauss_avg_list<N, true>(s, s.mem, cnt, pc.cl_sigma, lane, &gx, &gy, &gth);       // :168
+        gauss_avg_list<N, true>(s, s.mem, cnt, pc.cl_sigma, pc.cl_sigma_inv, lane, &gx, &gy, &gth);       // :168
         if (lane == 0) { s.orient[new_l] = normalize_orientation(gth, pc.cl_wrap_deg); s.size[new_l] = int16_t(cnt); }   // :175-176
         for (int k = lane; k < n; k += 32) if (s.label[k] == old_l) s.label[k] = int16_t(new_l);   // :179-183
         for (int w = lane; w < nw; w += 32) {                            // members + everything adjacent to a member
@@ -681,7 +685,7 @@ __device__ void cluster_warp_sm(int n, const PassConst& pc, ClusterSm<N>& s, con
             roots &= roots - 1;
             const int cnt = member_list(s, s.mem, n, i, i, lane, lt);
             double gx, gy, gth;
-            gauss_avg_list<N, false>(s, s.mem, cnt, pc.cl_sigma, lane, &gx, &gy, &gth);
+            gauss_avg_list<N, false>(s, s.mem, cnt, pc.cl_sigma, pc.cl_sigma_inv, lane, &gx, &gy, &gth);
             double d = DBL_MAX;
             int pos = lane;
             if (lane < cnt) {
@@ -792,7 +796,7 @@ __device__ void cluster_block_sm(int n, const PassConst& pc, ClusterSmB<N>& sb, 
             const int cnt = min(32, __shfl_sync(FULL, incl, 31));
             __syncwarp();
             double gx, gy, gth;
-            gauss_avg_list<N, true>(s, s.mem, cnt, pc.cl_sigma, lane, &gx, &gy, &gth);
+            gauss_avg_list<N, true>(s, s.mem, cnt, pc.cl_sigma, pc.cl_sigma_inv, lane, &gx, &gy, &gth);
             if (lane == 0) { s.orient[new_l] = normalize_orientation(gth, pc.cl_wrap_deg); s.size[new_l] = int16_t(cnt); }
         } else if (gw == 1) {                                             // dirty set: the members and every row adjacent to one
             uint32_t d = lane < nw ? sb.wmask[lane] : 0u;
@@ -841,7 +845,7 @@ __device__ void cluster_block_sm(int n, const PassConst& pc, ClusterSmB<N>& sb, 
             roots &= roots - 1;
             const int cnt = member_list(s, mem, n, i, i, lane, lt);
             double gx, gy, gth;
-            gauss_avg_list<N, false>(s, mem, cnt, pc.cl_sigma, lane, &gx, &gy, &gth);
+            gauss_avg_list<N, false>(s, mem, cnt, pc.cl_sigma, pc.cl_sigma_inv, lane, &gx, &gy, &gth);
             double d = DBL_MAX;
             int pos = lane;
             if (lane < cnt) {

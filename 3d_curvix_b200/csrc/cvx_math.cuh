@@ -37,6 +37,7 @@ struct PassConst {
     double delta, cos_thresh, parallel_deg;
     double loc_pert, tang_thresh, orient_pert;
     double cl_dist, cl_orient_rad, cl_wrap_deg, cl_sigma;
+    double cl_sigma_inv;   // 1 / cl_sigma when cl_sigma is a power of two (x / sigma == x * inv exactly), else 0
     double cl_dist_sq;   // smallest double s with sqrt(s) >= cl_dist: "sqrt(s) < cl_dist" == "s < cl_dist_sq" exactly (sqrt is monotone)
     double lowes_ratio;
     int32_t rows, cols, max_support, max_cluster, n_vali, pad;
