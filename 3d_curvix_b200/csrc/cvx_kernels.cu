@@ -582,7 +582,7 @@ __device__ __forceinline__ bool merge_candidate(ClusterSm<N>& s, int i, int nw, 
     constexpr int NW = N / 32;
     const int li = s.label[i];
     const double oi = s.orient[li], xi = s.x[i], yi = s.y[i];
-    double bd = DBL_MAX;
+    double bd = DBL_MAX, bs = DBL_MAX;                     // best distance and its square
     int bj = -1;
     for (int ww = 0; ww < nw; ww++) {
         uint32_t bits = s.adj[i * NW + ww];
@@ -593,8 +593,11 @@ __device__ __forceinline__ bool merge_candidate(ClusterSm<N>& s, int i, int nw, 
             const int lj = s.label[j];
             if (lj != li && fabs(oi - s.orient[lj]) < pc.cl_orient_rad) {          // :147-154
                 const double ddx = xi - s.x[j], ddy = yi - s.y[j];
-                const double d = sqrt(ddx * ddx + ddy * ddy);
-                if (d < bd) { bd = d; bj = j; }                                     // first minimum (j ascending)
+                const double sq = ddx * ddx + ddy * ddy;
+                if (sq < bs) {                                                      // sqrt is monotone: sq >= bs cannot give d < bd
+                    const double d = sqrt(sq);
+                    if (d < bd) { bd = d; bs = sq; bj = j; }                        // first minimum (j ascending)
+                }
             }
         }
     }
