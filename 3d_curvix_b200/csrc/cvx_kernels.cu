@@ -1306,15 +1306,22 @@ void launch_wedge31(const PassConst& pc, const ViewConst* vc, const double* x1, 
 //   index order == maximum, ties to the lowest index).  Threads of a warp are consecutive hypotheses of (mostly) one view-1
 //   edge and one view: they share wedge31 and hit neighbouring cells.  Queries that overlap many cells or long cells (wedges
 //   that wrap around 0/180 degrees, epipole inside the image: SURVEY.md a3) are walked by the whole warp instead of one lane.
+// Launch shape per variant (profiles/r01l_validate_variants.txt): the fused kernel (FP64 wedge + walk, issue bound) likes 256-thread blocks
+// and three independent record loads per walk step; the stand-alone support test (walk only, L1-lookup bound) 128-thread blocks and two.
+// 64 registers either way: occupancy beats a deeper batch (profiles/r01f_variants.txt).
 #ifndef VAL_THREADS
 #define VAL_THREADS 256
 #endif
+#ifndef VAL_THREADS_GIVEN
+#define VAL_THREADS_GIVEN 128
+#endif
 #ifndef VAL_BATCH
-#define VAL_BATCH 2           // entries a lane loads per step of its walk (independent loads in flight)
+#define VAL_BATCH 3           // entries a lane loads per step of its walk (independent loads in flight)
 #endif
-#ifndef VAL_MIN_BLOCKS
-#define VAL_MIN_BLOCKS 4      // 64 registers: the kernel is latency bound, occupancy beats a deeper batch (profiles/r01f_variants.txt)
+#ifndef VAL_BATCH_GIVEN
+#define VAL_BATCH_GIVEN 2
 #endif
+#define VAL_REGS_THREADS 1024  // resident threads per SM at 64 registers
 #define VAL_LIGHT_ROWS 4       // row ranges a lane keeps in registers
 #define VAL_COOP_MIN 32        // a query becomes a whole-warp job when its work exceeds this and VAL_COOP_RATIO x the warp's mean
 #define VAL_COOP_RATIO 2
@@ -1343,8 +1350,10 @@ __device__ __forceinline__ void support_visit(SupportAcc& s, const double4 e, in
 }
 // GIVEN: wedge32 / tangent are inputs (stand-alone support test on pre-formed hypotheses).
 template <bool GIVEN, bool STRICT>
-__global__ void __launch_bounds__(VAL_THREADS, VAL_MIN_BLOCKS) k_validate(const __grid_constant__ PassConst pc, const __grid_constant__ ValidateArgs a) {
-    const int64_t u = blockIdx.x * int64_t(VAL_THREADS) + threadIdx.x;
+__global__ void __launch_bounds__(GIVEN ? VAL_THREADS_GIVEN : VAL_THREADS, VAL_REGS_THREADS / (GIVEN ? VAL_THREADS_GIVEN : VAL_THREADS))
+    k_validate(const __grid_constant__ PassConst pc, const __grid_constant__ ValidateArgs a) {
+    constexpr int THREADS = GIVEN ? VAL_THREADS_GIVEN : VAL_THREADS, BATCH = GIVEN ? VAL_BATCH_GIVEN : VAL_BATCH;
+    const int64_t u = blockIdx.x * int64_t(THREADS) + threadIdx.x;
     const int v = blockIdx.y;
     const int lane = threadIdx.x & 31;
     unsigned long long c_sup = 0, c_par = 0, c_inl = 0, c_deg = 0, c_vis = 0, c_hvy = 0, mult = 0;
@@ -1419,22 +1428,22 @@ __global__ void __launch_bounds__(VAL_THREADS, VAL_MIN_BLOCKS) k_validate(const 
         const double4* __restrict__ rec = L.rec + off;
         const int32_t* __restrict__ idx_ = L.idx + off;
         if (r1 - r0 < VAL_LIGHT_ROWS) {
-            // the (at most VAL_LIGHT_ROWS) ranges are walked as one flattened list, VAL_BATCH entries per step, so that several
+            // the (at most VAL_LIGHT_ROWS) ranges are walked as one flattened list, BATCH entries per step, so that several
             // independent 32-byte loads are in flight per lane instead of one (the walk is latency bound)
             const int l0 = end[0] - beg[0], l1 = l0 + (end[1] - beg[1]), l2 = l1 + (end[2] - beg[2]);
             const int g0 = beg[1] - end[0], g1 = beg[2] - end[1], g2 = beg[3] - end[2];   // jumps between consecutive ranges
-            for (int k = 0; k < work; k += VAL_BATCH) {
-                int j[VAL_BATCH];
-                double4 e[VAL_BATCH];
+            for (int k = 0; k < work; k += BATCH) {
+                int j[BATCH];
+                double4 e[BATCH];
 #pragma unroll
-                for (int t = 0; t < VAL_BATCH; t++) {
+                for (int t = 0; t < BATCH; t++) {
                     const int kk = min(k + t, work - 1);
                     j[t] = beg[0] + kk + (kk >= l0 ? g0 : 0) + (kk >= l1 ? g1 : 0) + (kk >= l2 ? g2 : 0);
                 }
 #pragma unroll
-                for (int t = 0; t < VAL_BATCH; t++) e[t] = ld_rec(rec + j[t]);
+                for (int t = 0; t < BATCH; t++) e[t] = ld_rec(rec + j[t]);
 #pragma unroll
-                for (int t = 0; t < VAL_BATCH; t++)
+                for (int t = 0; t < BATCH; t++)
                     if (t == 0 || k + t < work) support_visit(acc, e[t], j[t], w1, w2, tg, a.cos_thresh, idx_);
             }
             acc.n_vis = unsigned(work);                 // entries visited (statistics)
@@ -1508,7 +1517,7 @@ __global__ void __launch_bounds__(VAL_THREADS, VAL_MIN_BLOCKS) k_validate(const 
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) c_inl += __shfl_xor_sync(FULL, c_inl, o);
     if (lane == 0) {
-        const int slot = int((blockIdx.x * (VAL_THREADS / 32) + (threadIdx.x >> 5) + blockIdx.y) & (CVX_CTR_SLOTS - 1));
+        const int slot = int((blockIdx.x * (THREADS / 32) + (threadIdx.x >> 5) + blockIdx.y) & (CVX_CTR_SLOTS - 1));
         if (c_sup) atomicAdd(&a.ctr->n_supported[slot], c_sup);
         if (c_par) atomicAdd(&a.ctr->n_parallel[slot], c_par);
         if (c_inl) atomicAdd(&a.ctr->n_inliers[slot], c_inl);
@@ -1519,10 +1528,11 @@ __global__ void __launch_bounds__(VAL_THREADS, VAL_MIN_BLOCKS) k_validate(const 
 }
 void launch_validate(const PassConst& pc, const ValidateArgs& a, bool given, cudaStream_t st) {
     if (a.U <= 0 || a.n_vali <= 0) return;
-    dim3 grid(unsigned((a.U + VAL_THREADS - 1) / VAL_THREADS), a.n_vali);
-    if (given) k_validate<true, false><<<grid, VAL_THREADS, 0, st>>>(pc, a);
-    else if (a.strict) k_validate<false, true><<<grid, VAL_THREADS, 0, st>>>(pc, a);
-    else k_validate<false, false><<<grid, VAL_THREADS, 0, st>>>(pc, a);
+    const int threads = given ? VAL_THREADS_GIVEN : VAL_THREADS;
+    dim3 grid(unsigned((a.U + threads - 1) / threads), a.n_vali);
+    if (given) k_validate<true, false><<<grid, threads, 0, st>>>(pc, a);
+    else if (a.strict) k_validate<false, true><<<grid, threads, 0, st>>>(pc, a);
+    else k_validate<false, false><<<grid, threads, 0, st>>>(pc, a);
 }
 
 // ----------------------------------------------------------------------------- vote + ratio test
