@@ -1432,18 +1432,32 @@ __global__ void __launch_bounds__(GIVEN ? VAL_THREADS_GIVEN : VAL_THREADS, VAL_R
             // independent 32-byte loads are in flight per lane instead of one (the walk is latency bound)
             const int l0 = end[0] - beg[0], l1 = l0 + (end[1] - beg[1]), l2 = l1 + (end[2] - beg[2]);
             const int g0 = beg[1] - end[0], g1 = beg[2] - end[1], g2 = beg[3] - end[2];   // jumps between consecutive ranges
-            for (int k = 0; k < work; k += BATCH) {
+            int k = 0;
+            for (; k + BATCH <= work; k += BATCH) {     // full steps: no clamping, no tail predicate
                 int j[BATCH];
                 double4 e[BATCH];
 #pragma unroll
                 for (int t = 0; t < BATCH; t++) {
-                    const int kk = min(k + t, work - 1);
+                    const int kk = k + t;
                     j[t] = beg[0] + kk + (kk >= l0 ? g0 : 0) + (kk >= l1 ? g1 : 0) + (kk >= l2 ? g2 : 0);
                 }
 #pragma unroll
                 for (int t = 0; t < BATCH; t++) e[t] = ld_rec(rec + j[t]);
 #pragma unroll
-                for (int t = 0; t < BATCH; t++)
+                for (int t = 0; t < BATCH; t++) support_visit(acc, e[t], j[t], w1, w2, tg, a.cos_thresh, idx_);
+            }
+            if (k < work) {                             // the last, partial step (indices clamped to the last entry)
+                int j[BATCH - 1];
+                double4 e[BATCH - 1];
+#pragma unroll
+                for (int t = 0; t < BATCH - 1; t++) {
+                    const int kk = min(k + t, work - 1);
+                    j[t] = beg[0] + kk + (kk >= l0 ? g0 : 0) + (kk >= l1 ? g1 : 0) + (kk >= l2 ? g2 : 0);
+                }
+#pragma unroll
+                for (int t = 0; t < BATCH - 1; t++) e[t] = ld_rec(rec + j[t]);
+#pragma unroll
+                for (int t = 0; t < BATCH - 1; t++)
                     if (t == 0 || k + t < work) support_visit(acc, e[t], j[t], w1, w2, tg, a.cos_thresh, idx_);
             }
             acc.n_vis = unsigned(work);                 // entries visited (statistics)
