@@ -1323,8 +1323,12 @@ void launch_wedge31(const PassConst& pc, const ViewConst* vc, const double* x1, 
 #endif
 #define VAL_REGS_THREADS 1024  // resident threads per SM at 64 registers
 #define VAL_LIGHT_ROWS 4       // row ranges a lane keeps in registers
+#ifndef VAL_COOP_MIN
 #define VAL_COOP_MIN 32        // a query becomes a whole-warp job when its work exceeds this and VAL_COOP_RATIO x the warp's mean
+#endif
+#ifndef VAL_COOP_RATIO
 #define VAL_COOP_RATIO 2
+#endif
 struct SupportAcc {
     double best;   // prev_prod, getSupportedEdgels.cpp:33
     int bj;        // position (in the walked layout) of the best entry so far, -1 = none
