@@ -3,7 +3,7 @@
 //
 // CPU restatement of the 3D Curvix edge-sketch hot path.  Every function cites the reference
 // file:line it follows (paths relative to the reference root, Edge_Reconst/ unless noted).
-// Parity status: unpinned by reference goldens (the reference ships none for this path).
+// Parity status: pinned against oracle/_ref (the reference's own sources), see curvix_oracle.hpp.
 // =====================================================================================
 #include "curvix_oracle.hpp"
 

@@ -5,11 +5,12 @@
 // path of C-H-Chien/3D_Curvix.  Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline /
 // --impl reference legs may load this library.  The product (3d_curvix_b200/) never links it.
 //
-// PARITY STATUS: "parity unpinned by reference goldens".  The reference ships no golden vectors or
-// known-answer tests for this path and cannot be compiled here (needs Eigen 3.3.2 and
-// yaml-cpp, both absent).  The oracle is pinned only by (a) an independent numpy restatement of
-// the angle / wedge / support functions (tests/test_oracle_numpy_crosscheck.py) and (b) the
-// reference's fixed numeric case test/test_functions.cpp:117-145 used as a self-consistency KAT.
+// PARITY STATUS: pinned against the reference itself.  The reference's unmodified sources compile against the stand-in
+// Eigen / yaml-cpp headers of oracle/ref_shim into oracle/_ref/libcurvix_ref.so; tests/test_oracle_vs_ref.py shows this port
+// equal to it bit for bit (getOreList, getOreListBar on 2-hit rows, getHYPO2_idx_Ore, epipolar correction, clustering,
+// reprojected tangents, wedges, getSupportIdx, 3-D tangents; whole passes: accepted pairs, support matrices, cluster map) and
+// to 1e-6 for linearTriangulation; tests/golden/ref_abc_*.npz are reference-generated vectors (tests/test_oracle_golden.py).
+// What stays a restatement: Eigen's reduction order inside 3x3 products (oracle/ref_shim/README.md, test_sum_order_sensitivity).
 //
 // Operation order mimics a non-fast-math build: 3-term dot products are summed left to right,
 // Matrix3d::inverse() is cofactor * (1/det), transcendental functions are scalar glibc calls.

@@ -6,7 +6,45 @@ import numpy as np
 
 from conftest import ROOT, make_oracle
 
+import pytest
+
 GOLD = os.path.join(ROOT, "tests", "golden", "oracle_abc_47_42.npz")
+
+
+@pytest.mark.parametrize("pair", [(47, 42), (28, 48)])
+def test_port_matches_reference_goldens(oracle_mod, abc_scene, pair):
+    """tests/golden/ref_abc_*.npz are outputs of the REFERENCE ITSELF (its unmodified sources compiled against oracle/ref_shim,
+    written by tests/golden/make_ref_goldens.py): accepted pairs, the support index of every accepted pair in every validation view,
+    the full all_supported_indices matrix of every processed view-1 edge, the hypo2_clusters map, 3-D points and tangents.
+    The port oracle must reproduce them: indices bit-exact, tangents bit-exact, points to 1e-6 (north_star)."""
+    g = np.load(os.path.join(ROOT, "tests", "golden", f"ref_abc_{pair[0]}_{pair[1]}.npz"))
+    o = make_oracle(oracle_mod, abc_scene)
+    o.set_pair(*pair)
+    o.run(mode=1)
+    p, f, t, S = o.pairs(), o.finalize(), o.h1_table(), o.support_matrix()
+    assert np.array_equal(p["h1"], g["pair_h1"]) and np.array_equal(p["h2rep"], g["pair_h2rep"])
+    assert np.array_equal(p["supports"], g["pair_supports"])
+    ok = f["nan_flag"] == 0
+    assert ok.all()
+    assert np.array_equal(f["tangent_world"], g["tangent_world"])
+    for k in ("gamma_cam", "gamma_world"):
+        rel = np.abs(f[k] - g[k]).max(1) / np.maximum(np.linalg.norm(g[k], axis=1), 1e-3)
+        assert rel.max() <= 1e-6, (k, rel.max())
+    # all_supported_indices: m rows per processed view-1 edge, rows >= n never written by the reference (-32768 in the golden)
+    proc = np.nonzero(t["n"] > 0)[0]
+    assert len(proc) == len(g["block_rows"]) and np.array_equal(t["m"][proc], g["block_rows"])
+    off = np.concatenate([[0], np.cumsum(g["block_rows"])])
+    sb = g["support_blocks"]
+    for i, h in enumerate(proc):
+        n, s = int(t["n"][h]), int(t["off"][h])
+        assert np.array_equal(sb[off[i]:off[i] + n], S[s:s + n]), f"support matrix of view-1 edge {h}"
+        assert (sb[off[i] + n:off[i + 1]] == -32768).all()
+    # hypo2_clusters: the lookup Finalize makes for every accepted pair (EdgeSketch_Core.hpp:193-202)
+    keys = {(int(a), int(b)): i for i, (a, b) in enumerate(zip(g["cluster_key_h1"], g["cluster_key_h2"]))}
+    for i in range(0, len(p["h1"]), 7):
+        k = keys.get((int(p["h1"][i]), int(p["h2rep"][i])))
+        want = g["cluster_members"][g["cluster_off"][k]:g["cluster_off"][k + 1]] if k is not None else np.array([p["h2rep"][i]])
+        assert np.array_equal(want, o.pair_cluster(i))
 
 
 def test_abc_pass_matches_committed_goldens(oracle_mod, abc_scene):
