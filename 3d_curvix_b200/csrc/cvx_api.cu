@@ -156,7 +156,7 @@ struct cvx_ctx {
     uint32_t* d_claim = nullptr;
     size_t claim_words = 0;
     DevBuf<unsigned long long> d_claim_cnt;
-    DevBuf<uint8_t> d_claim_mask;
+    DevBuf<uint8_t> d_claim_mask, d_keep;
     cvx_counts counts;
     cvx_timings tm;
     cudaEvent_t ev[10];                         // run: 0,1,3,4,5; finalize: 6,7; set_pair: 8,9
@@ -275,6 +275,9 @@ void cvx_default_config(cvx_config* c) {
 int cvx_create(const cvx_config* cfg, int device, cvx_ctx** out) {
     if (!cfg || !out || cfg->n_views < 3) return CVX_ERR_INVALID;
     *out = nullptr;
+    // With lowes_ratio >= 1 no row passes count > ratio * max and the reference falls back to the first element of its (unstable)
+    // std::sort (EdgeSketch_Core.cpp:505-507); that order is not reproduced on the device, so the range is rejected.
+    if (!(cfg->lowes_ratio >= 0.0 && cfg->lowes_ratio < 1.0) || cfg->max_support_views < 1) return CVX_ERR_INVALID;
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return CVX_ERR_NO_DEVICE;   // no CPU fallback by design
     if (device < 0 || device >= ndev) return CVX_ERR_INVALID;
@@ -589,7 +592,7 @@ int cvx_run_edge_sketch(cvx_ctx* ctx, int h1_begin, int h1_end) {
     cudaEventRecord(ctx->ev[5], st);
     // ---- vote + ratio test
     launch_count_u(ctx->d_support.p, int64_t(Ua), U, V, ctx->u_count.p, st);
-    launch_select(pc, ctx->d_row_off.p, h1_begin, h1_end, ctx->u_count.p, rt, ctx->d_nvalid.p, ctx->d_nsel.p, st);
+    launch_select(pc, ctx->d_row_off.p, h1_begin, h1_end, ctx->u_count.p, rt, ctx->d_nvalid.p, ctx->d_nsel.p, ctx->d_big_list.p + E1a + 6, st);   // cnts[6] = max selected rows of an edge
     launch_scan_i32_i64(ctx->d_nvalid.p, ctx->d_valid_off.p, E1, st);
     launch_scan_i32_i64(ctx->d_nsel.p, ctx->d_pair_off.p, E1, st);
     ctx->tm.kernel_launches += 4;
@@ -758,13 +761,14 @@ int cvx_get_pairs(cvx_ctx* ctx, int32_t* h1, int32_t* h2rep, int32_t* row, int32
     return CVX_OK;
 }
 
-int cvx_get_reference_order(cvx_ctx* ctx, int64_t* idx, int64_t* n_out) {
-    if (!ctx || !ctx->have_run || !idx || !n_out) return fail(ctx, CVX_ERR_INVALID, "cvx_get_reference_order: bad arguments");
-    CU(cudaSetDevice(ctx->device));
+// EdgeSketch_Core.cpp:480-526 on the host: per view-1 edge std::sort of the valid rows by count, ratio-test filter, n_views-row capacity
+static int reference_order(cvx_ctx* ctx, std::vector<int64_t>& idx) {
     const int64_t nv = ctx->n_valid;
     std::vector<int32_t> h1(nv), cnt(nv), sel(nv);
     D2H(h1.data(), ctx->v_h1.p, nv, int32_t); D2H(cnt.data(), ctx->v_count.p, nv, int32_t); D2H(sel.data(), ctx->v_sel.p, nv, int32_t);
-    int64_t out = 0, pair_base = 0;
+    idx.clear();
+    idx.reserve(size_t(ctx->P));
+    int64_t pair_base = 0;
     for (int64_t i = 0; i < nv;) {
         int64_t j = i;
         while (j < nv && h1[j] == h1[i]) j++;
@@ -776,11 +780,20 @@ int cvx_get_reference_order(cvx_ctx* ctx, int64_t* idx, int64_t* n_out) {
         std::sort(vp.begin(), vp.end(), [](const std::pair<int, int>& a, const std::pair<int, int>& b) { return a.second > b.second; });   // :488-491
         int taken = 0;
         for (const auto& pr : vp)
-            if (pair_of[pr.first] >= 0 && taken < ctx->cfg.n_views) { idx[out++] = pair_of[pr.first]; taken++; }   // :500-526
+            if (pair_of[pr.first] >= 0 && taken < ctx->cfg.n_views) { idx.push_back(pair_of[pr.first]); taken++; }   // :500-526
         pair_base = q;
         i = j;
     }
-    *n_out = out;
+    return CVX_OK;
+}
+int cvx_get_reference_order(cvx_ctx* ctx, int64_t* idx, int64_t* n_out) {
+    if (!ctx || !ctx->have_run || !idx || !n_out) return fail(ctx, CVX_ERR_INVALID, "cvx_get_reference_order: bad arguments");
+    CU(cudaSetDevice(ctx->device));
+    std::vector<int64_t> order;
+    const int rc = reference_order(ctx, order);
+    if (rc) return rc;
+    std::copy(order.begin(), order.end(), idx);
+    *n_out = int64_t(order.size());
     return CVX_OK;
 }
 
@@ -851,7 +864,20 @@ int cvx_claims_accumulate(cvx_ctx* ctx) {
     a.p_h1 = ctx->p_h1.p; a.p_h2rep = ctx->p_h2rep.p; a.p_sup = ctx->p_sup.p; a.nan_flag = ctx->f_nan.p; a.P = ctx->P;
     a.row_off = ctx->d_row_off.p; a.rawat = ctx->r_rawat.p; a.label = ctx->r_label.p;
     a.vali_view = ctx->d_vali.p; a.edge_off = ctx->d_edge_off.p; a.n_vali = ctx->n_vali; a.view1 = ctx->h1; a.view2 = ctx->h2;
-    a.E2 = ctx->edge_n[ctx->h2]; a.bits = ctx->d_claim;
+    a.E2 = ctx->edge_n[ctx->h2]; a.bits = ctx->d_claim; a.keep = nullptr;
+    if (ctx->pin->cnts[6] > ctx->cfg.n_views && ctx->P > 0) {
+        // Some view-1 edge selected more rows than paired_edge holds for it (n_views, EdgeSketch_Core.cpp:513-526): only the rows the
+        // reference keeps -- in its std::sort order -- reach the EdgeMapping insertions (:682-726).  Rare (never on ABC-NEF).
+        std::vector<int64_t> order;
+        const int rc2 = reference_order(ctx, order);
+        if (rc2) return rc2;
+        std::vector<uint8_t> keep(size_t(ctx->P), 0);
+        for (int64_t i : order) keep[size_t(i)] = 1;
+        CU(ctx->d_keep.reserve(size_t(ctx->P)));
+        CU(cudaMemcpyAsync(ctx->d_keep.p, keep.data(), size_t(ctx->P), cudaMemcpyHostToDevice, ctx->stream));
+        CU(cudaStreamSynchronize(ctx->stream));   // keep[] is a local
+        a.keep = ctx->d_keep.p;
+    }
     launch_claim_pairs(a, ctx->stream);
     ctx->tm.kernel_launches++;
     CU(cudaGetLastError());

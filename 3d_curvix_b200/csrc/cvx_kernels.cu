@@ -1568,7 +1568,8 @@ void launch_count_u(const int32_t* support, int64_t sup_stride, int64_t U, int n
 }
 // EdgeSketch_Core.cpp:430-508.  One warp per view-1 edge.  flags bit0 = valid (count >= N), bit1 = passes count > ratio * max.
 __global__ void __launch_bounds__(128) k_select(const __grid_constant__ PassConst pc, const int64_t* __restrict__ row_off, int h1_begin, int h1_end,
-                                                const int32_t* __restrict__ count_u, RowTable rt, int32_t* n_valid, int32_t* n_sel) {
+                                                const int32_t* __restrict__ count_u, RowTable rt, int32_t* n_valid, int32_t* n_sel,
+                                                int32_t* max_sel) {
     const int lane = threadIdx.x & 31;
     const int h1 = h1_begin + blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (h1 >= h1_end) return;
@@ -1591,13 +1592,18 @@ __global__ void __launch_bounds__(128) k_select(const __grid_constant__ PassCons
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) ns += __shfl_xor_sync(FULL, ns, o);
-    if (lane == 0) { n_valid[h1] = nv; n_sel[h1] = ns; }
+    if (lane == 0) {
+        n_valid[h1] = nv; n_sel[h1] = ns;
+        // the reference keeps at most n_views rows per view-1 edge (paired_edge capacity, EdgeSketch_Core.cpp:513-526): the host
+        // applies that cut only when some edge exceeds it
+        if (ns > *max_sel) atomicMax(max_sel, ns);
+    }
 }
 void launch_select(const PassConst& pc, const int64_t* row_off, int h1_begin, int h1_end, const int32_t* count_u, RowTable rt,
-                   int32_t* n_valid, int32_t* n_sel, cudaStream_t st) {
+                   int32_t* n_valid, int32_t* n_sel, int32_t* max_sel, cudaStream_t st) {
     const int n = h1_end - h1_begin;
     if (n <= 0) return;
-    k_select<<<(n + 3) / 4, 128, 0, st>>>(pc, row_off, h1_begin, h1_end, count_u, rt, n_valid, n_sel);
+    k_select<<<(n + 3) / 4, 128, 0, st>>>(pc, row_off, h1_begin, h1_end, count_u, rt, n_valid, n_sel, max_sel);
 }
 __global__ void __launch_bounds__(128) k_select_fill(const int64_t* __restrict__ row_off, int h1_begin, int h1_end, RowTable rt,
                                                      const int64_t* __restrict__ valid_off, const int64_t* __restrict__ pair_off, int32_t* v_h1,
@@ -1720,6 +1726,7 @@ __global__ void __launch_bounds__(128) k_claim_pairs(const __grid_constant__ Cla
     const int lane = threadIdx.x & 31;
     const int64_t p = blockIdx.x * int64_t(blockDim.x >> 5) + (threadIdx.x >> 5);
     if (p >= a.P) return;
+    if (a.keep && !a.keep[p]) return;                     // beyond the n_views rows paired_edge holds per view-1 edge (:513-526)
     if (a.nan_flag[p] != 0) return;                       // `continue` before the insertions (:639-642, :658-663)
     const int h1 = a.p_h1[p], h2 = a.p_h2rep[p];
     const int64_t off1 = a.edge_off[a.view1], off2 = a.edge_off[a.view2];

@@ -141,7 +141,7 @@ void launch_validate(const PassConst& pc, const ValidateArgs& a, bool given, cud
 // vote (per unique hypothesis), ratio test (per view-1 edge), compaction
 void launch_count_u(const int32_t* support, int64_t sup_stride, int64_t U, int n_vali, int32_t* count_u, cudaStream_t st);
 void launch_select(const PassConst& pc, const int64_t* row_off, int h1_begin, int h1_end, const int32_t* count_u, RowTable rt,
-                   int32_t* n_valid, int32_t* n_sel, cudaStream_t st);
+                   int32_t* n_valid, int32_t* n_sel, int32_t* max_sel, cudaStream_t st);
 void launch_select_fill(const int64_t* row_off, int h1_begin, int h1_end, RowTable rt, const int64_t* valid_off, const int64_t* pair_off,
                         int32_t* v_h1, int32_t* v_row, int32_t* v_count, int32_t* v_sel, int32_t* p_h1, int32_t* p_h2rep, int32_t* p_row,
                         int32_t* p_count, cudaStream_t st);
@@ -163,6 +163,7 @@ struct ClaimArgs {
     const int64_t* row_off; const int32_t *rawat, *label;   // hypothesis table (cluster lookup through the reference's key quirk)
     const int32_t* vali_view; const int64_t* edge_off; int n_vali, view1, view2, E2;
     uint32_t* bits;
+    const uint8_t* keep;    // NULL, or 1 for the accepted rows the reference's paired_edge capacity keeps (cvx_get_reference_order)
 };
 void launch_claim_pairs(const ClaimArgs& a, cudaStream_t st);
 void launch_claim_count(const uint32_t* bits, const int64_t* edge_off, const int32_t* edge_n, int n_views, unsigned long long* out, cudaStream_t st);

@@ -36,7 +36,8 @@ typedef struct cvx_config {
     double delta;                      /* YAML delta: edge location perturbation      EdgeSketch_Core.cpp:40 */
     double delta_theta_deg;            /* YAML delta_theta                            EdgeSketch_Core.cpp:41 */
     double parallel_angle_deg;         /* YAML Parallel_Epipolar_Line_Angle           EdgeSketch_Core.cpp:44 */
-    double lowes_ratio;                /* LOWES_RATIO_THRESHOLD (0.6)                 definitions.h:14 */
+    double lowes_ratio;                /* LOWES_RATIO_THRESHOLD (0.6), must be in [0,1) definitions.h:14 (>= 1 would need the
+                                        * reference's unstable-sort fallback, EdgeSketch_Core.cpp:505-507: cvx_create rejects it) */
     double epip_tangency_displ_thresh; /* EPIP_TANGENCY_DISPL_THRESH (3)              definitions.h:20 */
     double location_perturbation;      /* LOCATION_PERTURBATION (0.4)                 definitions.h:21 */
     double orient_perturbation;        /* ORIENT_PERTURBATION (0.174533)              definitions.h:22 */
@@ -168,7 +169,8 @@ int cvx_get_device_results(cvx_ctx* ctx, cvx_device_results* out);
  * into one std::set<int> per view; here the context keeps one bit per resident edge.  cvx_claims_accumulate marks, for every
  * accepted pair of the last run that reaches the EdgeMapping insertions (EdgeSketch_Core.cpp:682-726): the view-1 edge, the
  * view-2 representative, its cluster members (hypo2_clusters lookup, hpp:193-202) and the supporting edge of every
- * validation view.  Bits persist across passes until cvx_claims_reset or a new cvx_set_view_edges of that view. */
+ * validation view.  Only the rows the reference's paired_edge holds per view-1 edge (at most n_views, in its std::sort order,
+ * EdgeSketch_Core.cpp:513-526) claim.  Bits persist across passes until cvx_claims_reset or a new cvx_set_view_edges of that view. */
 int cvx_claims_reset(cvx_ctx* ctx);
 int cvx_claims_accumulate(cvx_ctx* ctx);
 /* claimed[v] = number of claimed edges of view v, total[v] = edges of view v (n_views entries each; either may be NULL) */

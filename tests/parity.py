@@ -53,6 +53,7 @@ def compare(orc, gpu, check_intermediates=False, check_finalize=True):
             assert fm[h] < MARGIN, f"view-1 edge {h}: hypothesis table differs and the oracle margin is {fm[h]:.3e}"
             bad_h1.add(h)
     rep["threshold_disagreements_form"] = len(bad_h1)
+    rep["bad_h1"] = sorted(int(h) for h in bad_h1)      # view-1 edges excluded downstream (oracle margin < 1e-9), for exact set comparisons
     # ---- rows: values and support matrix
     maxrel = 0.0
     n_sup_diff = 0
@@ -138,3 +139,23 @@ def compare(orc, gpu, check_intermediates=False, check_finalize=True):
         rep["tgt_maxabs"] = float(np.max(np.abs(inter["tgt"][both] - gi["tgt"][both]))) if both.any() else 0.0
         assert rep["wedge31_maxabs"] <= ABS_ANGLE and rep["wedge32_maxabs"] <= ABS_ANGLE and rep["tgt_maxabs"] <= 1e-9
     return rep
+
+
+def assert_claims_equal(orc, masks_o, masks_g, bad_h1, view2):
+    """Claimed-edge masks (one uint8 array per view): exact, except that view-2 bits of the hypothesis rows of `bad_h1` (view-1 edges
+    whose cluster representative is a sub-1e-9 tie) may differ.  Returns the number of differing bits (all attributed)."""
+    t, r = orc.h1_table(), orc.rows()
+    unsure = set()
+    for h in bad_h1:
+        n, s = int(t["n"][h]), int(t["off"][h])
+        unsure.update(r["h2_orig"][s:s + n].tolist())
+        unsure.update(r["raw_at_local"][s:s + n].tolist())
+    n_diff = 0
+    for v, (mo, mg) in enumerate(zip(masks_o, masks_g)):
+        d = np.nonzero(np.asarray(mo, bool) != np.asarray(mg, bool))[0]
+        if v == view2:
+            assert set(d.tolist()) <= unsure, f"view {v}: claim bits differ outside the near-tie rows: {sorted(set(d.tolist()) - unsure)[:10]}"
+        else:
+            assert len(d) == 0, f"view {v}: {len(d)} claim bits differ"
+        n_diff += len(d)
+    return n_diff
