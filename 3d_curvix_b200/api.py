@@ -16,7 +16,9 @@ SYMBOLS = [
     "cvx_set_hypothesis_pair", "cvx_run_edge_sketch", "cvx_get_counts", "cvx_get_h2_angles", "cvx_get_h1_wedges",
     "cvx_get_h1_table", "cvx_get_rows", "cvx_get_support_matrix", "cvx_set_keep_intermediates", "cvx_get_intermediates", "cvx_get_valid_rows",
     "cvx_get_pairs", "cvx_get_reference_order", "cvx_finalize", "cvx_get_device_results", "cvx_get_timings", "cvx_synchronize", "cvx_get_stream",
-    "cvx_claims_reset", "cvx_claims_accumulate", "cvx_claims_get_counts", "cvx_claims_get_mask",
+    "cvx_claims_reset", "cvx_claims_accumulate", "cvx_claims_get_counts", "cvx_claims_get_mask", "cvx_claims_allreduce",
+    "cvx_split_h1_by_rows", "cvx_comm_unique_id", "cvx_comm_init", "cvx_comm_attach", "cvx_comm_destroy", "cvx_gather_reset",
+    "cvx_gather_post", "cvx_gather_wait", "cvx_gather_get", "cvx_gather_fetch", "cvx_gather_stats",
     "cvx_support_problem_create", "cvx_support_problem_run", "cvx_support_problem_stats", "cvx_support_problem_result",
     "cvx_support_problem_destroy",
 ]
@@ -59,6 +61,11 @@ class CvxDeviceResults(C.Structure):
                 ("gamma_cam", C.c_void_p), ("gamma_world", C.c_void_p), ("tangent_world", C.c_void_p)]
 
 
+class CvxGatheredUnit(C.Structure):
+    _fields_ = [("meta", C.c_int64 * 8), ("pair_h1", C.c_void_p), ("pair_h2rep", C.c_void_p), ("pair_count", C.c_void_p), ("nan_flag", C.c_void_p),
+                ("pair_supports", C.c_void_p), ("gamma_world", C.c_void_p), ("tangent_world", C.c_void_p), ("gamma_cam", C.c_void_p)]
+
+
 _lib = None
 
 
@@ -81,6 +88,13 @@ def load():
     lib.cvx_support_problem_stats.argtypes = [C.c_void_p] + [C.POINTER(C.c_int64)] * 4
     lib.cvx_support_problem_result.argtypes = [C.c_void_p, C.c_void_p]
     lib.cvx_support_problem_destroy.argtypes = [C.c_void_p]
+    lib.cvx_gather_post.argtypes = [C.c_void_p, C.c_int64, C.c_int]
+    lib.cvx_gather_wait.argtypes = [C.c_void_p, C.c_int, C.c_int]
+    lib.cvx_gather_get.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(CvxGatheredUnit)]
+    lib.cvx_gather_fetch.argtypes = [C.c_void_p, C.c_int, C.c_int] + [C.c_void_p] * 8
+    lib.cvx_comm_init.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
+    lib.cvx_comm_attach.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int]
+    lib.cvx_split_h1_by_rows.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
     _lib = lib
     return lib
 
@@ -287,6 +301,59 @@ class EdgeSketch:
         out = np.zeros(self.n_edges[view], np.uint8)
         self._ck(self.lib.cvx_claims_get_mask(self.h, view, _vp(out)))
         return out.astype(bool)
+
+    def split_h1_by_rows(self, parts):
+        """parts + 1 bounds of contiguous view-1 ranges with about equal hypothesis-row counts (current pair)."""
+        b = np.empty(parts + 1, np.int32)
+        self._ck(self.lib.cvx_split_h1_by_rows(self.h, parts, _vp(b)))
+        return b
+
+    # ---- multi-GPU gather (cvx_comm.cu): NCCL behind the C-ABI
+    @staticmethod
+    def comm_unique_id():
+        buf = C.create_string_buffer(128)
+        rc = load().cvx_comm_unique_id(buf)
+        if rc != 0:
+            raise CurvixError("cvx_comm_unique_id failed (libnccl.so.2 not loadable?)")
+        return buf.raw
+
+    def comm_init(self, world, rank, unique_id):
+        self._ck(self.lib.cvx_comm_init(self.h, world, rank, C.c_char_p(unique_id)))
+        self.world, self.rank = world, rank
+
+    def gather_reset(self):
+        self._ck(self.lib.cvx_gather_reset(self.h))
+
+    def gather_post(self, unit_id=0, empty=False):
+        self._ck(self.lib.cvx_gather_post(self.h, int(unit_id), 1 if empty else 0))
+
+    def gather_wait(self, join_stream=True, host_sync=False):
+        self._ck(self.lib.cvx_gather_wait(self.h, 1 if join_stream else 0, 1 if host_sync else 0))
+
+    def gather_get(self, rnd, rank):
+        u = CvxGatheredUnit()
+        self._ck(self.lib.cvx_gather_get(self.h, rnd, rank, C.byref(u)))
+        return u
+
+    def gather_fetch(self, rnd, rank):
+        """Host copies of what `rank` contributed in round `rnd` (rank 0 only)."""
+        u = self.gather_get(rnd, rank)
+        P, V = int(u.meta[0]), int(u.meta[6])
+        out = dict(meta=[int(x) for x in u.meta], h1=np.empty(P, np.int32), h2rep=np.empty(P, np.int32), count=np.empty(P, np.int32),
+                   nan_flag=np.empty(P, np.int32), supports=np.empty((P, V), np.int32), gamma_world=np.empty((P, 3)),
+                   tangent_world=np.empty((P, 3)), gamma_cam=np.empty((P, 3)))
+        if P:
+            self._ck(self.lib.cvx_gather_fetch(self.h, rnd, rank, *[_vp(out[k]) for k in ("h1", "h2rep", "count", "nan_flag", "supports", "gamma_world",
+                                                                                         "tangent_world", "gamma_cam")]))
+        return out
+
+    def gather_stats(self):
+        a, b, ms = C.c_int64(), C.c_int64(), C.c_float()
+        self._ck(self.lib.cvx_gather_stats(self.h, C.byref(a), C.byref(b), C.byref(ms)))
+        return dict(bytes_sent=a.value, bytes_received=b.value, comm_ms=ms.value)
+
+    def claims_allreduce(self):
+        self._ck(self.lib.cvx_claims_allreduce(self.h))
 
     def device_results(self):
         r = CvxDeviceResults()

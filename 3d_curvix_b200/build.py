@@ -34,14 +34,14 @@ def _cxx():
 
 
 def build_cuda(force=False, verbose=False):
-    srcs = [os.path.join(CSRC, f) for f in ("cvx_kernels.cu", "cvx_api.cu")]
-    deps = srcs + [os.path.join(CSRC, f) for f in ("cvx_kernels.cuh", "cvx_math.cuh")] + [os.path.join(ROOT, "include", "curvix_b200.h")]
+    srcs = [os.path.join(CSRC, f) for f in ("cvx_kernels.cu", "cvx_api.cu", "cvx_comm.cu")]
+    deps = srcs + [os.path.join(CSRC, f) for f in ("cvx_kernels.cuh", "cvx_math.cuh", "cvx_internal.h")] + [os.path.join(ROOT, "include", "curvix_b200.h")]
     if not force and not _stale(LIB, deps):
         return LIB
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
     out = os.environ.get("CVX_LIB_OUT", LIB)            # experiments: alternative output name + extra -D flags
     extra = os.environ.get("CVX_NVCC_EXTRA", "").split()
-    cmd = [nvcc] + NVCC_FLAGS + extra + ["-ccbin", _cxx(), "-shared", "-o", out] + srcs
+    cmd = [nvcc] + NVCC_FLAGS + extra + ["-ccbin", _cxx(), "-shared", "-o", out] + srcs + ["-ldl"]   # NCCL is dlopen-ed (cvx_comm.cu)
     if verbose:
         cmd.insert(1, "-Xptxas=-v")
         print(" ".join(cmd))

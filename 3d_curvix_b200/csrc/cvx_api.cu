@@ -15,6 +15,7 @@
 #include <string>
 #include <vector>
 
+#include "cvx_internal.h"
 #include "cvx_kernels.cuh"
 
 using namespace cvx;
@@ -157,6 +158,7 @@ struct cvx_ctx {
     size_t claim_words = 0;
     DevBuf<unsigned long long> d_claim_cnt;
     DevBuf<uint8_t> d_claim_mask, d_keep;
+    CvxCommState* comm = nullptr;               // multi-GPU gather state (cvx_comm.cu), NULL until cvx_comm_init / cvx_comm_attach
     cvx_counts counts;
     cvx_timings tm;
     cudaEvent_t ev[10];                         // run: 0,1,3,4,5; finalize: 6,7; set_pair: 8,9
@@ -304,6 +306,7 @@ int cvx_destroy(cvx_ctx* ctx) {
     if (!ctx) return CVX_ERR_INVALID;
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
+    if (ctx->comm) { cvx_comm_release(ctx->comm); ctx->comm = nullptr; }
     free_arena(ctx->ea);
     DevBuf<int32_t>* ib[] = {&ctx->d_edge_n, &ctx->d_vali, &ctx->d_cell_end, &ctx->d_cell_end_b, &ctx->d_scan_tmp, &ctx->d_wflag_h1, &ctx->d_m, &ctx->d_n, &ctx->d_ncl,
                              &ctx->d_nvalid, &ctx->d_nsel, &ctx->r_h1, &ctx->r_h2orig, &ctx->r_local, &ctx->r_rawat, &ctx->r_label, &ctx->r_h2rep,
@@ -321,7 +324,7 @@ int cvx_destroy(cvx_ctx* ctx) {
     for (auto* b : d2) b->release();
     ctx->u_geom.release(); ctx->d_vc.release(); ctx->d_ctr.release(); ctx->d_big_list.release(); ctx->d_ingest.release(); ctx->d_ingest_tab.release(); ctx->d_vg.release(); ctx->d_minmax.release();
     if (ctx->d_claim) cudaFree(ctx->d_claim);
-    ctx->d_claim_cnt.release(); ctx->d_claim_mask.release();
+    ctx->d_claim_cnt.release(); ctx->d_claim_mask.release(); ctx->d_keep.release();
     for (auto& e : ctx->ev) cudaEventDestroy(e);
     cudaStreamDestroy(ctx->stream);
     if (ctx->pin) cudaFreeHost(ctx->pin);
@@ -917,6 +920,35 @@ int cvx_claims_get_mask(cvx_ctx* ctx, int view, uint8_t* out) {
     return CVX_OK;
 }
 
+// Row-balanced split of view 1 (include/curvix_b200.h): the count pass over all view-1 edges, an exclusive scan, and the edges at
+// which the running row count crosses k / parts of the total.
+int cvx_split_h1_by_rows(cvx_ctx* ctx, int parts, int32_t* bounds) {
+    if (!ctx || ctx->h1 < 0 || parts < 1 || !bounds) return fail(ctx, CVX_ERR_INVALID, "cvx_split_h1_by_rows: bad arguments / no pair");
+    CU(cudaSetDevice(ctx->device));
+    const int E1 = ctx->edge_n[ctx->h1], E2 = ctx->edge_n[ctx->h2];
+    const int E1a = std::max(E1, 1);
+    cudaStream_t st = ctx->stream;
+    const double *x1 = ctx->ea.x + ctx->edge_off[ctx->h1], *y1 = ctx->ea.y + ctx->edge_off[ctx->h1];
+    const double *x2 = ctx->ea.x + ctx->edge_off[ctx->h2], *y2 = ctx->ea.y + ctx->edge_off[ctx->h2], *th2 = ctx->ea.th + ctx->edge_off[ctx->h2];
+    CU(ctx->d_m.reserve(E1a)); CU(ctx->d_n.reserve(E1a)); CU(ctx->d_row_off.reserve(E1a + 1));
+    CU(cudaMemsetAsync(ctx->d_m.p, 0, E1a * 4, st)); CU(cudaMemsetAsync(ctx->d_n.p, 0, E1a * 4, st));
+    launch_form_count(ctx->pc, x1, y1, 0, E1, ctx->d_wedge_h1.p, x2, y2, th2, ctx->d_ang2.p, E2, ctx->h2ix, ctx->d_m.p, ctx->d_n.p, st);
+    launch_scan_i32_i64(ctx->d_n.p, ctx->d_row_off.p, E1, st);
+    ctx->tm.kernel_launches += 2;
+    std::vector<int64_t> off(size_t(E1) + 1);
+    D2H(off.data(), ctx->d_row_off.p, E1 + 1, int64_t);
+    ctx->have_run = false; ctx->have_final = false; ctx->h_row_off_valid = false;   // the tables of an earlier run were overwritten
+    const int64_t H = off[size_t(E1)];
+    bounds[0] = 0;
+    for (int k = 1; k < parts; k++) {
+        const int64_t target = (H * k) / parts;
+        const auto it = std::lower_bound(off.begin(), off.end(), target);
+        bounds[k] = std::max<int32_t>(bounds[k - 1], int32_t(std::min<int64_t>(it - off.begin(), E1)));
+    }
+    bounds[parts] = E1;
+    return CVX_OK;
+}
+
 int cvx_get_timings(cvx_ctx* ctx, cvx_timings* out) {
     if (!ctx || !out) return CVX_ERR_INVALID;
     if (ctx->timings_pending) {
@@ -1070,3 +1102,33 @@ int cvx_support_problem_destroy(cvx_support_problem* p) {
 }
 
 }  // extern "C"
+
+// ------------------------------------------------------------------------------------------------------------------
+// internal interface of cvx_comm.cu (cvx_internal.h)
+// ------------------------------------------------------------------------------------------------------------------
+int cvx_internal_fail(cvx_ctx* ctx, int code, const char* msg) { return fail(ctx, code, msg ? msg : ""); }
+CvxCommState** cvx_internal_comm_slot(cvx_ctx* ctx) { return &ctx->comm; }
+int cvx_internal_device(cvx_ctx* ctx, int* device, cudaStream_t* stream) {
+    if (device) *device = ctx->device;
+    if (stream) *stream = ctx->stream;
+    return CVX_OK;
+}
+void cvx_internal_count_launch(cvx_ctx* ctx, int n) { ctx->tm.kernel_launches += n; }
+int cvx_internal_results(cvx_ctx* ctx, CvxResultsView* out) {
+    if (!ctx || !out || !ctx->have_run) return fail(ctx, CVX_ERR_INVALID, "no run to gather");
+    CU(cudaSetDevice(ctx->device));
+    const int rc = run_finalize(ctx);
+    if (rc) return rc;
+    out->P = ctx->P; out->V = ctx->n_vali; out->device = ctx->device;
+    out->view1 = ctx->h1; out->view2 = ctx->h2; out->run_begin = ctx->run_begin; out->run_end = ctx->run_end;
+    out->h1 = ctx->p_h1.p; out->h2rep = ctx->p_h2rep.p; out->count = ctx->p_count.p; out->nan = ctx->f_nan.p; out->sup = ctx->p_sup.p;
+    out->gc = ctx->f_gc.p; out->gw = ctx->f_gw.p; out->tw = ctx->f_tw.p;
+    out->stream = ctx->stream;
+    return CVX_OK;
+}
+int cvx_internal_claim_words(cvx_ctx* ctx, uint32_t** words, size_t* n_words) {
+    CU(cudaSetDevice(ctx->device));
+    if (!ctx->d_claim) { const int rc = cvx_claims_reset(ctx); if (rc) return rc; }
+    *words = ctx->d_claim; *n_words = ctx->claim_words;
+    return CVX_OK;
+}

@@ -164,6 +164,54 @@ typedef struct cvx_device_results {
 } cvx_device_results;
 int cvx_get_device_results(cvx_ctx* ctx, cvx_device_results* out);
 
+/* Balanced split of the view-1 edges of the current pair into `parts` contiguous ranges of about equal HYPOTHESIS-ROW count
+ * (the candidate count pass of Run_3D_Edge_Sketch, EdgeSketch_Core.cpp:223-247, run over all of view 1; an equal-edge split is
+ * unbalanced when the edges come in scan order).  bounds has parts + 1 entries: range k = [bounds[k], bounds[k+1]).  This is the
+ * only split a data-dependent pass schedule (configs 1) can use across GPUs: every rank runs its range of the same pair. */
+int cvx_split_h1_by_rows(cvx_ctx* ctx, int parts, int32_t* bounds);
+
+/* ---- multi-GPU: the path's only exchange step, the gather of a unit's results to rank 0 ----------------------------
+ * One context per GPU (one process each, or one thread each in a single process).  The consumer is the rank-0 loop that feeds
+ * EdgeMapping::add3DToSupportingEdgesMapping (EdgeSketch_Core.cpp:682-726) and the output writers (:735-774).
+ * A "unit" is one cvx_run_edge_sketch (+ finalize) call: a whole hypothesis view pair, or a view-1 range of one.  Gathers are
+ * collective ROUNDS: in every round each rank contributes one unit (or nothing); counts travel with one ncclAllGather of a
+ * 64-byte record per rank, payloads with grouped ncclSend / ncclRecv of the exact byte counts to rank 0 on a side stream, so the
+ * transfer of round k overlaps the compute of round k + 1.  NCCL is loaded at run time (dlopen of libnccl.so.2); contexts that
+ * never call these functions do not need it.
+ *
+ * cvx_comm_unique_id fills 128 bytes (ncclUniqueId) on one rank; the caller broadcasts them by any means and every rank calls
+ * cvx_comm_init.  cvx_comm_attach adopts a communicator the caller created (ncclComm_t as void*, e.g. from ncclCommInitAll). */
+int cvx_comm_unique_id(void* id128);
+int cvx_comm_init(cvx_ctx* ctx, int world, int rank, const void* id128);
+int cvx_comm_attach(cvx_ctx* ctx, void* nccl_comm, int world, int rank);
+int cvx_comm_destroy(cvx_ctx* ctx);
+/* Starts a new sequence of rounds (rank 0 rewinds its receive arena). */
+int cvx_gather_reset(cvx_ctx* ctx);
+/* Contributes the results of the last run of this context (empty != 0: this rank has no unit in this round) as round
+ * number = calls since cvx_gather_reset.  unit_id is carried to rank 0 untouched.  Returns after enqueueing; the context may be
+ * used for the next unit immediately (its results were copied to a staging buffer on the context stream). */
+int cvx_gather_post(cvx_ctx* ctx, int64_t unit_id, int empty);
+/* Completes every posted round.  With join_stream != 0 the context stream is made to wait for the transfers (so an event
+ * recorded on it afterwards times them); with host_sync != 0 the call also blocks until they are done. */
+int cvx_gather_wait(cvx_ctx* ctx, int join_stream, int host_sync);
+/* Rank 0, after cvx_gather_wait: what `rank` contributed in `round`.  Device pointers into the receive arena, valid until the next
+ * cvx_gather_reset.  meta: {n_pairs, view1, view2, h1_begin, h1_end, unit_id, n_vali_views, 0}. */
+typedef struct cvx_gathered_unit {
+    int64_t meta[8];
+    const int32_t* pair_h1; const int32_t* pair_h2rep; const int32_t* pair_count; const int32_t* nan_flag; const int32_t* pair_supports;
+    const double* gamma_world; const double* tangent_world; const double* gamma_cam;
+} cvx_gathered_unit;
+int cvx_gather_get(cvx_ctx* ctx, int round, int rank, cvx_gathered_unit* out);
+/* Host copies of a gathered unit (any pointer may be NULL); synchronises. */
+int cvx_gather_fetch(cvx_ctx* ctx, int round, int rank, int32_t* h1, int32_t* h2rep, int32_t* count, int32_t* nan_flag, int32_t* supports,
+                     double* gamma_world, double* tangent_world, double* gamma_cam);
+/* Bitwise OR of the claimed-edge bitmaps of all ranks into every rank (ncclAllReduce is not defined for OR: the words are gathered
+ * and OR-ed), so that cvx_claims_get_counts / next-view selection see the claims of the whole pass when a pair was sharded by
+ * view-1 range.  Collective. */
+int cvx_claims_allreduce(cvx_ctx* ctx);
+/* bytes moved and milliseconds the comm stream was busy since cvx_gather_reset (rank-local; ms needs the rounds complete) */
+int cvx_gather_stats(cvx_ctx* ctx, int64_t* bytes_sent, int64_t* bytes_received, float* comm_ms);
+
 /* ---- claimed edges: replaces the bookkeeping half of Calculate_Edge_Support_Ratios_And_Select_Next_Views
  * (EdgeSketch_Core.cpp:776-813).  The reference re-reads all edge files and walks EdgeMapping::edge_3D_to_supporting_edges
  * into one std::set<int> per view; here the context keeps one bit per resident edge.  cvx_claims_accumulate marks, for every
