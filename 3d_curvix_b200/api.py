@@ -347,6 +347,18 @@ class EdgeSketch:
                                                                                          "tangent_world", "gamma_cam")]))
         return out
 
+    def gather_fetch_into(self, rnd, rank, ptrs):
+        """Same, into caller-owned host buffers (raw pointers, e.g. pinned memory): ptrs = dict with any of h1, h2rep, count, nan_flag,
+        supports, gamma_world, tangent_world, gamma_cam.  Returns the number of bytes copied."""
+        u = self.gather_get(rnd, rank)
+        P, V = int(u.meta[0]), int(u.meta[6])
+        if P == 0:
+            return 0
+        order = ("h1", "h2rep", "count", "nan_flag", "supports", "gamma_world", "tangent_world", "gamma_cam")
+        width = dict(h1=4, h2rep=4, count=4, nan_flag=4, supports=4 * V, gamma_world=24, tangent_world=24, gamma_cam=24)
+        self._ck(self.lib.cvx_gather_fetch(self.h, rnd, rank, *[C.c_void_p(ptrs[k]) if ptrs.get(k) else None for k in order]))
+        return sum(P * width[k] for k in order if ptrs.get(k))
+
     def gather_stats(self):
         a, b, ms = C.c_int64(), C.c_int64(), C.c_float()
         self._ck(self.lib.cvx_gather_stats(self.h, C.byref(a), C.byref(b), C.byref(ms)))

@@ -257,6 +257,7 @@ void EdgeSketch_Core::Finalize_Edge_Pairs_and_Reconstruct_3D_Edges(std::shared_p
 // ---- Stack_3D_Edges, EdgeSketch_Core.cpp:735-774.  The camera -> world transform R1^T (Gamma - T1) (:742-748) is done by the
 // finalize kernel; what remains is the two `ofstream << MatrixXd` writes and the concatenation.
 void EdgeSketch_Core::Stack_3D_Edges() {
+    const double t0 = now_s();
     if (opt_.write_3d_edges) {
         const std::string p_edges = opt_.outputs_dir + "/3D_edges_" + Post_File_Name_Str;
         const std::string p_tgts = opt_.outputs_dir + "/3D_tangents_" + Post_File_Name_Str;
@@ -266,6 +267,7 @@ void EdgeSketch_Core::Stack_3D_Edges() {
         if (!curvix_host::write_eigen_matrix(p_tgts, tangent3Ds.d.data(), tangent3Ds.rows, 3)) die_file(p_tgts);
     }
     all_3D_Edges.append_rows(Gamma1s_world);   // :766-773
+    stack_time += now_s() - t0;                // untimed in the reference; part of BASELINE.json's seconds-per-object metric
 }
 
 // ---- Calculate_Edge_Support_Ratios_And_Select_Next_Views, EdgeSketch_Core.cpp:776-871

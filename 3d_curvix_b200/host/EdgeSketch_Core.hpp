@@ -82,7 +82,7 @@ public:
     double K[9] = {0};           // single intrinsic matrix (Use_Multiple_K = false)
     std::vector<double> All_K;   // n x 9 when Use_Multiple_K
     double pair_edges_time = 0.0, finalize_edge_pair_time = 0.0, find_next_hypothesis_view_time = 0.0;
-    double read_edges_time = 0.0;   // not in the reference's total (file reading is untimed there)
+    double read_edges_time = 0.0, stack_time = 0.0;   // not in the reference's total (file reading is untimed there)
     double avg_ratio = 0.0;
     std::vector<int> history_hypothesis_views_index;
 

@@ -113,6 +113,7 @@ int main(int argc, char** argv) {
     std::cout << "     - Time for Pairing up Edges:              " << MWV_Edge_Rec.pair_edges_time << " (s)" << std::endl;
     std::cout << "     - Time for Finalizing Edge Pairs:         " << MWV_Edge_Rec.finalize_edge_pair_time << " (s)" << std::endl;
     std::cout << "     - Time for Finding Next Hypothesis Views: " << MWV_Edge_Rec.find_next_hypothesis_view_time << " (s)" << std::endl;
+    std::cout << "     - (untimed in the reference) Stacking 3D edges + writing the two files: " << MWV_Edge_Rec.stack_time << " (s)" << std::endl;
     std::cout << "     - (untimed in the reference) edge file reading + upload: " << MWV_Edge_Rec.read_edges_time << " (s)" << std::endl;
     std::cout << "     - passes: " << edge_sketch_pass_count << ", 3D edges: " << MWV_Edge_Rec.all_3D_Edges.rows << ", 3D-2D links: "
               << edgeMapping->num_support_links() << std::endl;

@@ -4,6 +4,8 @@
 // =====================================================================================
 #include "ref_capi.hpp"
 
+#include <omp.h>
+
 #include <cstring>
 #include <memory>
 #include <string>
@@ -66,6 +68,9 @@ const char* ref_build_info(void) {
 }
 
 ref_ctx* ref_create(const ref_config* c) {
+    // The reference clamps its YAML thread count to omp_get_max_threads() (EdgeSketch_Core.cpp:78-79).  Launchers such as torchrun
+    // export OMP_NUM_THREADS=1; the caller's explicit request takes precedence over that environment default.
+    if (c->num_threads > 0) omp_set_num_threads(c->num_threads);
     ref_ctx* r = new ref_ctx();
     r->cfg = *c;
     YAML::Node& y = r->yaml;
