@@ -143,6 +143,11 @@ struct cvx_ctx {
     DevBuf<int32_t> d_support, d_support_t;
     DevBuf<DevCounters> d_ctr;
     DevBuf<int32_t> d_big_list;
+    // run-based clustering of the > 128-row edges: work lists [long runs | short runs] and the scratch table of the long runs
+    DevBuf<int4> d_run_desc;
+    DevBuf<int32_t> d_run_ctr, vr_h2orig, vr_label, vr_h2rep, vr_urank, vr_oi, vr_n, vr_ncl, vr_order;
+    DevBuf<double> vr_xc, vr_yc, vr_th, vr_xbar, vr_ybar, vr_thbar;
+    DevBuf<int64_t> vr_off;
     DevBuf<double> d_ingest;            // cvx_set_all_view_edges: packed columns before the scatter into the arena slots
     DevBuf<int64_t> d_ingest_tab;
     std::vector<int64_t> h_ingest_tab;
@@ -324,7 +329,12 @@ int cvx_destroy(cvx_ctx* ctx) {
     for (auto* b : d2) b->release();
     ctx->u_geom.release(); ctx->d_vc.release(); ctx->d_ctr.release(); ctx->d_big_list.release(); ctx->d_ingest.release(); ctx->d_ingest_tab.release(); ctx->d_vg.release(); ctx->d_minmax.release();
     if (ctx->d_claim) cudaFree(ctx->d_claim);
-    ctx->d_claim_cnt.release(); ctx->d_claim_mask.release(); ctx->d_keep.release();
+    ctx->d_claim_cnt.release(); ctx->d_claim_mask.release(); ctx->d_keep.release(); ctx->d_run_desc.release(); ctx->d_run_ctr.release();
+    { DevBuf<int32_t>* vb[] = {&ctx->vr_h2orig, &ctx->vr_label, &ctx->vr_h2rep, &ctx->vr_urank, &ctx->vr_oi, &ctx->vr_n, &ctx->vr_ncl, &ctx->vr_order};
+      for (auto* b : vb) b->release();
+      DevBuf<double>* vd[] = {&ctx->vr_xc, &ctx->vr_yc, &ctx->vr_th, &ctx->vr_xbar, &ctx->vr_ybar, &ctx->vr_thbar};
+      for (auto* b : vd) b->release();
+      ctx->vr_off.release(); }
     for (auto& e : ctx->ev) cudaEventDestroy(e);
     cudaStreamDestroy(ctx->stream);
     if (ctx->pin) cudaFreeHost(ctx->pin);
@@ -559,10 +569,31 @@ int cvx_run_edge_sketch(cvx_ctx* ctx, int h1_begin, int h1_end) {
     DevBuf<double>* db[] = {&ctx->r_xc, &ctx->r_yc, &ctx->r_th, &ctx->r_xbar, &ctx->r_ybar, &ctx->r_thbar, &ctx->r_thn, &ctx->r_orient};
     for (auto* b : db) CU(b->reserve(Ha));
     RowTable rt = row_table(ctx);
+    // scratch of the run-based clustering, sized for the worst case: H / 2 short runs, H / 33 long ones holding at most H rows
+    RunScratch rs;
+    std::memset(&rs, 0, sizeof(rs));
+    const bool any_big = H > 0;
+    if (any_big) {
+        const int64_t cap_short = H / 2 + 1, cap_long = H / 33 + 1;
+        CU(ctx->d_run_desc.reserve(size_t(cap_short + cap_long))); CU(ctx->d_run_ctr.reserve(4));
+        DevBuf<double>* vd[] = {&ctx->vr_xc, &ctx->vr_yc, &ctx->vr_th, &ctx->vr_xbar, &ctx->vr_ybar, &ctx->vr_thbar};
+        for (auto* b : vd) CU(b->reserve(Ha));
+        DevBuf<int32_t>* vi[] = {&ctx->vr_h2orig, &ctx->vr_label, &ctx->vr_h2rep, &ctx->vr_urank, &ctx->vr_oi};
+        for (auto* b : vi) CU(b->reserve(Ha));
+        CU(ctx->vr_n.reserve(size_t(cap_long))); CU(ctx->vr_ncl.reserve(size_t(cap_long))); CU(ctx->vr_order.reserve(size_t(cap_long) + 8));
+        CU(ctx->vr_off.reserve(size_t(cap_long)));
+        rs.desc_short = ctx->d_run_desc.p; rs.desc_long = ctx->d_run_desc.p + cap_short; rs.ctr = ctx->d_run_ctr.p;
+        rs.cap_long = int32_t(cap_long); rs.cap_rows = H;
+        rs.vrt.xc = ctx->vr_xc.p; rs.vrt.yc = ctx->vr_yc.p; rs.vrt.th = ctx->vr_th.p; rs.vrt.xbar = ctx->vr_xbar.p; rs.vrt.ybar = ctx->vr_ybar.p;
+        rs.vrt.thbar = ctx->vr_thbar.p; rs.vrt.h2orig = ctx->vr_h2orig.p; rs.vrt.label = ctx->vr_label.p; rs.vrt.h2rep = ctx->vr_h2rep.p;
+        rs.vrt.urank = ctx->vr_urank.p;
+        rs.v_n = ctx->vr_n.p; rs.v_ncl = ctx->vr_ncl.p; rs.v_order = ctx->vr_order.p; rs.v_off = ctx->vr_off.p; rs.v_oi = ctx->vr_oi.p;
+    }
     launch_form_fill(pc, x1, y1, h1_begin, h1_end, ctx->d_wedge_h1.p, x2, y2, th2, ctx->d_ang2.p, E2, ctx->h2ix, ctx->d_m.p, ctx->d_n.p, ctx->d_row_off.p, rt,
-                     ctx->d_ncl.p, ctx->d_big_list.p, ctx->d_big_list.p + E1a, st, ctx->stream2, ctx->ev_fork, ctx->ev_join);   // order[E1], cnts[5]
+                     ctx->d_ncl.p, ctx->d_big_list.p, ctx->d_big_list.p + E1a, any_big ? &rs : nullptr, st, ctx->stream2, ctx->ev_fork,
+                     ctx->ev_join);   // order[E1], cnts[5]
     launch_scan_i32_i64(ctx->d_ncl.p, ctx->d_u_off.p, E1, st);
-    ctx->tm.kernel_launches += 5;
+    ctx->tm.kernel_launches += 14;
     cudaEventRecord(ctx->ev[1], st);
     CU(cudaMemcpyAsync(&ctx->pin->U, ctx->d_u_off.p + E1, 8, cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));

@@ -529,9 +529,9 @@ struct ClusterSm {
 // every sum runs in member order on every lane through shuffles (bit-identical to the sequential code: the products are formed
 // per member first, the additions are the reference's left-to-right chain); sqrt / exp of the members are lane-parallel.
 __device__ __forceinline__ double shfl_d(double v, int src) { return __shfl_sync(FULL, v, src); }
-template <int N, bool ORIENT_ONLY>   // ORIENT_ONLY: the merge step needs the averaged orientation alone (EdgeClusterer.cpp:168-176)
-__device__ __noinline__ void gauss_avg_list(ClusterSm<N>& s, const int16_t* mem, int cnt, double sigma, double sigma_inv, int lane, double* gx,
-                                            double* gy, double* gth) {
+template <class SM, bool ORIENT_ONLY>   // ORIENT_ONLY: the merge step needs the averaged orientation alone (EdgeClusterer.cpp:168-176)
+__device__ __noinline__ void gauss_avg_list_t(SM& s, const int16_t* mem, int cnt, double sigma, double sigma_inv, int lane, double* gx,
+                                              double* gy, double* gth) {
     double xi = 0, yi = 0, ti = 0;
     if (lane < cnt) { const int i = mem[lane]; xi = s.x[i]; yi = s.y[i]; ti = s.thn[i]; }
     double sx = 0, sy = 0;
@@ -558,6 +558,11 @@ __device__ __noinline__ void gauss_avg_list(ClusterSm<N>& s, const int16_t* mem,
         *gx = swx / tw; *gy = swy / tw;
     }
     *gth = swo / tw;
+}
+template <int N, bool ORIENT_ONLY>
+__device__ __forceinline__ void gauss_avg_list(ClusterSm<N>& s, const int16_t* mem, int cnt, double sigma, double sigma_inv, int lane, double* gx,
+                                               double* gy, double* gth) {
+    gauss_avg_list_t<ClusterSm<N>, ORIENT_ONLY>(s, mem, cnt, sigma, sigma_inv, lane, gx, gy, gth);
 }
 // members with label la or lb, ascending, into s.mem; returns the count (<= 32 by construction)
 template <int N>
@@ -1103,9 +1108,10 @@ __global__ void __launch_bounds__(FORM_WARPS * 32) k_form(const __grid_constant_
 // k_order_by_n: one block; order[] = edges with 1 <= n <= CL_N sorted by n descending, then those with CL_N < n <= CL_BIG_N, then
 // then CL_MID_N < n <= CL_BIG_N, then CL_BIG_N < n <= CL_HUGE_N, then the rest; cnts[0..4] = the five counts.
 #define ORDER_BUCKETS (CL_N + 4)
-__global__ void __launch_bounds__(1024) k_order_by_n(const int32_t* __restrict__ n_of, int h1_begin, int h1_end, int max_cluster, int small_max,
-                                                     int32_t* __restrict__ order, int32_t* __restrict__ cnts) {
+__global__ void __launch_bounds__(1024) k_order_by_n(const int32_t* __restrict__ n_of, int h1_begin, int h1_end, const int32_t* __restrict__ end_dev,
+                                                     int max_cluster, int small_max, int32_t* __restrict__ order, int32_t* __restrict__ cnts) {
     __shared__ int hist[ORDER_BUCKETS];
+    if (end_dev) h1_end = min(h1_end, *end_dev);          // a count that only the device knows (virtual edges of the run-based clustering)
     for (int k = threadIdx.x; k < ORDER_BUCKETS; k += blockDim.x) hist[k] = 0;
     __syncthreads();
     const bool sm_ok = max_cluster <= 32;          // the shared-memory algorithm keeps member lists of at most 32
@@ -1121,6 +1127,326 @@ __global__ void __launch_bounds__(1024) k_order_by_n(const int32_t* __restrict__
     }
     __syncthreads();
     for (int i = h1_begin + threadIdx.x; i < h1_end; i += blockDim.x) { const int n = n_of[i]; if (n > 0) order[atomicAdd(&hist[key(n)], 1)] = i; }
+}
+// ---- clustering by RUNS (the > CL_N-row classes).  Every corrected candidate of a view-1 edge lies on that edge's epipolar line
+// (snapped to it or moved along its tangent onto it, PairEdgeHypo.cpp:243-282), so "dist < CLUSTER_DIST_THRESH" links only
+// candidates that are neighbours along the line: sorted by their position t along the line, the candidates fall into runs separated by
+// gaps wider than the threshold, and no merge of EdgeClusterer.cpp:138-189 ever crosses a gap.  A row's merge decision reads only
+// its own cluster and the clusters of the rows within the distance threshold, so the reference's restarted scan, restricted to a run, is
+// the reference's scan of that run alone: the runs are clustered independently, each in the reference's order (~48 runs of ~5 rows
+// per edge on cfg4, against one sequential chain of ~250 rows) -- thousands of independent chains in flight instead of one per
+// block.  Same decisions in the same order and the same per-member arithmetic as cluster_warp_sm.
+//   k_runs_prepare  block per edge: position along the line, bitonic sort, run boundaries, rows of a run back into ascending row
+//                   order.  Single-row runs are finished here; runs of 2..32 rows go to a work list; longer runs are copied, as
+//                   "virtual edges", into a scratch hypothesis table
+//   k_runs_cluster  warp per short run, the run's state in 5 lanes-worth of registers and 1.3 KB of shared memory
+//   (long runs)     the per-edge kernels below (k_order_by_n, k_cluster_classes, k_cluster_coop) on the scratch table, then
+//   k_runs_scatter  results of the long runs back to their rows
+//   k_runs_finish   warp per edge: cluster ranks in ascending label order, cluster count
+// An edge whose rows are not collinear to 1e-6 px or not finite is left to the per-edge kernels (n_clusters = -1).
+#define RUN_NMAX CL_HUGE_N     // rows of an edge
+#define RUN_SHORT 32           // rows of a run handled by one warp in registers
+#define RUN_WARPS 8
+struct RunPrepSm {
+    double key[RUN_NMAX];                  // position along the epipolar line (sort key); reused as scratch afterwards
+    int16_t ord[RUN_NMAX];                 // rows sorted by key; then, run by run, by ascending row index
+    int16_t start[RUN_NMAX + 1];           // first sorted position of every run
+    int wcnt[RUN_WARPS];
+    int bad, n_long, n_short, rows_long, base_long, base_short, base_rows;
+    double lineA, lineB, lineC, lineInv;
+};
+__global__ void __launch_bounds__(RUN_WARPS * 32) k_runs_prepare(const __grid_constant__ PassConst pc, const int32_t* __restrict__ order,
+                                                                  const int32_t* __restrict__ cnts, const double* __restrict__ x1,
+                                                                  const double* __restrict__ y1, const int32_t* __restrict__ n_of,
+                                                                  const int64_t* __restrict__ row_off, RowTable rt, int32_t* n_clusters,
+                                                                  const __grid_constant__ RunScratch rs) {
+    __shared__ RunPrepSm s;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const unsigned lt = lanemask_lt();
+    const int base = cnts[0], total = cnts[1] + cnts[2] + cnts[3];        // the CL_N < n <= CL_HUGE_N classes
+    int32_t* run_ord = rt.urank;                                          // scratch until k_runs_finish writes the ranks
+    for (int e = blockIdx.x; e < total; e += gridDim.x) {
+        const int h1 = order[base + total - 1 - e];                       // longest edges first
+        const int n = n_of[h1];
+        const int64_t row0 = row_off[h1];
+        __syncthreads();                                                  // the previous edge is done with the shared memory
+        if (tid == 0) {
+            double coef[3];
+            mat_vec(pc.F21, x1[h1], y1[h1], 1.0, coef);                   // the epipolar line of the view-1 edge: A x + B y + C = 0
+            s.lineA = coef[0]; s.lineB = coef[1]; s.lineC = coef[2]; s.lineInv = 1.0 / sqrt(coef[0] * coef[0] + coef[1] * coef[1]);
+            s.bad = 0; s.n_long = 0; s.n_short = 0; s.rows_long = 0;
+        }
+        __syncthreads();
+        int P = 32;
+        while (P < n) P <<= 1;
+        {
+            const double A = s.lineA, B = s.lineB, C = s.lineC, inv = s.lineInv;
+            int bad = 0;
+            for (int k = tid; k < P; k += blockDim.x) {
+                if (k < n) {
+                    const double xk = rt.xc[row0 + k], yk = rt.yc[row0 + k];
+                    const double t = (B * xk - A * yk) * inv, res = fabs((A * xk + B * yk) + C) * inv;
+                    s.key[k] = t;
+                    if (!(res <= 1e-6) || !(fabs(t) < 1e300)) bad = 1;
+                } else {
+                    s.key[k] = DBL_MAX;
+                }
+                s.ord[k] = int16_t(k);
+            }
+            if (bad) s.bad = 1;
+        }
+        __syncthreads();
+        if (s.bad || pc.max_cluster > 32) { if (tid == 0) n_clusters[h1] = -1; continue; }
+        for (int kk = 2; kk <= P; kk <<= 1) {                             // bitonic sort of (key, row) over P slots
+            for (int j = kk >> 1; j > 0; j >>= 1) {
+                for (int i = tid; i < P; i += blockDim.x) {
+                    const int l = i ^ j;
+                    if (l > i) {
+                        const double a = s.key[i], b = s.key[l];
+                        const bool up = (i & kk) == 0;
+                        if ((a > b) == up) { s.key[i] = b; s.key[l] = a; const int16_t t = s.ord[i]; s.ord[i] = s.ord[l]; s.ord[l] = t; }
+                    }
+                }
+                __syncthreads();
+            }
+        }
+        // run starts: a gap wider than the distance threshold (plus the collinearity tolerance) cannot be bridged by any pair
+        int run_total = 0;
+        for (int b0 = 0; b0 < P; b0 += blockDim.x) {
+            const int k = b0 + tid;
+            const bool st = k < n && (k == 0 || s.key[k] - s.key[k - 1] > pc.cl_dist + 4e-6);
+            const unsigned m = __ballot_sync(FULL, st);
+            if (lane == 0) s.wcnt[warp] = __popc(m);
+            __syncthreads();
+            int off = run_total, tot = 0;
+            for (int w = 0; w < RUN_WARPS; w++) { const int cw = s.wcnt[w]; if (w < warp) off += cw; tot += cw; }
+            if (st) s.start[off + __popc(m & lt)] = int16_t(k);
+            run_total += tot;
+            __syncthreads();
+        }
+        if (tid == 0) s.start[run_total] = int16_t(n);
+        __syncthreads();
+        {
+            int nl = 0, ns = 0, rl = 0;
+            for (int r = tid; r < run_total; r += blockDim.x) {
+                const int c = s.start[r + 1] - s.start[r];
+                if (c > RUN_SHORT) { nl++; rl += c; } else if (c > 1) ns++;
+            }
+            if (nl) { atomicAdd(&s.n_long, nl); atomicAdd(&s.rows_long, rl); }
+            if (ns) atomicAdd(&s.n_short, ns);
+        }
+        __syncthreads();
+        if (tid == 0) {
+            s.base_long = s.n_long ? atomicAdd(&rs.ctr[0], s.n_long) : 0;
+            s.base_short = s.n_short ? atomicAdd(&rs.ctr[1], s.n_short) : 0;
+            s.base_rows = s.rows_long ? atomicAdd(&rs.ctr[2], s.rows_long) : 0;
+            if (s.base_long + s.n_long > rs.cap_long || int64_t(s.base_rows) + s.rows_long > rs.cap_rows) s.bad = 1;   // cannot happen with the sizes of cvx_api.cu
+            s.n_long = 0; s.n_short = 0; s.rows_long = 0;
+        }
+        int16_t* tmp = reinterpret_cast<int16_t*>(s.key);                // the keys are dead from here on
+        for (int k = tid; k < n; k += blockDim.x) tmp[k] = s.ord[k];
+        __syncthreads();
+        if (s.bad) { if (tid == 0) n_clusters[h1] = -1; continue; }
+        for (int r = warp; r < run_total; r += RUN_WARPS) {               // rows of a run into ascending row order; work-list entries
+            const int s0 = s.start[r], c = s.start[r + 1] - s0;
+            if (c == 1) {
+                if (lane == 0) {
+                    const int i = tmp[s0];
+                    rt.label[row0 + i] = i;
+                    rt.xbar[row0 + i] = rt.xc[row0 + i]; rt.ybar[row0 + i] = rt.yc[row0 + i];
+                    rt.thbar[row0 + i] = normalize_orientation(rt.th[row0 + i], pc.cl_wrap_deg);
+                    rt.h2rep[row0 + i] = rt.h2orig[row0 + i];
+                }
+                continue;
+            }
+            int vid = 0, voff = 0;
+            if (c > RUN_SHORT) {                                          // a virtual edge of the scratch table
+                if (lane == 0) { vid = s.base_long + atomicAdd(&s.n_long, 1); voff = s.base_rows + atomicAdd(&s.rows_long, c); }
+                vid = __shfl_sync(FULL, vid, 0); voff = __shfl_sync(FULL, voff, 0);
+            }
+            for (int k = lane; k < c; k += 32) {
+                const int mine = tmp[s0 + k];
+                int rk = 0;
+                for (int j = 0; j < c; j++) rk += (tmp[s0 + j] < mine);
+                if (c > RUN_SHORT) {
+                    const int64_t q = int64_t(voff) + rk;
+                    rs.vrt.xc[q] = rt.xc[row0 + mine]; rs.vrt.yc[q] = rt.yc[row0 + mine]; rs.vrt.th[q] = rt.th[row0 + mine];
+                    rs.vrt.h2orig[q] = rt.h2orig[row0 + mine]; rs.v_oi[q] = mine;
+                } else {
+                    run_ord[row0 + s0 + rk] = mine;
+                }
+            }
+            if (lane == 0) {
+                if (c > RUN_SHORT) { rs.desc_long[vid] = make_int4(h1, voff, c, 0); rs.v_n[vid] = c; rs.v_off[vid] = voff; }
+                else rs.desc_short[s.base_short + atomicAdd(&s.n_short, 1)] = make_int4(h1, s0, c, 0);
+            }
+        }
+        if (tid == 0) n_clusters[h1] = 0;                                 // marks "clustered by runs" for k_runs_finish
+    }
+}
+// One run of c <= 32 rows, lane k = local row k (ascending row index).  Coordinates, labels and the adjacency word live in registers;
+// the per-label orientation and size in shared memory (indexed by local label); neighbours are read through shuffles in a
+// warp-uniform loop over the run.
+struct RunWarpSm {
+    double x[RUN_SHORT], y[RUN_SHORT], thn[RUN_SHORT], orient[RUN_SHORT];
+    int16_t size[RUN_SHORT], mem[32];
+};
+__device__ void cluster_run_warp(RunWarpSm& s, int c, int oi, const PassConst& pc, const int32_t* __restrict__ h2orig, double* xbar, double* ybar,
+                                 double* thbar, int32_t* h2rep, int32_t* label_out, int lane) {
+    const unsigned lt = lanemask_lt();
+    const bool me = lane < c;
+    const double xi = s.x[lane], yi = s.y[lane];
+    uint32_t adj = 0u;
+    for (int j = 0; j < c; j++) {
+        const double ddx = xi - s.x[j], ddy = yi - s.y[j];
+        if (ddx * ddx + ddy * ddy < pc.cl_dist_sq && j != lane) adj |= 1u << j;   // == sqrt(.) < cl_dist, see cl_dist_sq
+    }
+    if (!me) adj = 0u;
+    int label = lane;
+    while (true) {
+        // would my row merge now?  (EdgeClusterer.cpp:143-166; nearest row of another cluster, first minimum in ascending row order)
+        int partner = -1;
+        {
+            const double o_i = s.orient[label];
+            double bd = DBL_MAX, bs = DBL_MAX;
+            uint32_t bits = adj;
+            const int maxdeg = __reduce_max_sync(FULL, __popc(adj));      // every lane walks its own neighbours, in step (the label of a
+            for (int it = 0; it < maxdeg; it++) {                         // neighbour is read from its lane: the shuffle needs all lanes)
+                const bool has = bits != 0u;
+                const int j = has ? __ffs(bits) - 1 : lane;
+                bits &= bits - 1u;
+                const int lj = __shfl_sync(FULL, label, j);
+                if (has && lj != label && fabs(o_i - s.orient[lj]) < pc.cl_orient_rad) {   // :147-154
+                    const double ddx = xi - s.x[j], ddy = yi - s.y[j];
+                    const double sq = ddx * ddx + ddy * ddy;
+                    if (sq < bs) {
+                        const double d = sqrt(sq);
+                        if (d < bd) { bd = d; bs = sq; partner = j; }
+                    }
+                }
+            }
+        }
+        const int lpartner = __shfl_sync(FULL, label, partner >= 0 ? partner : 0);
+        if (partner >= 0 && int(s.size[lpartner]) + int(s.size[label]) > pc.max_cluster) partner = -1;   // :166
+        const unsigned can = __ballot_sync(FULL, partner >= 0);
+        if (!can) break;
+        const int mi = __ffs(can) - 1;
+        const int mj = __shfl_sync(FULL, partner, mi);
+        const int new_l = __shfl_sync(FULL, label, mi), old_l = __shfl_sync(FULL, label, mj);
+        const bool in = me && (label == old_l || label == new_l);
+        const unsigned mm = __ballot_sync(FULL, in);
+        const int cnt = min(__popc(mm), 32);
+        if (in) s.mem[__popc(mm & lt)] = int16_t(lane);
+        __syncwarp();
+        double gx, gy, gth;
+        gauss_avg_list_t<RunWarpSm, true>(s, s.mem, cnt, pc.cl_sigma, pc.cl_sigma_inv, lane, &gx, &gy, &gth);     // :168
+        __syncwarp();
+        if (lane == 0) { s.orient[new_l] = normalize_orientation(gth, pc.cl_wrap_deg); s.size[new_l] = int16_t(cnt); }   // :175-176
+        if (label == old_l) label = new_l;                                // :179-183
+        __syncwarp();
+    }
+    // :250-290 per cluster: Gaussian-weighted average written to every member, representative = member closest to it
+    const int my_size = s.size[label];
+    const int label_row = __shfl_sync(FULL, oi, label);                   // row (within the edge) of the label
+    if (me) {
+        label_out[oi] = label_row;
+        if (my_size == 1) { xbar[oi] = xi; ybar[oi] = yi; thbar[oi] = s.thn[lane]; h2rep[oi] = h2orig[oi]; }
+    }
+    unsigned roots = __ballot_sync(FULL, me && label == lane && my_size > 1);
+    while (roots) {
+        const int root = __ffs(roots) - 1;
+        roots &= roots - 1;
+        const bool in = me && label == root;
+        const unsigned mm = __ballot_sync(FULL, in);
+        const int cnt = min(__popc(mm), 32);
+        if (in) s.mem[__popc(mm & lt)] = int16_t(lane);
+        __syncwarp();
+        double gx, gy, gth;
+        gauss_avg_list_t<RunWarpSm, false>(s, s.mem, cnt, pc.cl_sigma, pc.cl_sigma_inv, lane, &gx, &gy, &gth);
+        double d = DBL_MAX;
+        int pos = lane;
+        if (lane < cnt) {
+            const int j = s.mem[lane];
+            const double ddx = s.x[j] - gx, ddy = s.y[j] - gy;
+            d = sqrt(ddx * ddx + ddy * ddy);
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {                                // first minimum in member order (:270)
+            const double od = __shfl_xor_sync(FULL, d, o);
+            const int op = __shfl_xor_sync(FULL, pos, o);
+            if (od < d || (od == d && op < pos)) { d = od; pos = op; }
+        }
+        const int rep_lane = s.mem[pos];
+        const int rep = h2orig[__shfl_sync(FULL, oi, rep_lane)];          // corrected(closest, 8), :282
+        if (in) { xbar[oi] = gx; ybar[oi] = gy; thbar[oi] = gth; h2rep[oi] = rep; }
+        __syncwarp();
+    }
+}
+__global__ void __launch_bounds__(RUN_WARPS * 32, 4) k_runs_cluster(const __grid_constant__ PassConst pc, const int64_t* __restrict__ row_off,
+                                                                     RowTable rt, const __grid_constant__ RunScratch rs) {
+    __shared__ RunWarpSm sm[RUN_WARPS];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    RunWarpSm& s = sm[warp];
+    const int n_short = rs.ctr[1];
+    const int32_t* run_ord = rt.urank;
+    const int stride = gridDim.x * RUN_WARPS;
+    for (int r = blockIdx.x * RUN_WARPS + warp; r < n_short; r += stride) {
+        const int4 d = rs.desc_short[r];
+        const int64_t row0 = row_off[d.x];
+        const int c = d.z;
+        __syncwarp();
+        int oi = 0;
+        if (lane < c) {
+            oi = run_ord[row0 + d.y + lane];
+            const double t = normalize_orientation(rt.th[row0 + oi], pc.cl_wrap_deg);   // :131-135
+            s.x[lane] = rt.xc[row0 + oi]; s.y[lane] = rt.yc[row0 + oi]; s.thn[lane] = t; s.orient[lane] = t; s.size[lane] = 1;
+        } else {
+            s.x[lane] = 0.0; s.y[lane] = 0.0; s.thn[lane] = 0.0; s.orient[lane] = 0.0; s.size[lane] = 0;
+        }
+        __syncwarp();
+        cluster_run_warp(s, c, oi, pc, rt.h2orig + row0, rt.xbar + row0, rt.ybar + row0, rt.thbar + row0, rt.h2rep + row0, rt.label + row0, lane);
+    }
+}
+// results of the long runs (virtual edges of the scratch table) back to their rows: warp per run
+__global__ void __launch_bounds__(RUN_WARPS * 32) k_runs_scatter(const int64_t* __restrict__ row_off, RowTable rt, const __grid_constant__ RunScratch rs) {
+    const int lane = threadIdx.x & 31;
+    const int n_long = rs.ctr[0];
+    const int stride = gridDim.x * RUN_WARPS;
+    for (int r = blockIdx.x * RUN_WARPS + (threadIdx.x >> 5); r < n_long; r += stride) {
+        const int4 d = rs.desc_long[r];
+        const int64_t row0 = row_off[d.x], q0 = d.y;
+        for (int k = lane; k < d.z; k += 32) {
+            const int64_t q = q0 + k;
+            const int64_t i = row0 + rs.v_oi[q];
+            rt.xbar[i] = rs.vrt.xbar[q]; rt.ybar[i] = rs.vrt.ybar[q]; rt.thbar[i] = rs.vrt.thbar[q]; rt.h2rep[i] = rs.vrt.h2rep[q];
+            rt.label[i] = rs.v_oi[q0 + rs.vrt.label[q]];
+        }
+    }
+}
+// cluster ranks in ascending label order (the reference's std::map order) and the cluster count of every edge clustered by runs
+__global__ void __launch_bounds__(RUN_WARPS * 32) k_runs_finish(const int32_t* __restrict__ order, const int32_t* __restrict__ cnts,
+                                                                 const int32_t* __restrict__ n_of, const int64_t* __restrict__ row_off, RowTable rt,
+                                                                 int32_t* n_clusters) {
+    const int lane = threadIdx.x & 31;
+    const unsigned lt = lanemask_lt();
+    const int base = cnts[0], total = cnts[1] + cnts[2] + cnts[3];
+    const int e = blockIdx.x * RUN_WARPS + (threadIdx.x >> 5);
+    if (e >= total) return;
+    const int h1 = order[base + e];
+    if (n_clusters[h1] != 0) return;                                      // left to the per-edge kernels
+    const int n = n_of[h1];
+    const int64_t row0 = row_off[h1];
+    int nroots = 0;
+    for (int b0 = 0; b0 < n; b0 += 32) {
+        const int k = b0 + lane;
+        const bool root = k < n && rt.label[row0 + k] == k;
+        const unsigned m = __ballot_sync(FULL, root);
+        if (root) rt.urank[row0 + k] = nroots + __popc(m & lt);
+        nroots += __popc(m);
+    }
+    __syncwarp();
+    for (int k = lane; k < n; k += 32) { const int l = rt.label[row0 + k]; if (l != k) rt.urank[row0 + k] = rt.urank[row0 + l]; }
+    if (lane == 0) n_clusters[h1] = nroots;
 }
 // The <= 128 / 256 / 512-row classes in ONE launch.  A block is a "unit" of one shared-memory size (CL_SMEM_QUANTUM): one 512-row edge
 // (all 8 warps), two 256-row edges (4 warps each) or eight <= 128-row edges (a warp each); units are numbered longest class first, so the hardware
@@ -1144,20 +1470,24 @@ __device__ __forceinline__ void cluster_edge_block(int h1, const PassConst& pc, 
 }
 __global__ void __launch_bounds__(CL_SMALL_WARPS * 32, 4) k_cluster_classes(const __grid_constant__ PassConst pc, const int32_t* __restrict__ order,
                                                                          const int32_t* __restrict__ cnts, const int32_t* __restrict__ n_of,
-                                                                         const int64_t* __restrict__ row_off, RowTable rt, int32_t* n_clusters) {
+                                                                         const int64_t* __restrict__ row_off, RowTable rt, int32_t* n_clusters, int mode) {
+    // mode 3: every class; 1: the <= CL_N-row class only; 2: only the > CL_N-row edges that k_cluster_runs left behind (n_clusters == -1)
     extern __shared__ __align__(16) unsigned char cl_smem[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int n_small = cnts[0], n_mid = cnts[1], n_big = cnts[2];
-    const int u_big = n_big, u_mid = (n_mid + CL_MID_EDGES - 1) / CL_MID_EDGES, u_small = (n_small + CL_SMALL_WARPS - 1) / CL_SMALL_WARPS;
+    const int u_big = (mode & 2) ? n_big : 0, u_mid = (mode & 2) ? (n_mid + CL_MID_EDGES - 1) / CL_MID_EDGES : 0;
+    const int u_small = (mode & 1) ? (n_small + CL_SMALL_WARPS - 1) / CL_SMALL_WARPS : 0;
     const int units = u_big + u_mid + u_small;
+    const bool left_only = mode == 2;
     for (int unit = blockIdx.x; unit < units; unit += gridDim.x) {
         if (unit < u_big) {                                               // one edge, the whole block
-            cluster_edge_block<CL_BIG_N, CL_SMALL_WARPS>(order[n_small + n_mid + unit], pc, *reinterpret_cast<ClusterSmB<CL_BIG_N>*>(cl_smem), n_of, row_off,
-                                                         rt, n_clusters, warp, lane, 1);
+            const int h1 = order[n_small + n_mid + unit];
+            if (!left_only || n_clusters[h1] == -1)
+                cluster_edge_block<CL_BIG_N, CL_SMALL_WARPS>(h1, pc, *reinterpret_cast<ClusterSmB<CL_BIG_N>*>(cl_smem), n_of, row_off, rt, n_clusters, warp, lane, 1);
         } else if (unit < u_big + u_mid) {                                // CL_MID_EDGES edges, CL_MID_WARPS warps each
             const int g = warp / CL_MID_WARPS;
             const int e = (unit - u_big) * CL_MID_EDGES + g;
-            if (e < n_mid)
+            if (e < n_mid && (!left_only || n_clusters[order[n_small + e]] == -1))
                 cluster_edge_block<CL_MID_N, CL_MID_WARPS>(order[n_small + e], pc, reinterpret_cast<ClusterSmB<CL_MID_N>*>(cl_smem)[g], n_of, row_off, rt,
                                                            n_clusters, warp - g * CL_MID_WARPS, lane, 1 + g);
         } else {                                                          // one <= 128-row edge per warp
@@ -1171,13 +1501,15 @@ __global__ void __launch_bounds__(CL_SMALL_WARPS * 32, 4) k_cluster_classes(cons
 template <int N, int W>
 __global__ void __launch_bounds__(W * 32) k_cluster_coop(const __grid_constant__ PassConst pc, const int32_t* __restrict__ order,
                                                          const int32_t* __restrict__ cnts, int which, const int32_t* __restrict__ n_of,
-                                                         const int64_t* __restrict__ row_off, RowTable rt, int32_t* n_clusters) {
+                                                         const int64_t* __restrict__ row_off, RowTable rt, int32_t* n_clusters, int left_only) {
     extern __shared__ __align__(16) unsigned char cl_smem[];
     int base = 0;
     for (int k = 0; k < which; k++) base += cnts[k];
     const int cnt = cnts[which];
     for (int b = blockIdx.x; b < cnt; b += gridDim.x) {
-        cluster_edge_block<N, W>(order[base + b], pc, *reinterpret_cast<ClusterSmB<N>*>(cl_smem), n_of, row_off, rt, n_clusters, threadIdx.x >> 5,
+        const int h1 = order[base + b];
+        if (left_only && n_clusters[h1] != -1) continue;                  // already clustered by k_cluster_runs
+        cluster_edge_block<N, W>(h1, pc, *reinterpret_cast<ClusterSmB<N>*>(cl_smem), n_of, row_off, rt, n_clusters, threadIdx.x >> 5,
                                  threadIdx.x & 31, 1);
         __syncthreads();
     }
@@ -1207,7 +1539,7 @@ void launch_form_count(const PassConst& pc, const double* x1, const double* y1, 
 void launch_form_fill(const PassConst& pc, const double* x1, const double* y1, int h1_begin, int h1_end, const double2* wedge_h1,
                       const double* x2, const double* y2, const double* th2, const double* ang2, int E2, AngleIndex ix, const int32_t* m_of,
                       const int32_t* n_of, const int64_t* row_off, RowTable rt, int32_t* n_clusters, int32_t* big_list, int32_t* big_count,
-                      cudaStream_t st, cudaStream_t side, cudaEvent_t ev_fork, cudaEvent_t ev_join) {
+                      const RunScratch* rs, cudaStream_t st, cudaStream_t side, cudaEvent_t ev_fork, cudaEvent_t ev_join) {
     const int n = h1_end - h1_begin;
     if (n <= 0) return;
     const size_t smem = FORM_WARPS * 2 * FORM_CAND_CAP * sizeof(int32_t);
@@ -1218,31 +1550,46 @@ void launch_form_fill(const PassConst& pc, const double* x1, const double* y1, i
     int32_t* order = big_list;
     int32_t* cnts = big_count;
     static const int small_max = getenv("CVX_CL_SMALL_MAX") ? std::min(CL_N, std::max(1, atoi(getenv("CVX_CL_SMALL_MAX")))) : CL_N;
-    k_order_by_n<<<1, 1024, 0, st>>>(n_of, h1_begin, h1_end, pc.max_cluster, small_max, order, cnts);
+    k_order_by_n<<<1, 1024, 0, st>>>(n_of, h1_begin, h1_end, nullptr, pc.max_cluster, small_max, order, cnts);
     const size_t sm_q = CL_SMEM_QUANTUM, sm_huge = sizeof(ClusterSmB<CL_HUGE_N>);
     cudaFuncSetAttribute(k_cluster_classes, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sm_q));   // per device, cheap
     cudaFuncSetAttribute(k_cluster_coop<CL_HUGE_N, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sm_huge));
-    // the rare > 512-row edges (one 171 KB block per SM, or the global-memory fallback) run beside the rest on a side stream
+    // > CL_N-row edges: clustering by runs along the epipolar line (k_cluster_runs), then the per-edge kernels for whatever it left
+    // behind; all of it on a side stream beside the <= CL_N-row class.  CVX_CL_RUNS=0 restores the per-edge kernels for every class.
+    static const bool runs_on = !(getenv("CVX_CL_RUNS") && atoi(getenv("CVX_CL_RUNS")) == 0);
+    const bool use_runs = runs_on && rs != nullptr;
     cudaStream_t s_huge = side ? side : st;
-    // CVX_FORM_DEBUG=1: per-launch start / end times (stderr); a diagnostic, it synchronises the device
     static const bool dbg = getenv("CVX_FORM_DEBUG") != nullptr;
     cudaEvent_t de[4];
     if (dbg) for (auto& e : de) cudaEventCreate(&e);
     if (side) { cudaEventRecord(ev_fork, st); cudaStreamWaitEvent(side, ev_fork, 0); }
     if (dbg) cudaEventRecord(de[0], s_huge);
-    k_cluster_coop<CL_HUGE_N, 8><<<std::min(n, 148), 256, sm_huge, s_huge>>>(pc, order, cnts, 3, n_of, row_off, rt, n_clusters);
+    const int grid = std::min(n, (n + CL_SMALL_WARPS - 1) / CL_SMALL_WARPS + 148 * 4);
+    if (use_runs) {
+        cudaMemsetAsync(rs->ctr, 0, 4 * sizeof(int32_t), s_huge);
+        k_runs_prepare<<<std::min(n, 148 * 8), RUN_WARPS * 32, 0, s_huge>>>(pc, order, cnts, x1, y1, n_of, row_off, rt, n_clusters, *rs);
+        k_runs_cluster<<<148 * 8, RUN_WARPS * 32, 0, s_huge>>>(pc, row_off, rt, *rs);
+        // the long runs as virtual edges of the scratch table, through the per-edge kernels (count known on the device only)
+        cudaMemsetAsync(rs->v_order + rs->cap_long, 0, 8 * sizeof(int32_t), s_huge);
+        k_order_by_n<<<1, 1024, 0, s_huge>>>(rs->v_n, 0, rs->cap_long, rs->ctr, pc.max_cluster, small_max, rs->v_order, rs->v_order + rs->cap_long);
+        k_cluster_classes<<<148 * 4, CL_SMALL_WARPS * 32, sm_q, s_huge>>>(pc, rs->v_order, rs->v_order + rs->cap_long, rs->v_n, rs->v_off, rs->vrt, rs->v_ncl, 3);
+        k_cluster_coop<CL_HUGE_N, 8><<<148, 256, sm_huge, s_huge>>>(pc, rs->v_order, rs->v_order + rs->cap_long, 3, rs->v_n, rs->v_off, rs->vrt, rs->v_ncl, 0);
+        k_runs_scatter<<<148 * 4, RUN_WARPS * 32, 0, s_huge>>>(row_off, rt, *rs);
+        k_runs_finish<<<(n + RUN_WARPS - 1) / RUN_WARPS, RUN_WARPS * 32, 0, s_huge>>>(order, cnts, n_of, row_off, rt, n_clusters);
+        k_cluster_classes<<<std::min(n, 148 * 4), CL_SMALL_WARPS * 32, sm_q, s_huge>>>(pc, order, cnts, n_of, row_off, rt, n_clusters, 2);
+    }
+    k_cluster_coop<CL_HUGE_N, 8><<<std::min(n, 148), 256, sm_huge, s_huge>>>(pc, order, cnts, 3, n_of, row_off, rt, n_clusters, use_runs ? 1 : 0);
     k_cluster_huge<<<std::min(n, 148 * 4), 32, 0, s_huge>>>(pc, order, cnts, n_of, row_off, rt, n_clusters);
     if (dbg) { cudaEventRecord(de[1], s_huge); cudaEventRecord(de[2], st); }
     if (side) cudaEventRecord(ev_join, side);
     // one block per unit in the common case (units ~ n / 8 plus the few long edges); beyond that the blocks stride
-    const int grid = std::min(n, (n + CL_SMALL_WARPS - 1) / CL_SMALL_WARPS + 148 * 4);
-    k_cluster_classes<<<grid, CL_SMALL_WARPS * 32, sm_q, st>>>(pc, order, cnts, n_of, row_off, rt, n_clusters);
+    k_cluster_classes<<<grid, CL_SMALL_WARPS * 32, sm_q, st>>>(pc, order, cnts, n_of, row_off, rt, n_clusters, use_runs ? 1 : 3);
     if (dbg) {
         cudaEventRecord(de[3], st);
         cudaDeviceSynchronize();
         float t[4];
         for (int i = 0; i < 4; i++) cudaEventElapsedTime(&t[i], de[2], de[i]);
-        fprintf(stderr, "[form] relative to the k_cluster_classes launch: > 512-row classes %.3f..%.3f, <= 512-row classes 0..%.3f ms\n", t[0], t[1], t[3]);
+        fprintf(stderr, "[form] relative to the k_cluster_classes launch: > %d-row classes %.3f..%.3f, <= %d-row class 0..%.3f ms\n", CL_N, t[0], t[1], CL_N, t[3]);
         for (auto& e : de) cudaEventDestroy(e);
     }
     if (side) cudaStreamWaitEvent(st, ev_join, 0);

@@ -66,6 +66,18 @@ struct UniqTable {
 };
 
 
+// Scratch of the run-based clustering of the > 128-row edges (cvx_kernels.cu, "clustering by RUNS"): work lists of the short runs,
+// and a second hypothesis table into which the long runs are copied as virtual edges for the per-edge clustering kernels.
+struct RunScratch {
+    int4 *desc_long, *desc_short;      // (view-1 edge, scratch row offset | first sorted position, rows, 0)
+    int32_t* ctr;                      // [0] long runs, [1] short runs, [2] scratch rows used
+    int32_t cap_long; int64_t cap_rows;
+    RowTable vrt;                      // xc, yc, th, h2orig in; xbar, ybar, thbar, label, h2rep, urank out (thn / orient scratch)
+    int32_t *v_n, *v_ncl, *v_order;    // rows / cluster count / clustering order (+ 8 class counts) of the virtual edges
+    int64_t* v_off;                    // first scratch row of every virtual edge
+    int32_t* v_oi;                     // scratch row -> row within its edge
+};
+
 void launch_edge_trig(const double* th, double* cs, double* sn, int64_t n, cudaStream_t st);
 void launch_ingest_views(const double* sx, const double* sy, const double* st_, const int64_t* tab, int n_views, int64_t max_n, EdgeArena ea,
                          cudaStream_t st);
@@ -106,7 +118,7 @@ void launch_form_count(const PassConst& pc, const double* x1, const double* y1, 
 void launch_form_fill(const PassConst& pc, const double* x1, const double* y1, int h1_begin, int h1_end, const double2* wedge_h1,
                       const double* x2, const double* y2, const double* th2, const double* ang2, int E2, AngleIndex ix, const int32_t* m_of,
                       const int32_t* n_of, const int64_t* row_off, RowTable rt, int32_t* n_clusters, int32_t* big_list, int32_t* big_count,
-                      cudaStream_t st, cudaStream_t side, cudaEvent_t ev_fork, cudaEvent_t ev_join);
+                      const RunScratch* rs, cudaStream_t st, cudaStream_t side, cudaEvent_t ev_fork, cudaEvent_t ev_join);
 // unique-hypothesis table from the clustered rows (+ view-independent reprojection terms)
 void launch_uniq_fill(const PassConst& pc, const double* x1, const double* y1, const double* th1, RowTable rt, int64_t H,
                       const int64_t* row_off, const int64_t* u_off, UniqTable ut, cudaStream_t st);

@@ -12,6 +12,8 @@ data = importlib.import_module("3d_curvix_b200.data")
 
 name = sys.argv[1] if len(sys.argv) > 1 else "cfg4"
 w = data.workload(name)
+if len(sys.argv) > 2:
+    w["pairs"] = [tuple(int(t) for t in sys.argv[2].split(","))]
 t0 = time.time()
 scene = data.make_synthetic_scene(**w["scene"])
 print("scene built in %.1f s" % (time.time() - t0), flush=True)
