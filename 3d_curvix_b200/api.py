@@ -18,7 +18,7 @@ SYMBOLS = [
     "cvx_get_pairs", "cvx_get_reference_order", "cvx_finalize", "cvx_get_device_results", "cvx_get_timings", "cvx_synchronize", "cvx_get_stream",
     "cvx_claims_reset", "cvx_claims_accumulate", "cvx_claims_get_counts", "cvx_claims_get_mask", "cvx_claims_allreduce",
     "cvx_split_h1_by_rows", "cvx_comm_unique_id", "cvx_comm_init", "cvx_comm_attach", "cvx_comm_destroy", "cvx_gather_reset",
-    "cvx_gather_post", "cvx_gather_wait", "cvx_gather_get", "cvx_gather_fetch", "cvx_gather_stats",
+    "cvx_gather_post", "cvx_gather_wait", "cvx_gather_get", "cvx_gather_fetch", "cvx_gather_fetch_async", "cvx_gather_stats",
     "cvx_support_problem_create", "cvx_support_problem_run", "cvx_support_problem_stats", "cvx_support_problem_result",
     "cvx_support_problem_destroy",
 ]
@@ -63,7 +63,8 @@ class CvxDeviceResults(C.Structure):
 
 class CvxGatheredUnit(C.Structure):
     _fields_ = [("meta", C.c_int64 * 8), ("pair_h1", C.c_void_p), ("pair_h2rep", C.c_void_p), ("pair_count", C.c_void_p), ("nan_flag", C.c_void_p),
-                ("pair_supports", C.c_void_p), ("gamma_world", C.c_void_p), ("tangent_world", C.c_void_p), ("gamma_cam", C.c_void_p)]
+                ("support_off", C.c_void_p), ("support_entries", C.c_void_p), ("gamma_world", C.c_void_p), ("tangent_world", C.c_void_p),
+                ("gamma_cam", C.c_void_p)]
 
 
 _lib = None
@@ -91,7 +92,8 @@ def load():
     lib.cvx_gather_post.argtypes = [C.c_void_p, C.c_int64, C.c_int]
     lib.cvx_gather_wait.argtypes = [C.c_void_p, C.c_int, C.c_int]
     lib.cvx_gather_get.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(CvxGatheredUnit)]
-    lib.cvx_gather_fetch.argtypes = [C.c_void_p, C.c_int, C.c_int] + [C.c_void_p] * 8
+    lib.cvx_gather_fetch.argtypes = [C.c_void_p, C.c_int, C.c_int] + [C.c_void_p] * 9
+    lib.cvx_gather_fetch_async.argtypes = [C.c_void_p, C.c_int, C.c_int] + [C.c_void_p] * 9
     lib.cvx_comm_init.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
     lib.cvx_comm_attach.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int]
     lib.cvx_split_h1_by_rows.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
@@ -335,29 +337,43 @@ class EdgeSketch:
         self._ck(self.lib.cvx_gather_get(self.h, rnd, rank, C.byref(u)))
         return u
 
+    GATHER_FIELDS = ("h1", "h2rep", "count", "nan_flag", "support_off", "support_entries", "gamma_world", "tangent_world", "gamma_cam")
+
+    @staticmethod
+    def gather_widths(P, S):
+        """bytes of every field of a gathered unit with P rows and S supports"""
+        return dict(h1=4 * P, h2rep=4 * P, count=4 * P, nan_flag=4 * P, support_off=8 * (P + 1), support_entries=8 * S, gamma_world=24 * P,
+                    tangent_world=24 * P, gamma_cam=24 * P)
+
     def gather_fetch(self, rnd, rank):
-        """Host copies of what `rank` contributed in round `rnd` (rank 0 only)."""
+        """Host copies of what `rank` contributed in round `rnd` (rank 0 only).  `supports` is the CSR list expanded to the reference's
+        dense P x V layout (-2 = no support)."""
         u = self.gather_get(rnd, rank)
-        P, V = int(u.meta[0]), int(u.meta[6])
+        P, V, S = int(u.meta[0]), int(u.meta[6]), int(u.meta[7])
         out = dict(meta=[int(x) for x in u.meta], h1=np.empty(P, np.int32), h2rep=np.empty(P, np.int32), count=np.empty(P, np.int32),
-                   nan_flag=np.empty(P, np.int32), supports=np.empty((P, V), np.int32), gamma_world=np.empty((P, 3)),
-                   tangent_world=np.empty((P, 3)), gamma_cam=np.empty((P, 3)))
+                   nan_flag=np.empty(P, np.int32), support_off=np.zeros(P + 1, np.int64), support_entries=np.empty((S, 2), np.int32),
+                   gamma_world=np.empty((P, 3)), tangent_world=np.empty((P, 3)), gamma_cam=np.empty((P, 3)))
         if P:
-            self._ck(self.lib.cvx_gather_fetch(self.h, rnd, rank, *[_vp(out[k]) for k in ("h1", "h2rep", "count", "nan_flag", "supports", "gamma_world",
-                                                                                         "tangent_world", "gamma_cam")]))
+            self._ck(self.lib.cvx_gather_fetch(self.h, rnd, rank, *[_vp(out[k]) for k in self.GATHER_FIELDS]))
+        dense = np.full((P, V), -2, np.int32)
+        if S:
+            rows = np.repeat(np.arange(P), np.diff(out["support_off"]))
+            dense[rows, out["support_entries"][:, 0]] = out["support_entries"][:, 1]
+        out["supports"] = dense
         return out
 
-    def gather_fetch_into(self, rnd, rank, ptrs):
-        """Same, into caller-owned host buffers (raw pointers, e.g. pinned memory): ptrs = dict with any of h1, h2rep, count, nan_flag,
-        supports, gamma_world, tangent_world, gamma_cam.  Returns the number of bytes copied."""
+    def gather_fetch_into(self, rnd, rank, ptrs, wait=True):
+        """Same fields (supports as the CSR list), into caller-owned host buffers (raw pointers, e.g. pinned memory): ptrs = dict with any
+        of GATHER_FIELDS.  wait=False: enqueued behind the round's transfers, completed by gather_wait(host_sync=True).  Returns the
+        number of bytes copied."""
         u = self.gather_get(rnd, rank)
-        P, V = int(u.meta[0]), int(u.meta[6])
+        P, S = int(u.meta[0]), int(u.meta[7])
         if P == 0:
             return 0
-        order = ("h1", "h2rep", "count", "nan_flag", "supports", "gamma_world", "tangent_world", "gamma_cam")
-        width = dict(h1=4, h2rep=4, count=4, nan_flag=4, supports=4 * V, gamma_world=24, tangent_world=24, gamma_cam=24)
-        self._ck(self.lib.cvx_gather_fetch(self.h, rnd, rank, *[C.c_void_p(ptrs[k]) if ptrs.get(k) else None for k in order]))
-        return sum(P * width[k] for k in order if ptrs.get(k))
+        width = self.gather_widths(P, S)
+        fn = self.lib.cvx_gather_fetch if wait else self.lib.cvx_gather_fetch_async
+        self._ck(fn(self.h, rnd, rank, *[C.c_void_p(ptrs[k]) if ptrs.get(k) else None for k in self.GATHER_FIELDS]))
+        return sum(width[k] for k in self.GATHER_FIELDS if ptrs.get(k))
 
     def gather_stats(self):
         a, b, ms = C.c_int64(), C.c_int64(), C.c_float()

@@ -19,6 +19,7 @@
 #include <vector>
 
 #include "cvx_internal.h"
+#include "cvx_kernels.cuh"
 
 namespace {
 
@@ -60,25 +61,46 @@ NcclApi* nccl_api() {
     return &api;
 }
 
-constexpr int META = 8;          // int64 per rank and round: {P, view1, view2, h1_begin, h1_end, unit_id, V, 0}
+constexpr int META = 8;          // int64 per rank and round: {P, view1, view2, h1_begin, h1_end, unit_id, V, S = supporting edges of all rows}
 constexpr int SLOTS = 2;         // staging buffers in flight
 
 inline size_t align16(size_t x) { return (x + 15) & ~size_t(15); }
-// byte offsets of the fields of a packed unit with P rows and V validation views
-struct Layout { size_t h1, h2, cnt, nan, sup, gw, tw, gc, total; };
-Layout layout_of(int64_t P, int V) {
+// Byte offsets of the fields of a packed unit with P rows and S supports.  The support indices travel as a CSR list (row r owns
+// entries [sup_off[r], sup_off[r+1]), each {validation view slot, edge index}, ascending slot): a row is supported by ~10 of ~100
+// views, so the dense P x V matrix of the reference's paired_edge (EdgeSketch_Core.cpp:510-526) would be ~4x the bytes.
+struct Layout { size_t h1, h2, cnt, nan, gw, tw, gc, soff, sent, total; };
+Layout layout_of(int64_t P, int64_t S) {
     Layout l;
     size_t o = 0;
     l.h1 = o; o = align16(o + size_t(P) * 4);
     l.h2 = o; o = align16(o + size_t(P) * 4);
     l.cnt = o; o = align16(o + size_t(P) * 4);
     l.nan = o; o = align16(o + size_t(P) * 4);
-    l.sup = o; o = align16(o + size_t(P) * size_t(V) * 4);
     l.gw = o; o = align16(o + size_t(P) * 24);
     l.tw = o; o = align16(o + size_t(P) * 24);
     l.gc = o; o = align16(o + size_t(P) * 24);
+    l.soff = o; o = align16(o + size_t(P + 1) * 8);
+    l.sent = o; o = align16(o + size_t(S) * 8);
     l.total = o;
     return l;
+}
+// one warp per accepted row: the non-empty entries of its dense support row, in view order
+__global__ void __launch_bounds__(256) k_pack_supports(const int32_t* __restrict__ sup, int64_t P, int V, const int64_t* __restrict__ off,
+                                                       int2* __restrict__ ent) {
+    const int lane = threadIdx.x & 31;
+    const int64_t p = blockIdx.x * int64_t(blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (p >= P) return;
+    int64_t o = off[p];
+    for (int v0 = 0; v0 < V; v0 += 32) {
+        const int v = v0 + lane;
+        const int e = v < V ? sup[p * V + v] : -2;
+        const unsigned m = __ballot_sync(0xffffffffu, e != -2);
+        if (e != -2) ent[o + __popc(m & ((1u << lane) - 1u))] = make_int2(v, e);
+        o += __popc(m);
+    }
+}
+__global__ void k_write_meta(int64_t* meta, int64_t P, int v1, int v2, int rb, int re, int64_t unit, int V, const int64_t* S) {
+    meta[0] = P; meta[1] = v1; meta[2] = v2; meta[3] = rb; meta[4] = re; meta[5] = unit; meta[6] = V; meta[7] = (P > 0 && S) ? *S : 0;
 }
 
 struct Round {
@@ -175,23 +197,24 @@ int post_round(cvx_ctx* ctx, CvxCommState* s, NcclApi* api, size_t r) {
     if (s->rank == 0) {
         R.base.assign(size_t(s->world), nullptr);
         for (int q = 0; q < s->world; q++) {
-            const Layout l = layout_of(m[q * META], int(m[q * META + 6]));
+            const Layout l = layout_of(m[q * META], m[q * META + 7]);
             if (m[q * META] > 0) { R.base[size_t(q)] = arena_take(ctx, s, l.total); if (!R.base[size_t(q)]) return CVX_ERR_NOMEM; }
         }
         NCC(api->GroupStart());
         for (int q = 1; q < s->world; q++)
             if (m[q * META] > 0) {
-                const size_t b = layout_of(m[q * META], int(m[q * META + 6])).total;
+                const size_t b = layout_of(m[q * META], m[q * META + 7]).total;
                 NCC(api->Recv(R.base[size_t(q)], b, ncclChar, q, s->comm, s->cs));
                 s->bytes_recv += int64_t(b);
             }
         NCC(api->GroupEnd());
-        if (m[0] > 0) CUC(cudaMemcpyAsync(R.base[0], s->stage[k], s->stage_bytes[k], cudaMemcpyDeviceToDevice, s->cs));
+        if (m[0] > 0) CUC(cudaMemcpyAsync(R.base[0], s->stage[k], layout_of(m[0], m[7]).total, cudaMemcpyDeviceToDevice, s->cs));
     } else if (m[s->rank * META] > 0) {
+        const size_t b = layout_of(m[s->rank * META], m[s->rank * META + 7]).total;   // exact: the support count came back with the meta
         NCC(api->GroupStart());
-        NCC(api->Send(s->stage[k], s->stage_bytes[k], ncclChar, 0, s->comm, s->cs));
+        NCC(api->Send(s->stage[k], b, ncclChar, 0, s->comm, s->cs));
         NCC(api->GroupEnd());
-        s->bytes_sent += int64_t(s->stage_bytes[k]);
+        s->bytes_sent += int64_t(b);
     }
     CUC(cudaEventRecord(s->ev_sent[k], s->cs));
     R.posted = true;
@@ -295,7 +318,8 @@ int cvx_gather_post(cvx_ctx* ctx, int64_t unit_id, int empty) {
     int dev;
     cvx_internal_device(ctx, &dev, &main_stream);
     if (!empty) { const int rc = cvx_internal_results(ctx, &v); if (rc) return rc; }
-    const Layout l = layout_of(v.P, v.V);
+    const Layout l = layout_of(v.P, v.P * int64_t(v.V));          // capacity: every support slot taken
+    int64_t* d_S = nullptr;
     if (v.P > 0) {
         if (l.total > s->stage_cap[k]) {
             if (s->stage[k]) CUC(cudaFree(s->stage[k]));
@@ -310,18 +334,22 @@ int cvx_gather_post(cvx_ctx* ctx, int64_t unit_id, int empty) {
         CUC(cudaMemcpyAsync(b + l.h2, v.h2rep, P * 4, cudaMemcpyDeviceToDevice, main_stream));
         CUC(cudaMemcpyAsync(b + l.cnt, v.count, P * 4, cudaMemcpyDeviceToDevice, main_stream));
         CUC(cudaMemcpyAsync(b + l.nan, v.nan, P * 4, cudaMemcpyDeviceToDevice, main_stream));
-        CUC(cudaMemcpyAsync(b + l.sup, v.sup, P * size_t(v.V) * 4, cudaMemcpyDeviceToDevice, main_stream));
         CUC(cudaMemcpyAsync(b + l.gw, v.gw, P * 24, cudaMemcpyDeviceToDevice, main_stream));
         CUC(cudaMemcpyAsync(b + l.tw, v.tw, P * 24, cudaMemcpyDeviceToDevice, main_stream));
         CUC(cudaMemcpyAsync(b + l.gc, v.gc, P * 24, cudaMemcpyDeviceToDevice, main_stream));
+        // supports as a CSR list: offsets = exclusive scan of the per-row support counts (the vote of EdgeSketch_Core.cpp:414-427)
+        int64_t* off = reinterpret_cast<int64_t*>(b + l.soff);
+        cvx::launch_scan_i32_i64(v.count, off, int(v.P), main_stream);
+        k_pack_supports<<<unsigned((v.P + 7) / 8), 256, 0, main_stream>>>(v.sup, v.P, v.V, off, reinterpret_cast<int2*>(b + l.sent));
+        cvx_internal_count_launch(ctx, 2);
+        d_S = off + v.P;
     }
-    s->stage_bytes[k] = v.P > 0 ? l.total : 0;
+    // the 64-byte record of this rank (the support count is only known on the device), all-gathered
+    k_write_meta<<<1, 1, 0, main_stream>>>(s->d_meta_send + k * META, v.P, v.view1, v.view2, v.run_begin, v.run_end, unit_id, v.V, d_S);
+    CUC(cudaGetLastError());
     CUC(cudaEventRecord(s->ev_packed[k], main_stream));
     CUC(cudaStreamWaitEvent(s->cs, s->ev_packed[k], 0));
     if (!s->timing_open) { CUC(cudaEventRecord(s->ev_t0, s->cs)); s->timing_open = true; }
-    // the 64-byte record of this rank, all-gathered
-    int64_t* hm = s->h_meta_send + k * META;
-    hm[0] = v.P; hm[1] = v.view1; hm[2] = v.view2; hm[3] = v.run_begin; hm[4] = v.run_end; hm[5] = unit_id; hm[6] = v.V; hm[7] = 0;
     if (r == s->rounds.size()) {
         Round N;
         CUC(cudaEventCreateWithFlags(&N.ev_meta, cudaEventDisableTiming));
@@ -331,7 +359,6 @@ int cvx_gather_post(cvx_ctx* ctx, int64_t unit_id, int empty) {
     Round& R = s->rounds[r];
     R.slot = k; R.posted = false;
     int64_t* d_all = s->d_meta_all + size_t(k) * s->world * META;
-    CUC(cudaMemcpyAsync(s->d_meta_send + k * META, hm, META * 8, cudaMemcpyHostToDevice, s->cs));
     NCC(api->AllGather(s->d_meta_send + k * META, d_all, META, ncclInt64, s->comm, s->cs));
     CUC(cudaMemcpyAsync(R.h_meta, d_all, size_t(s->world) * META * 8, cudaMemcpyDeviceToHost, s->cs));
     CUC(cudaEventRecord(R.ev_meta, s->cs));
@@ -366,32 +393,40 @@ int cvx_gather_get(cvx_ctx* ctx, int round, int rank, cvx_gathered_unit* out) {
     std::memcpy(out->meta, R.h_meta + rank * META, META * 8);
     const int64_t P = out->meta[0];
     if (P <= 0) return CVX_OK;
-    const Layout l = layout_of(P, int(out->meta[6]));
+    const Layout l = layout_of(P, out->meta[7]);
     const char* b = R.base[size_t(rank)];
     out->pair_h1 = reinterpret_cast<const int32_t*>(b + l.h1); out->pair_h2rep = reinterpret_cast<const int32_t*>(b + l.h2);
     out->pair_count = reinterpret_cast<const int32_t*>(b + l.cnt); out->nan_flag = reinterpret_cast<const int32_t*>(b + l.nan);
-    out->pair_supports = reinterpret_cast<const int32_t*>(b + l.sup);
+    out->support_off = reinterpret_cast<const int64_t*>(b + l.soff); out->support_entries = reinterpret_cast<const int32_t*>(b + l.sent);
     out->gamma_world = reinterpret_cast<const double*>(b + l.gw); out->tangent_world = reinterpret_cast<const double*>(b + l.tw);
     out->gamma_cam = reinterpret_cast<const double*>(b + l.gc);
     return CVX_OK;
 }
 
-int cvx_gather_fetch(cvx_ctx* ctx, int round, int rank, int32_t* h1, int32_t* h2rep, int32_t* count, int32_t* nan_flag, int32_t* supports,
-                     double* gamma_world, double* tangent_world, double* gamma_cam) {
+static int gather_fetch_impl(cvx_ctx* ctx, int round, int rank, int32_t* h1, int32_t* h2rep, int32_t* count, int32_t* nan_flag, int64_t* support_off,
+                             int32_t* support_entries, double* gamma_world, double* tangent_world, double* gamma_cam, bool wait) {
     cvx_gathered_unit u;
     const int rc = cvx_gather_get(ctx, round, rank, &u);
     if (rc) return rc;
     CvxCommState* s = state_of(ctx);
-    const size_t P = size_t(u.meta[0]), V = size_t(u.meta[6]);
+    const size_t P = size_t(u.meta[0]), S = size_t(u.meta[7]);
     if (P == 0) return CVX_OK;
     CUC(cudaSetDevice(s->device));
 #define CVX_FETCH(dst, src, bytes) if (dst) CUC(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, s->cs))
     CVX_FETCH(h1, u.pair_h1, P * 4); CVX_FETCH(h2rep, u.pair_h2rep, P * 4); CVX_FETCH(count, u.pair_count, P * 4); CVX_FETCH(nan_flag, u.nan_flag, P * 4);
-    CVX_FETCH(supports, u.pair_supports, P * V * 4);
+    CVX_FETCH(support_off, u.support_off, (P + 1) * 8); CVX_FETCH(support_entries, u.support_entries, S * 8);
     CVX_FETCH(gamma_world, u.gamma_world, P * 24); CVX_FETCH(tangent_world, u.tangent_world, P * 24); CVX_FETCH(gamma_cam, u.gamma_cam, P * 24);
 #undef CVX_FETCH
-    CUC(cudaStreamSynchronize(s->cs));
+    if (wait) CUC(cudaStreamSynchronize(s->cs));
     return CVX_OK;
+}
+int cvx_gather_fetch(cvx_ctx* ctx, int round, int rank, int32_t* h1, int32_t* h2rep, int32_t* count, int32_t* nan_flag, int64_t* support_off,
+                     int32_t* support_entries, double* gamma_world, double* tangent_world, double* gamma_cam) {
+    return gather_fetch_impl(ctx, round, rank, h1, h2rep, count, nan_flag, support_off, support_entries, gamma_world, tangent_world, gamma_cam, true);
+}
+int cvx_gather_fetch_async(cvx_ctx* ctx, int round, int rank, int32_t* h1, int32_t* h2rep, int32_t* count, int32_t* nan_flag, int64_t* support_off,
+                           int32_t* support_entries, double* gamma_world, double* tangent_world, double* gamma_cam) {
+    return gather_fetch_impl(ctx, round, rank, h1, h2rep, count, nan_flag, support_off, support_entries, gamma_world, tangent_world, gamma_cam, false);
 }
 
 int cvx_gather_stats(cvx_ctx* ctx, int64_t* bytes_sent, int64_t* bytes_received, float* comm_ms) {

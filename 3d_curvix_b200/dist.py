@@ -24,6 +24,32 @@ def shard_pairs(pairs, rank, world):
     return [p for i, p in enumerate(pairs) if i % world == rank]
 
 
+def lpt_assign(costs, world):
+    """Longest-processing-time-first: units by decreasing cost, each to the least loaded rank.  -> (unit lists per rank, loads)."""
+    order = sorted(range(len(costs)), key=lambda i: (-costs[i], i))
+    load = [0.0] * world
+    out = [[] for _ in range(world)]
+    for i in order:
+        r = min(range(world), key=lambda q: (load[q], q))
+        out[r].append(i)
+        load[r] += costs[i]
+    return out, load
+
+
+def plan_units(costs, pair_of, world):
+    """Static plan of a fixed schedule cut into units (a hypothesis view pair, or a view-1 range of one): LPT over the measured unit
+    costs, then inside every rank the units of one pair made adjacent (the pair is staged once), pairs by decreasing cost of their
+    heaviest unit.  Every rank computes the same plan from the same inputs.  -> (unit lists per rank, planned loads)."""
+    assign, load = lpt_assign(costs, world)
+    out = []
+    for a in assign:
+        heaviest = {}
+        for i in a:
+            heaviest[pair_of[i]] = max(heaviest.get(pair_of[i], 0.0), costs[i])
+        out.append(sorted(a, key=lambda i: (-heaviest[pair_of[i]], pair_of[i], i)))
+    return out, load
+
+
 class _DevArray:
     """Exposes a raw device pointer of the C-ABI (cvx_get_device_results) through __cuda_array_interface__."""
 

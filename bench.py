@@ -54,7 +54,7 @@ def parse():
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="target time of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extras", action="store_true", help="skip secondary / roofline_support_test / sec_per_object")
-    ap.add_argument("--parts", type=int, default=0, help="view-1 ranges per pair (0 = 1 at N <= 4, 2 at N = 8)")
+    ap.add_argument("--parts", type=int, default=0, help="view-1 ranges per pair (0 = whole pairs while there are two per rank)")
     ap.add_argument("--shard", default="pairs", choices=["pairs", "h1"], help="h1: every pair sharded by view-1 range over all ranks")
     ap.add_argument("--pair", default="", help="cfg2 secondary / single-pair runs: hypothesis view pair a,b")
     ap.add_argument("--cfg5-views", type=int, default=0, help="cfg5: number of validation views (default 200; 40 inside the default line)")
@@ -308,15 +308,7 @@ def algorithmic_bytes_fused(c, edges_vali):
 
 
 def lpt_assign(costs, world):
-    """Longest-processing-time-first: units sorted by decreasing cost, each to the least loaded rank.  -> list of unit-index lists."""
-    order = sorted(range(len(costs)), key=lambda i: -costs[i])
-    load = [0.0] * world
-    out = [[] for _ in range(world)]
-    for i in order:
-        r = min(range(world), key=lambda q: (load[q], q))
-        out[r].append(i)
-        load[r] += costs[i]
-    return out, load
+    return pkg("dist").lpt_assign(costs, world)
 
 
 def ncu_notes(kernel):
@@ -350,9 +342,31 @@ class HostBuffers:
         self.spec = {"h1": (1, 4), "h2rep": (1, 4), "count": (1, 4), "supports": (V, 4), "gamma_cam": (3, 8), "gamma_world": (3, 8),
                      "tangent_world": (3, 8), "nan_flag": (1, 4)}
         self.cap, self.buf = 0, {}
+        self.arenas, self.chunk, self.arena_off, self.arena_bytes = [], 0, 0, 1 << 20
 
     def upload(self, g):
         g.set_all_view_edges_ptr(self.n_per_view, self.pinned[0].data_ptr(), self.pinned[1].data_ptr(), self.pinned[2].data_ptr())
+
+    def arena_reset(self):
+        self.chunk, self.arena_off = 0, 0
+
+    def arena_ptrs(self, widths):
+        """Room for one more unit (field -> bytes) in a growing list of pinned chunks: the asynchronous fetches of a whole step stay in
+        flight together, so nothing is reused before arena_reset."""
+        need = sum(((b + 255) // 256) * 256 for b in widths.values())
+        while True:
+            if self.chunk == len(self.arenas):
+                self.arenas.append(self.torch.empty(max(need, self.arena_bytes if not self.arenas else self.arena_bytes // 4), dtype=self.torch.uint8).pin_memory())
+            if self.arena_off + need <= self.arenas[self.chunk].numel():
+                break
+            self.chunk += 1
+            self.arena_off = 0
+        base, ptrs = self.arenas[self.chunk].data_ptr() + self.arena_off, {}
+        for k, b in widths.items():
+            ptrs[k] = base
+            base += ((b + 255) // 256) * 256
+        self.arena_off += need
+        return ptrs
 
     def out_ptrs(self, P):
         if P > self.cap:
@@ -399,7 +413,8 @@ def run_schedule(args, rank, world, local_rank):
     if args.shard == "h1":
         S = world
     else:
-        S = args.parts if args.parts > 0 else (2 if world >= 8 and len(pairs) < 4 * world else 1)
+        # whole pairs while there are at least two per rank (splitting a pair costs ~8 % in launch tails: profiles/r02g); finer otherwise
+        S = args.parts if args.parts > 0 else max(1, -(-2 * world // len(pairs)))
     units = [dict(id=i * S + k, pair=p, part=k) for i, p in enumerate(pairs) for k in range(S)]
     bounds_of = {}
     if args.shard == "h1":
@@ -421,11 +436,24 @@ def run_schedule(args, rank, world, local_rank):
             g.run()
         return g.device_results()                    # runs the finalize kernel; results stay on the device
 
+    def fetch_rounds(r0, r1, to_host):
+        """Rank 0 hands the gathered units of rounds [r0, r1) to the host consumer: asynchronous copies into the pinned arena."""
+        n = 0
+        for r in range(r0, r1):
+            for q in range(world):
+                u = g.gather_get(r, q)
+                if int(u.meta[0]):
+                    n += g.gather_fetch_into(r, q, to_host.arena_ptrs(g.gather_widths(int(u.meta[0]), int(u.meta[7]))), wait=False)
+        return n
+
     def step(mine, rounds, measure=None, to_host=None):
         """One pass over this rank's units (+ the gather rounds).  measure: dict unit id -> (ms, counts, phases); to_host: HostBuffers."""
         d2h = 0
+        fetched = [0]
         if use_dist:
             g.gather_reset()
+            if to_host is not None:
+                to_host.arena_reset()
         for r in range(rounds):
             if r < len(mine):
                 u = units[mine[r]]
@@ -434,22 +462,21 @@ def run_schedule(args, rank, world, local_rank):
                     tm = g.timings()
                     measure[u["id"]] = (tm["set_pair_ms"] + tm["run_ms"] + tm["finalize_ms"], g.counts(), tm)
                 if use_dist:
-                    g.gather_post(u["id"])
+                    g.gather_post(u["id"])            # also hands round r - 1 to NCCL
                 elif to_host is not None:
                     ptrs, nbytes = to_host.out_ptrs(int(res.n_pairs))
                     g.results_into(ptrs)              # accepted pairs, supports, 3-D edges, tangents -> pinned host buffers
                     d2h += nbytes
             elif use_dist:
                 g.gather_post(empty=True)
+            if use_dist and to_host is not None and rank == 0 and r >= 1:
+                d2h += fetch_rounds(fetched[0], r, to_host)   # rounds < r: device -> pinned host behind their transfers, not waited for
+                fetched[0] = r
         if use_dist:
+            if to_host is not None and rank == 0:     # the last round(s) still on the device
+                g.gather_wait(join_stream=True, host_sync=False)
+                d2h += fetch_rounds(fetched[0], rounds, to_host)
             g.gather_wait(join_stream=True, host_sync=to_host is not None)
-            if to_host is not None and rank == 0:     # rank 0 hands every gathered unit to the host consumer
-                for r in range(rounds):
-                    for q in range(world):
-                        P = int(g.gather_get(r, q).meta[0])
-                        if P:
-                            ptrs, _ = to_host.out_ptrs(P)
-                            d2h += g.gather_fetch_into(r, q, ptrs)
         return d2h
 
     def barrier():
@@ -461,28 +488,31 @@ def run_schedule(args, rank, world, local_rank):
         return max(len(x) for x in a)
 
     with torch.cuda.stream(stream):
-        # ---- warm-up 1: every unit measured on the rank it was dealt to; then longest-first assignment from the measured times
-        meas = {}
+        # ---- warm-up: one cold pass (allocations), then every unit measured on the rank it was dealt to; longest-first assignment
+        # from the measured times; the remaining warm-up passes run the final assignment
         state["pair"] = None
+        step(assign[rank], rounds_of(assign))
+        barrier()
+        meas = {}
         step(assign[rank], rounds_of(assign), measure=meas)
         barrier()
+        mine_meas = {k: (v[0], v[1]["n_validations"], v[1]["n_pairs"]) for k, v in meas.items()}
         if use_dist:
             allm = [None] * world
-            tdist.all_gather_object(allm, {k: (v[0], v[1]["n_validations"]) for k, v in meas.items()})
-            cost = {k: v[0] for m in allm for k, v in m.items()}
-            vals_of = {k: v[1] for m in allm for k, v in m.items()}
+            tdist.all_gather_object(allm, mine_meas)
         else:
-            cost = {k: v[0] for k, v in meas.items()}
-            vals_of = {k: v[1]["n_validations"] for k, v in meas.items()}
+            allm = [mine_meas]
+        cost = {k: v[0] for m in allm for k, v in m.items()}
+        vals_of = {k: v[1] for m in allm for k, v in m.items()}
+        # pinned arena of the e2e leg at N > 1: 100 B per accepted row + its supports as a CSR list (at most the dense V x 8 B)
+        host.arena_bytes = int(sum(v[2] * (100 + 8 * min(V, 24)) + 4096 for m in allm for v in m.values())) + (1 << 20)
         if use_dist and args.shard == "pairs":
-            assign, load = lpt_assign([cost[u["id"]] for u in units], world)
-            for a in assign:                          # same-pair units adjacent (one staging), longest pair first
-                a.sort(key=lambda i: (-max(cost[j] for j in a if units[j]["pair"] == units[i]["pair"]), units[i]["pair"], units[i]["part"]))
+            assign, load = pkg("dist").plan_units([cost[u["id"]] for u in units], [u["pair"] for u in units], world)
         else:
             load = [sum(cost[i] for i in a) for a in assign]
         mine, rounds = assign[rank], rounds_of(assign)
         vals_all = int(sum(vals_of.values()))
-        for _ in range(max(args.warmup, 3) - 1):
+        for _ in range(max(args.warmup, 3) - 2):
             flush.zero_()
             step(mine, rounds)
         barrier()

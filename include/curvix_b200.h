@@ -195,16 +195,25 @@ int cvx_gather_post(cvx_ctx* ctx, int64_t unit_id, int empty);
  * recorded on it afterwards times them); with host_sync != 0 the call also blocks until they are done. */
 int cvx_gather_wait(cvx_ctx* ctx, int join_stream, int host_sync);
 /* Rank 0, after cvx_gather_wait: what `rank` contributed in `round`.  Device pointers into the receive arena, valid until the next
- * cvx_gather_reset.  meta: {n_pairs, view1, view2, h1_begin, h1_end, unit_id, n_vali_views, 0}. */
+ * cvx_gather_reset.  meta: {n_pairs, view1, view2, h1_begin, h1_end, unit_id, n_vali_views, n_supports}.
+ * The supporting edges of the accepted rows (columns 2.. of the reference's paired_edge, EdgeSketch_Core.cpp:510-526) travel as a CSR
+ * list: row r owns entries [support_off[r], support_off[r+1]), each entry two int32 {validation-view slot, edge index in that view},
+ * ascending slot; a slot without an entry is the reference's -2.  (A row is supported by ~10 % of the views: a quarter of the bytes.) */
 typedef struct cvx_gathered_unit {
     int64_t meta[8];
-    const int32_t* pair_h1; const int32_t* pair_h2rep; const int32_t* pair_count; const int32_t* nan_flag; const int32_t* pair_supports;
+    const int32_t* pair_h1; const int32_t* pair_h2rep; const int32_t* pair_count; const int32_t* nan_flag;
+    const int64_t* support_off; const int32_t* support_entries;
     const double* gamma_world; const double* tangent_world; const double* gamma_cam;
 } cvx_gathered_unit;
 int cvx_gather_get(cvx_ctx* ctx, int round, int rank, cvx_gathered_unit* out);
-/* Host copies of a gathered unit (any pointer may be NULL); synchronises. */
-int cvx_gather_fetch(cvx_ctx* ctx, int round, int rank, int32_t* h1, int32_t* h2rep, int32_t* count, int32_t* nan_flag, int32_t* supports,
-                     double* gamma_world, double* tangent_world, double* gamma_cam);
+/* Host copies of a gathered unit (any pointer may be NULL; support_off n_pairs + 1 entries, support_entries 2 * n_supports); synchronises. */
+int cvx_gather_fetch(cvx_ctx* ctx, int round, int rank, int32_t* h1, int32_t* h2rep, int32_t* count, int32_t* nan_flag, int64_t* support_off,
+                     int32_t* support_entries, double* gamma_world, double* tangent_world, double* gamma_cam);
+/* Same copies, enqueued on the gather's side stream behind the transfers of `round` and not waited for: the round must have been
+ * handed to NCCL (any later cvx_gather_post or cvx_gather_wait did that); pinned destinations then fill while the context computes
+ * its next unit.  cvx_gather_wait(ctx, x, 1) completes them. */
+int cvx_gather_fetch_async(cvx_ctx* ctx, int round, int rank, int32_t* h1, int32_t* h2rep, int32_t* count, int32_t* nan_flag, int64_t* support_off,
+                           int32_t* support_entries, double* gamma_world, double* tangent_world, double* gamma_cam);
 /* Bitwise OR of the claimed-edge bitmaps of all ranks into every rank (ncclAllReduce is not defined for OR: the words are gathered
  * and OR-ed), so that cvx_claims_get_counts / next-view selection see the claims of the whole pass when a pair was sharded by
  * view-1 range.  Collective. */

@@ -73,3 +73,29 @@ def test_gather_two_ranks_matches_unsharded(oracle_mod, tiny_scene, tmp_path):
     assert g["counts"].sum() == len(pf["h1"]) and (g["counts"] > 0).all()
     assert np.array_equal(g["h1"], pf["h1"]) and np.array_equal(g["h2"], pf["h2rep"]) and np.array_equal(g["sup"], pf["supports"])
     assert np.array_equal(g["gw"], ff["gamma_world"]) and np.array_equal(g["tw"], ff["tangent_world"])
+
+
+def test_unit_plan_is_balanced_and_deterministic():
+    """LPT over measured unit costs (bench.py --gpus N, curvix_main --devices): every unit exactly once, loads within the LPT bound,
+    units of one pair adjacent on a rank, the same plan on every call."""
+    dist = pkg("dist")
+    costs = [146.6, 118.4, 261.4, 118.4, 88.5, 157.6, 151.3, 153.3, 232.8, 248.2, 176.0, 141.5, 140.4, 104.2, 212.6, 122.0]   # cfg4, r02 probe (ms)
+    pairs = [(2 * k, 2 * k + 1) for k in range(16)]
+    for world in (1, 2, 4, 8):
+        a, load = dist.plan_units(costs, pairs, world)
+        assert sorted(i for r in a for i in r) == list(range(16))
+        assert max(load) <= sum(costs) / world + max(costs) * (1 - 1 / world) + 1e-9      # Graham's bound for list scheduling
+        assert dist.plan_units(costs, pairs, world) == (a, load)
+    a8, load8 = dist.plan_units(costs, pairs, 8)
+    assert sum(load8) / 8 / max(load8) > 0.9                                                # 16 whole pairs on 8 ranks: ~0.91
+    # two parts per pair: finer units balance better, and both parts of a pair that land on one rank are adjacent
+    c2 = [c / 2 for c in costs for _ in range(2)]
+    p2 = [p for p in pairs for _ in range(2)]
+    b, load = dist.plan_units(c2, p2, 8)
+    assert sum(load) / 8 / max(load) > 0.95
+    for r in b:
+        seen = []
+        for i in r:
+            if p2[i] in seen:
+                assert seen[-1] == p2[i]
+            seen.append(p2[i])
