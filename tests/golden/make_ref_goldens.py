@@ -42,6 +42,58 @@ def one_pass(h1, h2):
     print((h1, h2), "pairs", len(p["h1"]), "blocks", len(blocks), "cluster keys", len(keys), r.times())
 
 
+def full_run(workdir="/tmp/refrun"):
+    """The reference's own main (oracle/_ref/curvix_main_ref = cmd/main.cpp + all of Edge_Reconst, unmodified, built against
+    oracle/ref_shim) on the bundled scene with configs/3D_Curvix_ABC_NEF.yaml (only Dataset_Path and the thread count changed; the
+    un-refined poses are presented under the refined_{R,T}.txt names the build expects, definitions.h:11).  ~11 min on 8 cores.
+    -> tests/golden/ref_abc_full_run.npz (schedule, claimed ratios, 3-D edges / tangents of every pass as printed, 6 digits) and
+       tests/golden/ref_final_curves_abc.txt.gz (outputs/final_curves.txt)."""
+    import gzip
+    import re
+    import shutil
+    import subprocess
+    ref = ref_py.REF_ROOT
+    out = os.path.join(workdir, "outputs")
+    log = os.path.join(workdir, "full_run.log")
+    if not os.path.exists(os.path.join(out, "final_curves.txt")):
+        ref_py.build(("strict",), main=True)
+        scene_dir = os.path.join(workdir, "data", "ABC-NEF", "00000006")
+        os.makedirs(os.path.join(scene_dir, "RnT"), exist_ok=True)
+        os.makedirs(os.path.join(workdir, "run", "bin"), exist_ok=True)
+        os.makedirs(out, exist_ok=True)
+        for d in ("Edges", "curvelets"):
+            if not os.path.exists(os.path.join(scene_dir, d)):
+                os.symlink(os.path.join(ref, "datasets", "ABC-NEF", "00000006", d), os.path.join(scene_dir, d))
+        shutil.copy(os.path.join(ref, "datasets/ABC-NEF/00000006/RnT/R_matrix.txt"), os.path.join(scene_dir, "RnT", "refined_R.txt"))
+        shutil.copy(os.path.join(ref, "datasets/ABC-NEF/00000006/RnT/T_matrix.txt"), os.path.join(scene_dir, "RnT", "refined_T.txt"))
+        cfg = open(os.path.join(ref, "configs", "3D_Curvix_ABC_NEF.yaml")).read()
+        cfg = re.sub(r"^Dataset_Path:.*$", "Dataset_Path: " + os.path.join(workdir, "data") + "/", cfg, flags=re.M)
+        cfg = re.sub(r"^Num_Of_OMP_Threads:.*$", "Num_Of_OMP_Threads: %d" % (os.cpu_count() or 1), cfg, flags=re.M)
+        open(os.path.join(workdir, "cfg.yaml"), "w").write(cfg)
+        with open(log, "w") as f:
+            subprocess.run([os.path.join(ref_py.OUT, "curvix_main_ref"), "-c", "../../cfg.yaml"], cwd=os.path.join(workdir, "run", "bin"), stdout=f,
+                           stderr=subprocess.STDOUT, check=True)
+    text = open(log).read()
+    sched = [(int(a), int(b)) for a, b in re.findall(r"Selected views for hypotheses are (\d+) and (\d+)", text)]
+    ratios = [float(x) for x in re.findall(r"Average ratio of claimed edges: ([0-9.eE+-]+)", text)]
+    npairs = [int(x) for x in re.findall(r"Number of edge pairs: (\d+)", text)]
+    times = {k: float(v) for k, v in re.findall(r"Time for (Pairing up Edges|Finalizing Edge Pairs|Finding Next Hypothesis Views):\s+([0-9.eE+-]+)", text)}
+    d = dict(schedule=np.array(sched), avg_ratio=np.array(ratios), n_pairs=np.array(npairs), build_info=np.array(ref_py.build_info()),
+             pair_edges_s=times.get("Pairing up Edges", np.nan), finalize_s=times.get("Finalizing Edge Pairs", np.nan),
+             next_views_s=times.get("Finding Next Hypothesis Views", np.nan), threads=os.cpu_count() or 1)
+    for i, (a, b) in enumerate(sched):
+        name = f"ABC-NEF_00000006_hypo1_{a}_hypo2_{b}.txt"
+        d[f"edges_{i}"] = np.loadtxt(os.path.join(out, "3D_edges_" + name)).reshape(-1, 3)
+        d[f"tangents_{i}"] = np.loadtxt(os.path.join(out, "3D_tangents_" + name)).reshape(-1, 3)
+    np.savez_compressed(os.path.join(ROOT, "tests", "golden", "ref_abc_full_run.npz"), **d)
+    with open(os.path.join(out, "final_curves.txt"), "rb") as f, gzip.GzipFile(os.path.join(ROOT, "tests", "golden", "ref_final_curves_abc.txt.gz"), "wb", 9, mtime=0) as g:
+        g.write(f.read())
+    print("full run:", sched, ratios, npairs, times)
+
+
 if __name__ == "__main__":
-    for pr in ((47, 42), (28, 48)):
-        one_pass(*pr)
+    if "--full" in sys.argv:
+        full_run()
+    else:
+        for pr in ((47, 42), (28, 48)):
+            one_pass(*pr)

@@ -4,6 +4,7 @@
 #include <iostream>
 #include <string>
 
+#include "../3d_curvix_b200/host/curve_io.hpp"
 #include "../3d_curvix_b200/host/dataset_io.hpp"
 #include "../3d_curvix_b200/host/edge_mapping.hpp"
 #include "../3d_curvix_b200/host/flat_yaml.hpp"
@@ -44,6 +45,14 @@ int main(int argc, char** argv) {
         std::vector<double> m(size_t(rows) * size_t(cols));
         for (double& v : m) std::cin >> v;
         return write_eigen_matrix(arg, m.data(), rows, cols) ? 0 : 4;
+    }
+    if (cmd == "curves") {   // read arg (reference layout), report, write it back to arg + ".out"
+        std::vector<Curve3D> c;
+        if (!read_curves_file(arg, &c)) return 3;
+        size_t nodes = 0;
+        for (const auto& k : c) nodes += k.nodes.size();
+        std::printf("%zu %zu\n", c.size(), nodes);
+        return write_curves_file(arg + ".out", c) ? 0 : 4;
     }
     if (cmd == "mapping") {   // same 3-D point twice + another one -> 2 edges, 3 links
         EdgeMapping em;

@@ -78,6 +78,35 @@ def test_abc_nef_first_pass_parity(oracle_mod, abc_scene):
     assert rep["n_pairs_compared"] >= 0.97 * rep["n_pairs_oracle"]
 
 
+@pytest.mark.parametrize("pair", [(47, 42), (28, 48)])
+def test_abc_against_reference_goldens(abc_scene, pair):
+    """The CUDA path against vectors written by the REFERENCE ITSELF (tests/golden/ref_abc_*.npz: its unmodified sources built against
+    oracle/ref_shim): accepted view-1 edges, the support index of every accepted row in every validation view and the support counts
+    bit-exact; the view-2 representative exact except for tied 2-member clusters (the other member of the same cluster, counted);
+    3-D points / tangents to 1e-6 on the rows with the same representative."""
+    gold = np.load(os.path.join(ROOT, "tests", "golden", f"ref_abc_{pair[0]}_{pair[1]}.npz"))
+    g = _gpu(abc_scene)
+    g.set_pair(*pair); g.run()
+    order = g.reference_order()
+    p, f, r, t = g.pairs(), g.finalize(), g.rows(), g.h1_table()
+    assert len(order) == len(gold["pair_h1"])
+    assert np.array_equal(p["h1"][order], gold["pair_h1"])
+    assert np.array_equal(p["supports"][order], gold["pair_supports"])
+    same = p["h2rep"][order] == gold["pair_h2rep"]
+    n_tied = int((~same).sum())
+    assert n_tied <= 0.03 * len(order)
+    for k in np.nonzero(~same)[0]:                       # the reference's representative is another member of the SAME cluster
+        row = int(p["row"][order[k]]); h1 = int(p["h1"][order[k]])
+        s0, n = int(t["off"][h1]), int(t["n"][h1])
+        members = r["h2_orig"][s0:s0 + n][r["label"][s0:s0 + n] == r["label"][row]]
+        assert int(gold["pair_h2rep"][k]) in members.tolist() and len(members) == 2
+    ok = same & (f["nan_flag"][order] == 0)
+    for key in ("gamma_world", "tangent_world"):
+        a, b = f[key][order][ok], gold[key][ok]
+        assert np.max(np.abs(a - b) / np.maximum(np.linalg.norm(b, axis=1, keepdims=True), 1e-3)) <= 1e-6, key
+    _report(f"abc_{pair[0]}_{pair[1]}_vs_reference", {"pairs": int(len(order)), "tied_representatives": n_tied})
+
+
 def test_strict_libm_order_switch(oracle_mod, abc_scene):
     """cvx_config.strict_libm_order = 1: the validation kernel evaluates the view-2 wedge in the reference's libm call order
     (wedge_row) instead of wedge_row_fast; both must satisfy the parity rule, and they select the same pairs on this pass."""

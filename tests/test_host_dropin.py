@@ -12,7 +12,6 @@ from test_host_io import ABC_YAML
 
 pytestmark = pytest.mark.gpu
 
-N_PASSES = 4
 
 
 def _oracle_schedule(oracle_mod, scene, n_passes, start=(47, 42), stop_ratio=0.7):
@@ -111,38 +110,41 @@ def abc_on_disk(abc_scene, tmp_path_factory):
     return root, cfg
 
 
-def test_curvix_main_matches_oracle_over_passes(oracle_mod, abc_scene, abc_on_disk):
-    """BASELINE.json config 1 end to end through the C++ drop-in: same pass schedule, same accepted pairs, 3-D edges and
-    tangents within 1e-6 relative of the oracle's (files carry 6 significant digits)."""
+def test_curvix_main_full_run_matches_the_reference(abc_scene, abc_on_disk):
+    """BASELINE.json config 1 end to end through the C++ drop-in, to the stop criterion (no --max-passes): the pass schedule, the claimed
+    ratios, the number of 3-D edges of every pass and the rows of the output files against tests/golden/ref_abc_full_run.npz, which
+    is the REFERENCE's own run (its cmd/main.cpp built against oracle/ref_shim; tests/golden/make_ref_goldens.py --full)."""
     build = pkg("build")
     exe = build.build_host(force=False)
     assert exe and os.path.exists(exe)
+    g = np.load(os.path.join(ROOT, "tests", "golden", "ref_abc_full_run.npz"))
     root, cfg = abc_on_disk
     out = root / "outputs"
     sched = root / "schedule.txt"
-    r = subprocess.run([exe, "-c", str(cfg), "--outputs", str(out), "--max-passes", str(N_PASSES), "--schedule", str(sched),
-                        "--edge-cache", str(root)], capture_output=True, text=True, timeout=600)
+    r = subprocess.run([exe, "-c", str(cfg), "--outputs", str(out), "--schedule", str(sched), "--edge-cache", str(root)],
+                       capture_output=True, text=True, timeout=600)
     assert r.returncode == 0 and "3D Curvix is Finished!" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
-    ref = _oracle_schedule(oracle_mod, abc_scene, N_PASSES)
     rows = [l.split() for l in sched.read_text().splitlines()]
-    assert len(rows) == len(ref)
-    for row, ps in zip(rows, ref):
-        a, b = ps["pair"]
-        assert (int(row[1]), int(row[2])) == (a, b)                       # identical pass schedule
-        assert abs(float(row[7]) - ps["avg"]) < 1e-3
+    assert [(int(x[1]), int(x[2])) for x in rows] == [tuple(int(v) for v in p) for p in g["schedule"]]      # identical pass schedule, same stop
+    n_diff_rows = 0
+    for i, row in enumerate(rows):
+        a, b = int(row[1]), int(row[2])
+        assert abs(float(row[7]) - g["avg_ratio"][i]) < 1e-6
         name = f"ABC-NEF_00000006_hypo1_{a}_hypo2_{b}.txt"
         E = np.loadtxt(out / ("3D_edges_" + name)).reshape(-1, 3)
         T = np.loadtxt(out / ("3D_tangents_" + name)).reshape(-1, 3)
-        ok = ps["fin"]["nan_flag"] == 0
-        Eo, To = ps["fin"]["gamma_world"][ok], ps["fin"]["tangent_world"][ok]
-        assert abs(len(E) - len(Eo)) <= 0.02 * len(Eo) and len(T) == len(E)
-        # compare as sets of rows rounded to the file precision (row order inside one view-1 edge follows std::sort; the tied
-        # cluster representatives change ~1 % of the rows)
-        key = lambda M: {tuple(np.round(r, 3)) for r in M}
-        kE, kO = key(E), key(Eo)           # duplicated (view-1 edge, representative) pairs give duplicated rows: compare distinct rows
-        assert len(kE & kO) >= 0.97 * len(kO) and len(kE) <= 1.03 * len(kO), (len(kE & kO), len(kE), len(kO))
-        kT, kTo = key(T), key(To)
-        assert len(kT & kTo) >= 0.97 * len(kTo), (len(kT & kTo), len(kTo))
+        Eo, To = g[f"edges_{i}"], g[f"tangents_{i}"]
+        assert E.shape == Eo.shape and T.shape == To.shape                                                # the same number of 3-D edges
+        # Row by row (same order: ascending view-1 edge, std::sort order inside).  The only rows that may differ are those whose view-2
+        # representative is the other member of a tied 2-member cluster (an exact tie decided by the last bit of tan(), counted by
+        # test_gpu_parity through the oracle's margins): ~1 % of the view-1 edges, and then both the point and the tangent move.
+        same = np.isclose(E, Eo, rtol=2e-5, atol=1e-9).all(1) & np.isclose(T, To, rtol=2e-5, atol=2e-6).all(1)
+        n_diff_rows += int((~same).sum())
+        assert (~same).mean() < 0.02, (i, int((~same).sum()), len(E))
+        # a differing row is still a reconstruction of the same view-1 edge from a neighbouring view-2 edge: it stays within a pixel-scale
+        # distance of the reference row (scene radius ~1, image 800 px)
+        assert np.linalg.norm(E[~same] - Eo[~same], axis=1).max(initial=0.0) < 0.05
+    print("rows that differ from the reference run (tied cluster representatives):", n_diff_rows)
     # second run from the binary edge cache gives byte-identical outputs
     first = {f: (out / f).read_bytes() for f in os.listdir(out)}
     r = subprocess.run([exe, "-c", str(cfg), "--outputs", str(out), "--max-passes", "2", "--edge-cache", str(root), "--quiet"],

@@ -109,3 +109,23 @@ def test_edge_mapping_insertion_api(io_check, tmp_path):
     out = subprocess.run([io_check, "mapping", str(p)], check=True, capture_output=True, text=True).stdout.split()
     assert out == ["2", "3"]          # keyed on the exact doubles of the 3-D point, like the reference's unordered_map
     assert len(p.read_text().splitlines()) == 3
+
+
+def test_final_curves_file_layout_round_trips_the_reference_file(io_check, tmp_path):
+    """tests/golden/ref_final_curves_abc.txt.gz is outputs/final_curves.txt as the REFERENCE wrote it (its own cmd/main.cpp built against
+    oracle/ref_shim, ABC-NEF 00000006, 5 passes; tests/golden/make_ref_goldens.py --full).  The host reader (the loop of
+    visualization/plot_curves.m:17-38) parses it, and the host writer (edge_mapping.cpp:1126-1164 layout) reproduces it byte for byte."""
+    import gzip
+    gold = os.path.join(ROOT, "tests", "golden", "ref_final_curves_abc.txt.gz")
+    if not os.path.exists(gold):
+        pytest.skip("reference final_curves golden missing")
+    text = gzip.open(gold, "rb").read()
+    p = tmp_path / "final_curves.txt"
+    p.write_bytes(text)
+    out = subprocess.run([io_check, "curves", str(p)], check=True, capture_output=True, text=True).stdout.split()
+    lines = text.decode().splitlines()
+    assert lines[0].startswith("# Curves") and lines[1].startswith("# Format: CurveID")
+    body = [l for l in lines[2:] if l.strip()]
+    n_curves = len({l.split()[0] for l in body})
+    assert int(out[0]) == n_curves == 780 and int(out[1]) == len(body)
+    assert (tmp_path / "final_curves.txt.out").read_bytes() == text

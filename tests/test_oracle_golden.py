@@ -94,3 +94,32 @@ def test_h1_range_additivity(oracle_mod, tiny_scene):
     assert tot == full["n_validations"]
     assert np.array_equal(np.concatenate([p["h1"] for p in parts]), pf["h1"])
     assert np.array_equal(np.concatenate([p["supports"] for p in parts]), pf["supports"])
+
+
+def test_port_reproduces_the_reference_full_run(oracle_mod, abc_scene):
+    """tests/golden/ref_abc_full_run.npz: the reference's own main on ABC-NEF 00000006 to its stop criterion (5 passes, claimed ratio
+    0.712898 > 0.7).  The port, driven through the same pass loop -- claims of the accepted rows that fit paired_edge, claimed-edge
+    ratios, next-view selection (EdgeSketch_Core.cpp:776-871) -- visits the same pairs, accepts the same number of rows and prints the
+    same files (6 significant digits)."""
+    g = np.load(os.path.join(ROOT, "tests", "golden", "ref_abc_full_run.npz"))
+    o = make_oracle(oracle_mod, abc_scene)
+    masks = [np.zeros(len(e), np.uint8) for e in abc_scene.edges]
+    total = np.array([len(e) for e in abc_scene.edges], np.int64)
+    pair, hist = (47, 42), []
+    for i in range(len(g["schedule"])):
+        assert pair == tuple(int(v) for v in g["schedule"][i]), f"pass {i}: the port selected {pair}"
+        hist += list(pair)
+        o.set_pair(*pair)
+        o.run(mode=1)
+        p, f = o.pairs(), o.finalize()
+        assert len(p["h1"]) == g["n_pairs"][i]
+        ok = f["nan_flag"] == 0
+        E, T = g[f"edges_{i}"], g[f"tangents_{i}"]
+        assert ok.sum() == len(E)
+        assert np.allclose(f["gamma_world"][ok], E, rtol=6e-6, atol=1e-9) and np.allclose(f["tangent_world"][ok], T, rtol=6e-6, atol=6e-7)
+        o.accumulate_claims(masks)
+        claimed = np.array([int(m.sum()) for m in masks], np.int64)
+        b1, b2, avg, stop = oracle_mod.select_next_views(claimed, total, hist, 0.7)
+        assert abs(avg - g["avg_ratio"][i]) < 5e-7 * max(1.0, avg) + 5e-7, (avg, g["avg_ratio"][i])
+        assert stop == (i == len(g["schedule"]) - 1)
+        pair = (b1, b2)
