@@ -64,7 +64,7 @@ class CvxDeviceResults(C.Structure):
 class CvxGatheredUnit(C.Structure):
     _fields_ = [("meta", C.c_int64 * 8), ("pair_h1", C.c_void_p), ("pair_h2rep", C.c_void_p), ("pair_count", C.c_void_p), ("nan_flag", C.c_void_p),
                 ("support_off", C.c_void_p), ("support_entries", C.c_void_p), ("gamma_world", C.c_void_p), ("tangent_world", C.c_void_p),
-                ("gamma_cam", C.c_void_p)]
+                ("gamma_cam", C.c_void_p), ("h2_corrected_xy", C.c_void_p)]
 
 
 _lib = None
@@ -92,8 +92,8 @@ def load():
     lib.cvx_gather_post.argtypes = [C.c_void_p, C.c_int64, C.c_int]
     lib.cvx_gather_wait.argtypes = [C.c_void_p, C.c_int, C.c_int]
     lib.cvx_gather_get.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(CvxGatheredUnit)]
-    lib.cvx_gather_fetch.argtypes = [C.c_void_p, C.c_int, C.c_int] + [C.c_void_p] * 9
-    lib.cvx_gather_fetch_async.argtypes = [C.c_void_p, C.c_int, C.c_int] + [C.c_void_p] * 9
+    lib.cvx_gather_fetch.argtypes = [C.c_void_p, C.c_int, C.c_int] + [C.c_void_p] * 10
+    lib.cvx_gather_fetch_async.argtypes = [C.c_void_p, C.c_int, C.c_int] + [C.c_void_p] * 10
     lib.cvx_comm_init.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
     lib.cvx_comm_attach.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int]
     lib.cvx_split_h1_by_rows.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
@@ -337,13 +337,13 @@ class EdgeSketch:
         self._ck(self.lib.cvx_gather_get(self.h, rnd, rank, C.byref(u)))
         return u
 
-    GATHER_FIELDS = ("h1", "h2rep", "count", "nan_flag", "support_off", "support_entries", "gamma_world", "tangent_world", "gamma_cam")
+    GATHER_FIELDS = ("h1", "h2rep", "count", "nan_flag", "support_off", "support_entries", "gamma_world", "tangent_world", "gamma_cam", "h2_corrected")
 
     @staticmethod
     def gather_widths(P, S):
         """bytes of every field of a gathered unit with P rows and S supports"""
         return dict(h1=4 * P, h2rep=4 * P, count=4 * P, nan_flag=4 * P, support_off=8 * (P + 1), support_entries=8 * S, gamma_world=24 * P,
-                    tangent_world=24 * P, gamma_cam=24 * P)
+                    tangent_world=24 * P, gamma_cam=24 * P, h2_corrected=16 * P)
 
     def gather_fetch(self, rnd, rank):
         """Host copies of what `rank` contributed in round `rnd` (rank 0 only).  `supports` is the CSR list expanded to the reference's
@@ -352,7 +352,7 @@ class EdgeSketch:
         P, V, S = int(u.meta[0]), int(u.meta[6]), int(u.meta[7])
         out = dict(meta=[int(x) for x in u.meta], h1=np.empty(P, np.int32), h2rep=np.empty(P, np.int32), count=np.empty(P, np.int32),
                    nan_flag=np.empty(P, np.int32), support_off=np.zeros(P + 1, np.int64), support_entries=np.empty((S, 2), np.int32),
-                   gamma_world=np.empty((P, 3)), tangent_world=np.empty((P, 3)), gamma_cam=np.empty((P, 3)))
+                   gamma_world=np.empty((P, 3)), tangent_world=np.empty((P, 3)), gamma_cam=np.empty((P, 3)), h2_corrected=np.empty((P, 2)))
         if P:
             self._ck(self.lib.cvx_gather_fetch(self.h, rnd, rank, *[_vp(out[k]) for k in self.GATHER_FIELDS]))
         dense = np.full((P, V), -2, np.int32)

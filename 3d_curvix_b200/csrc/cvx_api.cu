@@ -1153,7 +1153,7 @@ int cvx_internal_results(cvx_ctx* ctx, CvxResultsView* out) {
     out->P = ctx->P; out->V = ctx->n_vali; out->device = ctx->device;
     out->view1 = ctx->h1; out->view2 = ctx->h2; out->run_begin = ctx->run_begin; out->run_end = ctx->run_end;
     out->h1 = ctx->p_h1.p; out->h2rep = ctx->p_h2rep.p; out->count = ctx->p_count.p; out->nan = ctx->f_nan.p; out->sup = ctx->p_sup.p;
-    out->gc = ctx->f_gc.p; out->gw = ctx->f_gw.p; out->tw = ctx->f_tw.p;
+    out->gc = ctx->f_gc.p; out->gw = ctx->f_gw.p; out->tw = ctx->f_tw.p; out->h2c = ctx->f_h2c.p;
     out->stream = ctx->stream;
     return CVX_OK;
 }

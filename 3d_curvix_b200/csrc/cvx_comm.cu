@@ -68,7 +68,7 @@ inline size_t align16(size_t x) { return (x + 15) & ~size_t(15); }
 // Byte offsets of the fields of a packed unit with P rows and S supports.  The support indices travel as a CSR list (row r owns
 // entries [sup_off[r], sup_off[r+1]), each {validation view slot, edge index}, ascending slot): a row is supported by ~10 of ~100
 // views, so the dense P x V matrix of the reference's paired_edge (EdgeSketch_Core.cpp:510-526) would be ~4x the bytes.
-struct Layout { size_t h1, h2, cnt, nan, gw, tw, gc, soff, sent, total; };
+struct Layout { size_t h1, h2, cnt, nan, gw, tw, gc, h2c, soff, sent, total; };
 Layout layout_of(int64_t P, int64_t S) {
     Layout l;
     size_t o = 0;
@@ -79,6 +79,7 @@ Layout layout_of(int64_t P, int64_t S) {
     l.gw = o; o = align16(o + size_t(P) * 24);
     l.tw = o; o = align16(o + size_t(P) * 24);
     l.gc = o; o = align16(o + size_t(P) * 24);
+    l.h2c = o; o = align16(o + size_t(P) * 16);
     l.soff = o; o = align16(o + size_t(P + 1) * 8);
     l.sent = o; o = align16(o + size_t(S) * 8);
     l.total = o;
@@ -337,6 +338,7 @@ int cvx_gather_post(cvx_ctx* ctx, int64_t unit_id, int empty) {
         CUC(cudaMemcpyAsync(b + l.gw, v.gw, P * 24, cudaMemcpyDeviceToDevice, main_stream));
         CUC(cudaMemcpyAsync(b + l.tw, v.tw, P * 24, cudaMemcpyDeviceToDevice, main_stream));
         CUC(cudaMemcpyAsync(b + l.gc, v.gc, P * 24, cudaMemcpyDeviceToDevice, main_stream));
+        CUC(cudaMemcpyAsync(b + l.h2c, v.h2c, P * 16, cudaMemcpyDeviceToDevice, main_stream));
         // supports as a CSR list: offsets = exclusive scan of the per-row support counts (the vote of EdgeSketch_Core.cpp:414-427)
         int64_t* off = reinterpret_cast<int64_t*>(b + l.soff);
         cvx::launch_scan_i32_i64(v.count, off, int(v.P), main_stream);
@@ -399,12 +401,12 @@ int cvx_gather_get(cvx_ctx* ctx, int round, int rank, cvx_gathered_unit* out) {
     out->pair_count = reinterpret_cast<const int32_t*>(b + l.cnt); out->nan_flag = reinterpret_cast<const int32_t*>(b + l.nan);
     out->support_off = reinterpret_cast<const int64_t*>(b + l.soff); out->support_entries = reinterpret_cast<const int32_t*>(b + l.sent);
     out->gamma_world = reinterpret_cast<const double*>(b + l.gw); out->tangent_world = reinterpret_cast<const double*>(b + l.tw);
-    out->gamma_cam = reinterpret_cast<const double*>(b + l.gc);
+    out->gamma_cam = reinterpret_cast<const double*>(b + l.gc); out->h2_corrected_xy = reinterpret_cast<const double*>(b + l.h2c);
     return CVX_OK;
 }
 
 static int gather_fetch_impl(cvx_ctx* ctx, int round, int rank, int32_t* h1, int32_t* h2rep, int32_t* count, int32_t* nan_flag, int64_t* support_off,
-                             int32_t* support_entries, double* gamma_world, double* tangent_world, double* gamma_cam, bool wait) {
+                             int32_t* support_entries, double* gamma_world, double* tangent_world, double* gamma_cam, double* h2c, bool wait) {
     cvx_gathered_unit u;
     const int rc = cvx_gather_get(ctx, round, rank, &u);
     if (rc) return rc;
@@ -416,17 +418,18 @@ static int gather_fetch_impl(cvx_ctx* ctx, int round, int rank, int32_t* h1, int
     CVX_FETCH(h1, u.pair_h1, P * 4); CVX_FETCH(h2rep, u.pair_h2rep, P * 4); CVX_FETCH(count, u.pair_count, P * 4); CVX_FETCH(nan_flag, u.nan_flag, P * 4);
     CVX_FETCH(support_off, u.support_off, (P + 1) * 8); CVX_FETCH(support_entries, u.support_entries, S * 8);
     CVX_FETCH(gamma_world, u.gamma_world, P * 24); CVX_FETCH(tangent_world, u.tangent_world, P * 24); CVX_FETCH(gamma_cam, u.gamma_cam, P * 24);
+    CVX_FETCH(h2c, u.h2_corrected_xy, P * 16);
 #undef CVX_FETCH
     if (wait) CUC(cudaStreamSynchronize(s->cs));
     return CVX_OK;
 }
 int cvx_gather_fetch(cvx_ctx* ctx, int round, int rank, int32_t* h1, int32_t* h2rep, int32_t* count, int32_t* nan_flag, int64_t* support_off,
-                     int32_t* support_entries, double* gamma_world, double* tangent_world, double* gamma_cam) {
-    return gather_fetch_impl(ctx, round, rank, h1, h2rep, count, nan_flag, support_off, support_entries, gamma_world, tangent_world, gamma_cam, true);
+                     int32_t* support_entries, double* gamma_world, double* tangent_world, double* gamma_cam, double* h2_corrected_xy) {
+    return gather_fetch_impl(ctx, round, rank, h1, h2rep, count, nan_flag, support_off, support_entries, gamma_world, tangent_world, gamma_cam, h2_corrected_xy, true);
 }
 int cvx_gather_fetch_async(cvx_ctx* ctx, int round, int rank, int32_t* h1, int32_t* h2rep, int32_t* count, int32_t* nan_flag, int64_t* support_off,
-                           int32_t* support_entries, double* gamma_world, double* tangent_world, double* gamma_cam) {
-    return gather_fetch_impl(ctx, round, rank, h1, h2rep, count, nan_flag, support_off, support_entries, gamma_world, tangent_world, gamma_cam, false);
+                           int32_t* support_entries, double* gamma_world, double* tangent_world, double* gamma_cam, double* h2_corrected_xy) {
+    return gather_fetch_impl(ctx, round, rank, h1, h2rep, count, nan_flag, support_off, support_entries, gamma_world, tangent_world, gamma_cam, h2_corrected_xy, false);
 }
 
 int cvx_gather_stats(cvx_ctx* ctx, int64_t* bytes_sent, int64_t* bytes_received, float* comm_ms) {

@@ -9,7 +9,7 @@ struct CvxResultsView {
     int64_t P; int V; int device;
     int view1, view2, run_begin, run_end;
     const int32_t *h1, *h2rep, *count, *nan, *sup;
-    const double *gc, *gw, *tw;
+    const double *gc, *gw, *tw, *h2c;
     cudaStream_t stream;
 };
 struct CvxCommState;

@@ -8,6 +8,7 @@
 #include <cstring>
 #include <iostream>
 #include <numeric>
+#include <thread>
 
 using curvix_host::EdgeTable;
 using curvix_host::FlatYaml;
@@ -58,16 +59,33 @@ EdgeSketch_Core::EdgeSketch_Core(const FlatYaml& y, const HostOptions& opt) : op
     cfg.img_rows = Img_Rows;
     cfg.img_cols = Img_Cols;
     cfg.max_support_views = Max_Num_Of_Support_Views;
-    const int rc = cvx_create(&cfg, opt_.device, &gpu_);
-    if (rc != CVX_OK) {
-        std::cerr << "ERROR: cvx_create failed with status " << rc << (rc == CVX_ERR_NO_DEVICE ? " (no CUDA device; this build has no CPU path)" : "")
-                  << std::endl;
-        std::exit(1);
+    std::vector<int> devs = opt_.devices.empty() ? std::vector<int>{opt_.device} : opt_.devices;
+    for (int d : devs) {
+        cvx_ctx* c = nullptr;
+        const int rc = cvx_create(&cfg, d, &c);
+        if (rc != CVX_OK) {
+            std::cerr << "ERROR: cvx_create on device " << d << " failed with status " << rc
+                      << (rc == CVX_ERR_NO_DEVICE ? " (no CUDA device; this build has no CPU path)" : "") << std::endl;
+            std::exit(1);
+        }
+        gpus_.push_back(c);
+    }
+    gpu_ = gpus_[0];
+    if (multi()) {   // one NCCL communicator over the contexts: the id from the library, one cvx_comm_init per device, concurrently
+        char id[128];
+        check(cvx_comm_unique_id(id), "cvx_comm_unique_id");
+        std::vector<std::thread> th;
+        std::vector<int> rcs(gpus_.size(), 0);
+        for (size_t d = 0; d < gpus_.size(); d++)
+            th.emplace_back([&, d] { rcs[d] = cvx_comm_init(gpus_[d], int(gpus_.size()), int(d), id); });
+        for (auto& t : th) t.join();
+        for (size_t d = 0; d < gpus_.size(); d++)
+            if (rcs[d] != CVX_OK) { std::cerr << "ERROR: cvx_comm_init failed on rank " << d << ": " << cvx_last_error(gpus_[d]) << std::endl; std::exit(1); }
     }
 }
 
 EdgeSketch_Core::~EdgeSketch_Core() {
-    if (gpu_) cvx_destroy(gpu_);
+    for (cvx_ctx* c : gpus_) if (c) cvx_destroy(c);
 }
 
 void EdgeSketch_Core::check(int rc, const char* what) const {   // the reference has no error path inside the sketch: log + exit(1)
@@ -98,9 +116,9 @@ void EdgeSketch_Core::Read_Camera_Data() {
         const std::string kp = rnt + "K_matrix.txt";
         if (!curvix_host::read_R_file(kp, &All_K) || int(All_K.size() / 9) < Num_Of_Total_Imgs) die_file(kp);
         All_K.resize(size_t(Num_Of_Total_Imgs) * 9);
-        check(cvx_set_cameras(gpu_, Num_Of_Total_Imgs, All_R.data(), All_T.data(), All_K.data(), 1), "cvx_set_cameras");
+        for (cvx_ctx* c : gpus_) check(cvx_set_cameras(c, Num_Of_Total_Imgs, All_R.data(), All_T.data(), All_K.data(), 1), "cvx_set_cameras");
     } else {
-        check(cvx_set_cameras(gpu_, Num_Of_Total_Imgs, All_R.data(), All_T.data(), K, 0), "cvx_set_cameras");
+        for (cvx_ctx* c : gpus_) check(cvx_set_cameras(c, Num_Of_Total_Imgs, All_R.data(), All_T.data(), K, 0), "cvx_set_cameras");
     }
     if (!opt_.quiet) std::cout << "Camera poses: " << (refined ? "refined" : "un-refined") << " (" << rp << ")" << std::endl;
 }
@@ -134,9 +152,10 @@ void EdgeSketch_Core::Read_Edgels_Data() {
             if (!curvix_host::read_edge_file(path, &t)) die_file(path);
             if (!cache.empty()) curvix_host::write_edge_cache(cache, t);
         }
-        check(cvx_set_view_edges(gpu_, v, t.size(), t.x.data(), t.y.data(), t.theta.data(), t.strength.data()), "cvx_set_view_edges");
+        for (cvx_ctx* c : gpus_)
+            check(cvx_set_view_edges(c, v, t.size(), t.x.data(), t.y.data(), t.theta.data(), t.strength.data()), "cvx_set_view_edges");
     }
-    check(cvx_claims_reset(gpu_), "cvx_claims_reset");
+    for (cvx_ctx* c : gpus_) check(cvx_claims_reset(c), "cvx_claims_reset");
     edges_uploaded_ = true;
     read_edges_time += now_s() - t0;
 }
@@ -144,13 +163,110 @@ void EdgeSketch_Core::Read_Edgels_Data() {
 // ---- Set_Hypothesis_Views_Edgels, EdgeSketch_Core.cpp:145-166 (+ the per-view staging hoisted out of Run_3D_Edge_Sketch)
 void EdgeSketch_Core::Set_Hypothesis_Views_Edgels() {
     const double t0 = now_s();
-    check(cvx_set_hypothesis_pair(gpu_, hyp01_view_indx, hyp02_view_indx), "cvx_set_hypothesis_pair");
+    for (cvx_ctx* c : gpus_) check(cvx_set_hypothesis_pair(c, hyp01_view_indx, hyp02_view_indx), "cvx_set_hypothesis_pair");   // asynchronous
     pair_edges_time += now_s() - t0;   // in the reference this work sits inside Run_3D_Edge_Sketch's loops
 }
 
 // ---- Run_3D_Edge_Sketch, EdgeSketch_Core.cpp:168-573
+// The pass over several GPUs: the view-1 edges are independent (EdgeSketch_Core.cpp:209, disjoint paired_edge rows :515-523), so every
+// device takes a contiguous range of them balanced by hypothesis rows; one host thread per context.  The accepted rows, 3-D edges and
+// tangents of every range are gathered to the first device (cvx_gather_*: NCCL) in rank order = ascending view-1 edge = the
+// single-GPU row order; the claimed-edge bits are OR-ed over the ranks; the cluster tables stay per rank.
+void EdgeSketch_Core::run_sharded() {
+    const int D = int(gpus_.size()), N = Num_Of_Total_Imgs, V = N - 2;
+    shard_bounds_.assign(size_t(D) + 1, 0);
+    check(cvx_split_h1_by_rows(gpu_, D, shard_bounds_.data()), "cvx_split_h1_by_rows");
+    const int E1 = All_Edgels[size_t(hyp01_view_indx)].size();
+    std::vector<cvx_counts> cnt(static_cast<size_t>(D));
+    std::vector<std::vector<int64_t>> ord(static_cast<size_t>(D));
+    rk_row_off_.assign(size_t(D), {}); rk_row_n_.assign(size_t(D), {}); rk_rawat_.assign(size_t(D), {}); rk_label_.assign(size_t(D), {});
+    std::vector<std::string> err(static_cast<size_t>(D));
+    auto worker = [&](int d) {
+        cvx_ctx* c = gpus_[size_t(d)];
+        auto ck = [&](int rc, const char* what) { if (rc != CVX_OK && err[size_t(d)].empty()) err[size_t(d)] = std::string(what) + ": " + cvx_last_error(c); return rc == CVX_OK; };
+        if (!ck(cvx_run_edge_sketch(c, shard_bounds_[size_t(d)], shard_bounds_[size_t(d) + 1]), "cvx_run_edge_sketch")) return;
+        ck(cvx_get_counts(c, &cnt[size_t(d)]), "cvx_get_counts");
+        ck(cvx_claims_accumulate(c), "cvx_claims_accumulate");          // runs the finalize kernel; claims of this range
+        if (d == 0) ck(cvx_gather_reset(c), "cvx_gather_reset");
+    };
+    {   // phase 1: compute
+        std::vector<std::thread> th;
+        for (int d = 0; d < D; d++) th.emplace_back(worker, d);
+        for (auto& t : th) t.join();
+    }
+    for (int d = 0; d < D; d++) if (!err[size_t(d)].empty()) { std::cerr << "ERROR (device rank " << d << "): " << err[size_t(d)] << std::endl; std::exit(1); }
+    {   // phase 2: the exchange (collective calls, one thread per rank) + the per-rank tables
+        std::vector<std::thread> th;
+        for (int d = 0; d < D; d++)
+            th.emplace_back([&, d] {
+                cvx_ctx* c = gpus_[size_t(d)];
+                auto ck = [&](int rc, const char* what) { if (rc != CVX_OK && err[size_t(d)].empty()) err[size_t(d)] = std::string(what) + ": " + cvx_last_error(c); };
+                if (d != 0) ck(cvx_gather_reset(c), "cvx_gather_reset");
+                ck(cvx_gather_post(c, d, 0), "cvx_gather_post");
+                ck(cvx_gather_wait(c, 1, 1), "cvx_gather_wait");
+                ck(cvx_claims_allreduce(c), "cvx_claims_allreduce");
+                const int64_t P = cnt[size_t(d)].n_pairs, H = cnt[size_t(d)].n_hypotheses;
+                ord[size_t(d)].assign(size_t(std::max<int64_t>(P, 1)), 0);
+                int64_t n_out = 0;
+                ck(cvx_get_reference_order(c, ord[size_t(d)].data(), &n_out), "cvx_get_reference_order");
+                ord[size_t(d)].resize(size_t(n_out));
+                rk_row_off_[size_t(d)].assign(size_t(E1), -1); rk_row_n_[size_t(d)].assign(size_t(E1), 0);
+                rk_rawat_[size_t(d)].assign(size_t(H), 0); rk_label_[size_t(d)].assign(size_t(H), 0);
+                ck(cvx_get_h1_table(c, nullptr, rk_row_n_[size_t(d)].data(), rk_row_off_[size_t(d)].data()), "cvx_get_h1_table");
+                ck(cvx_get_rows(c, nullptr, nullptr, nullptr, rk_rawat_[size_t(d)].data(), nullptr, nullptr, nullptr, nullptr, nullptr, nullptr,
+                                rk_label_[size_t(d)].data(), nullptr, nullptr), "cvx_get_rows");
+            });
+        for (auto& t : th) t.join();
+    }
+    for (int d = 0; d < D; d++) if (!err[size_t(d)].empty()) { std::cerr << "ERROR (device rank " << d << "): " << err[size_t(d)] << std::endl; std::exit(1); }
+    // rank 0: the gathered units, concatenated in rank order
+    std::memset(&last_counts, 0, sizeof(last_counts));
+    int64_t Ptot = 0;
+    for (int d = 0; d < D; d++) {
+        const cvx_counts& c = cnt[size_t(d)];
+        last_counts.n_h1_total = c.n_h1_total; last_counts.n_h1_processed += c.n_h1_processed; last_counts.n_candidates += c.n_candidates;
+        last_counts.n_hypotheses += c.n_hypotheses; last_counts.n_validations += c.n_validations; last_counts.n_valid_rows += c.n_valid_rows;
+        last_counts.n_pairs += c.n_pairs; last_counts.n_degenerate_wedges += c.n_degenerate_wedges; last_counts.n_supported += c.n_supported;
+        last_counts.n_parallel += c.n_parallel; last_counts.n_inliers += c.n_inliers; last_counts.n_unique_hypotheses += c.n_unique_hypotheses;
+        Ptot += c.n_pairs;
+    }
+    std::vector<int32_t> h1(size_t(Ptot), 0), h2(size_t(Ptot), 0);
+    std::vector<int64_t> soff;
+    std::vector<int32_t> sent;
+    mg_gc_.assign(size_t(Ptot) * 3, 0.0); mg_gw_.assign(size_t(Ptot) * 3, 0.0); mg_tw_.assign(size_t(Ptot) * 3, 0.0); mg_h2c_.assign(size_t(Ptot) * 2, 0.0);
+    mg_nf_.assign(size_t(Ptot), 0);
+    std::vector<int32_t> sup(size_t(Ptot) * size_t(V), -2);
+    order_.clear();
+    int64_t base = 0;
+    for (int d = 0; d < D; d++) {
+        cvx_gathered_unit u;
+        check(cvx_gather_get(gpu_, 0, d, &u), "cvx_gather_get");
+        const int64_t P = u.meta[0], S = u.meta[7];
+        if (P != cnt[size_t(d)].n_pairs) { std::cerr << "ERROR: gathered unit of rank " << d << " has " << P << " rows, expected " << cnt[size_t(d)].n_pairs << std::endl; std::exit(1); }
+        if (P > 0) {
+            soff.assign(size_t(P) + 1, 0); sent.assign(size_t(S) * 2, 0);
+            check(cvx_gather_fetch(gpu_, 0, d, h1.data() + base, h2.data() + base, nullptr, mg_nf_.data() + base, soff.data(), sent.data(),
+                                   mg_gw_.data() + base * 3, mg_tw_.data() + base * 3, mg_gc_.data() + base * 3, mg_h2c_.data() + base * 2), "cvx_gather_fetch");
+            for (int64_t r = 0; r < P; r++)
+                for (int64_t e = soff[size_t(r)]; e < soff[size_t(r) + 1]; e++)
+                    sup[size_t(base + r) * size_t(V) + size_t(sent[size_t(e) * 2])] = sent[size_t(e) * 2 + 1];
+        }
+        for (int64_t i : ord[size_t(d)]) order_.push_back(base + i);
+        base += P;
+    }
+    const int64_t n_out = int64_t(order_.size());
+    paired_edge_final = Matrix(n_out, N, -2.0);   // :596-601
+    for (int64_t i = 0; i < n_out; i++) {
+        const int64_t p = order_[size_t(i)];
+        paired_edge_final(i, 0) = h1[size_t(p)];
+        paired_edge_final(i, 1) = h2[size_t(p)];
+        for (int v = 0; v < V; v++) paired_edge_final(i, 2 + v) = sup[size_t(p) * size_t(V) + size_t(v)];
+    }
+}
+
 void EdgeSketch_Core::Run_3D_Edge_Sketch() {
     const double t0 = now_s();
+    if (multi()) { run_sharded(); pair_edges_time += now_s() - t0; return; }
     check(cvx_run_edge_sketch(gpu_, 0, -1), "cvx_run_edge_sketch");
     check(cvx_get_counts(gpu_, &last_counts), "cvx_get_counts");
     const int N = Num_Of_Total_Imgs, V = N - 2;
@@ -183,13 +299,20 @@ void EdgeSketch_Core::Run_3D_Edge_Sketch() {
 
 std::vector<int> EdgeSketch_Core::get_edges_in_same_cluster(int hypo1_edge, int hypo2_edge) const {
     // key = (view-1 edge, HYPO2_idx_raw(local row)), value = HYPO2_idx_raw of every row of that cluster (EdgeClusterer.cpp:216-236)
-    if (hypo1_edge >= 0 && size_t(hypo1_edge) < row_off_.size() && row_off_[size_t(hypo1_edge)] >= 0) {
-        const int64_t r0 = row_off_[size_t(hypo1_edge)], r1 = r0 + row_n_[size_t(hypo1_edge)];
+    const std::vector<int64_t>* off = &row_off_;
+    const std::vector<int32_t>*rn = &row_n_, *raw = &raw_at_local_, *lab = &label_;
+    if (multi()) {   // the tables of the rank that owns this view-1 edge
+        size_t d = 0;
+        while (d + 1 < gpus_.size() && hypo1_edge >= shard_bounds_[d + 1]) d++;
+        off = &rk_row_off_[d]; rn = &rk_row_n_[d]; raw = &rk_rawat_[d]; lab = &rk_label_[d];
+    }
+    if (hypo1_edge >= 0 && size_t(hypo1_edge) < off->size() && (*off)[size_t(hypo1_edge)] >= 0) {
+        const int64_t r0 = (*off)[size_t(hypo1_edge)], r1 = r0 + (*rn)[size_t(hypo1_edge)];
         for (int64_t r = r0; r < r1; r++) {
-            if (raw_at_local_[size_t(r)] != hypo2_edge) continue;
+            if ((*raw)[size_t(r)] != hypo2_edge) continue;
             std::vector<int> members;
             for (int64_t q = r0; q < r1; q++)
-                if (label_[size_t(q)] == label_[size_t(r)]) members.push_back(raw_at_local_[size_t(q)]);
+                if ((*lab)[size_t(q)] == (*lab)[size_t(r)]) members.push_back((*raw)[size_t(q)]);
             return members;
         }
     }
@@ -205,8 +328,12 @@ void EdgeSketch_Core::Finalize_Edge_Pairs_and_Reconstruct_3D_Edges(std::shared_p
     const size_t Ps = static_cast<size_t>(P);
     std::vector<double> gc(Ps * 3, 0.0), gw(Ps * 3, 0.0), tw(Ps * 3, 0.0), h2c(Ps * 2, 0.0);
     std::vector<int32_t> nf(Ps, 0);
-    check(cvx_finalize(gpu_, gc.data(), gw.data(), tw.data(), h2c.data(), nf.data()), "cvx_finalize");
-    check(cvx_claims_accumulate(gpu_), "cvx_claims_accumulate");   // device-side counterpart of the insertions below (:682-726)
+    if (multi()) {   // finalize kernels and claims ran on every rank inside the pass; the geometry came with the gather
+        gc = mg_gc_; gw = mg_gw_; tw = mg_tw_; h2c = mg_h2c_; nf = mg_nf_;
+    } else {
+        check(cvx_finalize(gpu_, gc.data(), gw.data(), tw.data(), h2c.data(), nf.data()), "cvx_finalize");
+        check(cvx_claims_accumulate(gpu_), "cvx_claims_accumulate");   // device-side counterpart of the insertions below (:682-726)
+    }
     const EdgeTable& E1 = All_Edgels[size_t(hyp01_view_indx)];
     const EdgeTable& E2 = All_Edgels[size_t(hyp02_view_indx)];
     Gamma1s = Matrix(0, 3); Gamma1s_world = Matrix(0, 3); tangent3Ds = Matrix(0, 3);

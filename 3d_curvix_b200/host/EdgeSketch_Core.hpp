@@ -40,6 +40,8 @@ struct Matrix {
 
 struct HostOptions {
     int device = 0;
+    std::vector<int> devices;                    // more than one: every pass is sharded by view-1 edge range over these GPUs (one context and
+                                                 // one host thread each), results gathered to the first with cvx_gather_* (NCCL)
     std::string outputs_dir = "../../outputs";   // OUTPUT_FOLDER_NAME, definitions.h:4
     std::string edge_cache_dir;                  // optional binary SoA cache of the parsed edge files
     int use_refined_poses = -1;                  // USE_REFINED_CAM_POSES (definitions.h:11): 1 / 0, -1 = refined when the files exist
@@ -111,8 +113,17 @@ private:
     std::string scene_dir() const;
 
     curvix_host::HostOptions opt_;
-    cvx_ctx* gpu_ = nullptr;
+    cvx_ctx* gpu_ = nullptr;                     // the first device: where results are gathered and the claims are read
+    std::vector<cvx_ctx*> gpus_;                 // all devices (gpus_[0] == gpu_)
+    bool multi() const { return gpus_.size() > 1; }
+    void run_sharded();                          // Run_3D_Edge_Sketch over gpus_
     bool edges_uploaded_ = false;
+    // multi-device pass: what rank 0 received (rank order = ascending view-1 edge), and every rank's cluster tables
+    std::vector<double> mg_gc_, mg_gw_, mg_tw_, mg_h2c_;
+    std::vector<int32_t> mg_nf_;
+    std::vector<int32_t> shard_bounds_;
+    std::vector<std::vector<int64_t>> rk_row_off_;
+    std::vector<std::vector<int32_t>> rk_row_n_, rk_rawat_, rk_label_;
     // per-pass host copies used by Finalize (EdgeMapping insertions) and the cluster lookup
     std::vector<int64_t> order_;                 // device pair index of every paired_edge_final row
     std::vector<int64_t> row_off_;               // first hypothesis row of every view-1 edge (-1: none)

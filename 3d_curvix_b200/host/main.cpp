@@ -3,6 +3,7 @@
 //   --outputs DIR       where 3D_edges_*.txt / 3D_tangents_*.txt go   (default ../../outputs, definitions.h:4)
 //   --dataset-path DIR  overrides the settings file's Dataset_Path
 //   --device N          CUDA device ordinal
+//   --devices 0,1,..    several GPUs: every pass sharded by view-1 edge range (balanced by hypothesis rows), results gathered over NCCL
 //   --edge-cache DIR    binary cache of the parsed edge files
 //   --max-passes N      overrides Max_Num_Of_3D_Edge_Sketch_Passes
 //   --schedule FILE     one line per pass: what was run (views, hypotheses, validations, pairs, claimed ratio, timings)
@@ -39,6 +40,11 @@ int main(int argc, char** argv) {
         else if (a == "--outputs") opt.outputs_dir = next();
         else if (a == "--dataset-path") dataset_override = next();
         else if (a == "--device") opt.device = std::atoi(next().c_str());
+        else if (a == "--devices") {   // 0,1,2,...: every pass sharded by view-1 edge range over these GPUs
+            const std::string l = next();
+            size_t b = 0;
+            while (b <= l.size()) { const size_t e = l.find(',', b); opt.devices.push_back(std::atoi(l.substr(b, e == std::string::npos ? e : e - b).c_str())); if (e == std::string::npos) break; b = e + 1; }
+        }
         else if (a == "--edge-cache") opt.edge_cache_dir = next();
         else if (a == "--max-passes") max_passes = std::atoi(next().c_str());
         else if (a == "--schedule") schedule_path = next();

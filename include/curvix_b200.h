@@ -204,16 +204,17 @@ typedef struct cvx_gathered_unit {
     const int32_t* pair_h1; const int32_t* pair_h2rep; const int32_t* pair_count; const int32_t* nan_flag;
     const int64_t* support_off; const int32_t* support_entries;
     const double* gamma_world; const double* tangent_world; const double* gamma_cam;
+    const double* h2_corrected_xy;     /* P x 2: the epipolar-corrected location of the view-2 representative (EdgeSketch_Core.cpp:636,651) */
 } cvx_gathered_unit;
 int cvx_gather_get(cvx_ctx* ctx, int round, int rank, cvx_gathered_unit* out);
 /* Host copies of a gathered unit (any pointer may be NULL; support_off n_pairs + 1 entries, support_entries 2 * n_supports); synchronises. */
 int cvx_gather_fetch(cvx_ctx* ctx, int round, int rank, int32_t* h1, int32_t* h2rep, int32_t* count, int32_t* nan_flag, int64_t* support_off,
-                     int32_t* support_entries, double* gamma_world, double* tangent_world, double* gamma_cam);
+                     int32_t* support_entries, double* gamma_world, double* tangent_world, double* gamma_cam, double* h2_corrected_xy);
 /* Same copies, enqueued on the gather's side stream behind the transfers of `round` and not waited for: the round must have been
  * handed to NCCL (any later cvx_gather_post or cvx_gather_wait did that); pinned destinations then fill while the context computes
  * its next unit.  cvx_gather_wait(ctx, x, 1) completes them. */
 int cvx_gather_fetch_async(cvx_ctx* ctx, int round, int rank, int32_t* h1, int32_t* h2rep, int32_t* count, int32_t* nan_flag, int64_t* support_off,
-                           int32_t* support_entries, double* gamma_world, double* tangent_world, double* gamma_cam);
+                           int32_t* support_entries, double* gamma_world, double* tangent_world, double* gamma_cam, double* h2_corrected_xy);
 /* Bitwise OR of the claimed-edge bitmaps of all ranks into every rank (ncclAllReduce is not defined for OR: the words are gathered
  * and OR-ed), so that cvx_claims_get_counts / next-view selection see the claims of the whole pass when a pair was sharded by
  * view-1 range.  Collective. */

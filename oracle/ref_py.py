@@ -180,6 +180,12 @@ class Reference:
         self.lib.ref_select_next_views(self.h, C.byref(b1), C.byref(b2), C.byref(avg), C.byref(ab))
         return b1.value, b2.value, avg.value, bool(ab.value)
 
+    def mapping_add_many(self, rec, image, edge_idx):
+        """rec: n x 12 doubles {X Y Z, tx ty tz, x y, ux uy utheta, 0}: EdgeMapping::add3DToSupportingEdgesMapping for every record."""
+        rec = np.ascontiguousarray(rec, np.float64).reshape(-1, 12)
+        image = np.ascontiguousarray(image, np.int32); edge_idx = np.ascontiguousarray(edge_idx, np.int32)
+        assert self.lib.ref_mapping_add_many(self.h, C.c_int64(len(rec)), _d(rec), _i(image), _i(edge_idx)) == 0
+
     def consolidate(self):
         with _run_dir():
             self.lib.ref_consolidate(self.h)

@@ -150,6 +150,21 @@ int ref_select_next_views(ref_ctx* r, int32_t* best1, int32_t* best2, double* av
     *abort_flag = c.enable_aborting_3D_edge_sketch ? 1 : 0;
     return 0;
 }
+int ref_mapping_add(ref_ctx* r, const double* e3, const double* t3, const double* se, const double* su, int image, int edge_idx) {
+    const EdgeSketch_Core& c = *r->core;
+    if (image < 0 || size_t(image) >= c.All_R.size()) return -1;
+    r->mapping->add3DToSupportingEdgesMapping(v3(e3), v3(t3), Eigen::Vector2d(se[0], se[1]), v3(su), image, edge_idx, c.All_R[size_t(image)],
+                                              c.All_T[size_t(image)]);
+    return 0;
+}
+int ref_mapping_add_many(ref_ctx* r, int64_t n, const double* rec, const int32_t* image, const int32_t* edge_idx) {
+    for (int64_t i = 0; i < n; i++) {
+        const double* q = rec + 12 * i;
+        const int rc = ref_mapping_add(r, q, q + 3, q + 6, q + 8, image[i], edge_idx[i]);
+        if (rc) return rc;
+    }
+    return 0;
+}
 int ref_consolidate(ref_ctx* r) {
     EdgeSketch_Core& c = *r->core;
     r->mapping->Setup_Data_Parameters(r->yaml);

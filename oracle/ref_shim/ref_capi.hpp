@@ -39,6 +39,12 @@ int ref_finalize(ref_ctx* r);   // Finalize_Edge_Pairs_and_Reconstruct_3D_Edges 
 int ref_clear(ref_ctx* r);      // Clear_Data
 // Calculate_Edge_Support_Ratios_And_Select_Next_Views (re-reads the edge files under dataset_path)
 int ref_select_next_views(ref_ctx* r, int32_t* best1, int32_t* best2, double* avg_ratio, int32_t* abort_flag);
+// EdgeMapping::add3DToSupportingEdgesMapping on the context's map (rotation / translation of `image` from ref_set_cameras): lets a
+// different producer of 3-D edges -- the port oracle, the CUDA path -- feed the reference's own host-side curve grouping
+int ref_mapping_add(ref_ctx* r, const double* edge_3d, const double* tangent_3d_world, const double* supporting_edge /*2*/,
+                    const double* supporting_edge_uncorrected /*3*/, int image, int edge_idx);
+// many at once: n records of 12 doubles {X Y Z, tx ty tz, x y, ux uy utheta, 0} + image[n], edge_idx[n]
+int ref_mapping_add_many(ref_ctx* r, int64_t n, const double* rec, const int32_t* image, const int32_t* edge_idx);
 // EdgeMapping::Setup_Data_Parameters + consolidate_3D_edges (writes ../../outputs/final_curves.txt etc.)
 int ref_consolidate(ref_ctx* r);
 void ref_get_times(ref_ctx* r, double* pair_edges, double* finalize, double* next_views);

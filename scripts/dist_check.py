@@ -31,13 +31,13 @@ ids = [api.EdgeSketch.comm_unique_id() if rank == 0 else None]
 tdist.broadcast_object_list(ids, src=0)
 g.comm_init(world, rank, ids[0])
 
-FIELDS = ("h1", "h2rep", "count", "nan_flag", "supports", "gamma_world", "tangent_world", "gamma_cam")
+FIELDS = ("h1", "h2rep", "count", "nan_flag", "supports", "gamma_world", "tangent_world", "gamma_cam", "h2_corrected")
 
 
 def local_results():
     p, f = g.pairs(), g.finalize()
     return dict(h1=p["h1"], h2rep=p["h2rep"], count=p["count"], nan_flag=f["nan_flag"], supports=p["supports"], gamma_world=f["gamma_world"],
-                tangent_world=f["tangent_world"], gamma_cam=f["gamma_cam"])
+                tangent_world=f["tangent_world"], gamma_cam=f["gamma_cam"], h2_corrected=f["h2_corrected"])
 
 
 # ---- (1) fixed schedule, 2 * world + 1 pairs dealt round-robin: the last round has one contributor
