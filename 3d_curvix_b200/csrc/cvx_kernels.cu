@@ -1668,7 +1668,9 @@ void launch_wedge31(const PassConst& pc, const ViewConst* vc, const double* x1, 
 #ifndef VAL_BATCH_GIVEN
 #define VAL_BATCH_GIVEN 2
 #endif
+#ifndef VAL_REGS_THREADS
 #define VAL_REGS_THREADS 1024  // resident threads per SM at 64 registers
+#endif
 #define VAL_LIGHT_ROWS 4       // row ranges a lane keeps in registers
 #ifndef VAL_COOP_MIN
 #define VAL_COOP_MIN 32        // a query becomes a whole-warp job when its work exceeds this and VAL_COOP_RATIO x the warp's mean
