@@ -1,9 +1,13 @@
 // =====================================================================================
 // cvx_math.cuh -- per-element FP64 geometry of the edge-sketch path (device functions).
 //
-// Everything here is plain IEEE double arithmetic written in the reference's operation order and
-// compiled with -fmad=false, so +,-,*,/,sqrt results are bit-identical to an un-fused CPU build;
-// only atan/asin/sin/cos/tan/exp (CUDA libdevice vs glibc, <= 2 ulp) can differ.
+// Two kinds of functions live here.  (1) The reference-order transcriptions (ore_angle, wedge_row, epipolar correction, Gaussian
+// average, reprojection, triangulation, ...): plain IEEE double arithmetic in the reference's operation order, compiled with
+// -fmad=false, so +,-,*,/,sqrt results are bit-identical to an un-fused CPU build and only atan/asin/sin/cos/tan/exp (CUDA
+// libdevice vs glibc, <= 2 ulp) can differ.  (2) wedge_row_fast, the validation kernel's default: an algebraic rewrite of
+// getOreListBar that is NOT in reference operation order (2 of its 11 libm calls remain, reciprocals shared); its bounds agree with
+// wedge_row to < 2e-12 degrees, which the parity rule absorbs like the libm difference (tests/test_device_math_host.py,
+// tests/test_gpu_parity.py::test_strict_libm_order_switch); cvx_config.strict_libm_order = 1 selects (1) in the kernel.
 // Reference citations are file:line under Edge_Reconst/ of C-H-Chien/3D_Curvix.
 //
 // The functions are __host__ __device__ only so that tests/host_harness.cpp can unit-test this
