@@ -1147,10 +1147,13 @@ __global__ void __launch_bounds__(1024) k_order_by_n(const int32_t* __restrict__
 #define RUN_NMAX CL_HUGE_N     // rows of an edge
 #define RUN_SHORT 32           // rows of a run handled by one warp in registers
 #define RUN_WARPS 8
+#define RUN_START_FLAG (1 << 30)   // run_ord entry: first row of a run inside its pack
 struct RunPrepSm {
     double key[RUN_NMAX];                  // position along the epipolar line (sort key); reused as scratch afterwards
     int16_t ord[RUN_NMAX];                 // rows sorted by key; then, run by run, by ascending row index
     int16_t start[RUN_NMAX + 1];           // first sorted position of every run
+    int16_t pbase[RUN_NMAX];               // short runs: first position in the edge's compacted list of pack rows
+    int2 pack[RUN_NMAX / 2];               // packs of the edge: (first compacted position, rows)
     int wcnt[RUN_WARPS];
     int bad, n_long, n_short, rows_long, base_long, base_short, base_rows;
     double lineA, lineB, lineC, lineInv;
@@ -1227,13 +1230,25 @@ __global__ void __launch_bounds__(RUN_WARPS * 32) k_runs_prepare(const __grid_co
         if (tid == 0) s.start[run_total] = int16_t(n);
         __syncthreads();
         {
-            int nl = 0, ns = 0, rl = 0;
+            int nl = 0, rl = 0;
             for (int r = tid; r < run_total; r += blockDim.x) {
                 const int c = s.start[r + 1] - s.start[r];
-                if (c > RUN_SHORT) { nl++; rl += c; } else if (c > 1) ns++;
+                if (c > RUN_SHORT) { nl++; rl += c; }
             }
             if (nl) { atomicAdd(&s.n_long, nl); atomicAdd(&s.rows_long, rl); }
-            if (ns) atomicAdd(&s.n_short, ns);
+        }
+        if (tid == 0) {
+            // packs: consecutive short runs (2 .. RUN_SHORT rows; single rows and long runs are skipped) while they fit one warp
+            int pos = 0, p0 = 0, prow = 0, np = 0;
+            for (int r = 0; r < run_total; r++) {
+                const int c = s.start[r + 1] - s.start[r];
+                if (c < 2 || c > RUN_SHORT) continue;
+                if (prow + c > RUN_SHORT) { s.pack[np++] = make_int2(p0, prow); p0 = pos; prow = 0; }
+                s.pbase[r] = int16_t(pos);
+                pos += c; prow += c;
+            }
+            if (prow) s.pack[np++] = make_int2(p0, prow);
+            s.n_short = np;
         }
         __syncthreads();
         if (tid == 0) {
@@ -1241,7 +1256,7 @@ __global__ void __launch_bounds__(RUN_WARPS * 32) k_runs_prepare(const __grid_co
             s.base_short = s.n_short ? atomicAdd(&rs.ctr[1], s.n_short) : 0;
             s.base_rows = s.rows_long ? atomicAdd(&rs.ctr[2], s.rows_long) : 0;
             if (s.base_long + s.n_long > rs.cap_long || int64_t(s.base_rows) + s.rows_long > rs.cap_rows) s.bad = 1;   // cannot happen with the sizes of cvx_api.cu
-            s.n_long = 0; s.n_short = 0; s.rows_long = 0;
+            s.n_long = 0; s.rows_long = 0;
         }
         int16_t* tmp = reinterpret_cast<int16_t*>(s.key);                // the keys are dead from here on
         for (int k = tid; k < n; k += blockDim.x) tmp[k] = s.ord[k];
@@ -1273,36 +1288,88 @@ __global__ void __launch_bounds__(RUN_WARPS * 32) k_runs_prepare(const __grid_co
                     rs.vrt.xc[q] = rt.xc[row0 + mine]; rs.vrt.yc[q] = rt.yc[row0 + mine]; rs.vrt.th[q] = rt.th[row0 + mine];
                     rs.vrt.h2orig[q] = rt.h2orig[row0 + mine]; rs.v_oi[q] = mine;
                 } else {
-                    run_ord[row0 + s0 + rk] = mine;
+                    run_ord[row0 + s.pbase[r] + rk] = mine | (rk == 0 ? RUN_START_FLAG : 0);
                 }
             }
-            if (lane == 0) {
-                if (c > RUN_SHORT) { rs.desc_long[vid] = make_int4(h1, voff, c, 0); rs.v_n[vid] = c; rs.v_off[vid] = voff; }
-                else rs.desc_short[s.base_short + atomicAdd(&s.n_short, 1)] = make_int4(h1, s0, c, 0);
-            }
+            if (lane == 0 && c > RUN_SHORT) { rs.desc_long[vid] = make_int4(h1, voff, c, 0); rs.v_n[vid] = c; rs.v_off[vid] = voff; }
         }
+        for (int k = tid; k < s.n_short; k += blockDim.x) rs.desc_short[s.base_short + k] = make_int4(h1, s.pack[k].x, s.pack[k].y, 0);
         if (tid == 0) n_clusters[h1] = 0;                                 // marks "clustered by runs" for k_runs_finish
     }
 }
-// One run of c <= 32 rows, lane k = local row k (ascending row index).  Coordinates, labels and the adjacency word live in registers;
-// the per-label orientation and size in shared memory (indexed by local label); neighbours are read through shuffles in a
-// warp-uniform loop over the run.
+// A PACK of short runs of one view-1 edge: up to 32 rows, lane k = row k of the pack, every run a contiguous SEGMENT of lanes in ascending
+// row order.  Runs are independent (no pair of rows of different runs is within the distance threshold), so every segment performs its own
+// next merge of the reference's scan in the same step of the loop below, and all clusters of the pack are averaged at once at the end:
+// the step count is the largest merge count of a run instead of the sum over the runs.  Sums over the members of a cluster run in ascending
+// member order on every lane of that cluster (the reference's left-to-right chain), members read through shuffles from a per-lane source.
 struct RunWarpSm {
-    double x[RUN_SHORT], y[RUN_SHORT], thn[RUN_SHORT], orient[RUN_SHORT];
-    int16_t size[RUN_SHORT], mem[32];
+    double x[RUN_SHORT], y[RUN_SHORT], orient[RUN_SHORT];   // row location; per-label averaged orientation (label = lane of the cluster's first row)
+    int16_t size[RUN_SHORT];
 };
-__device__ void cluster_run_warp(RunWarpSm& s, int c, int oi, const PassConst& pc, const int32_t* __restrict__ h2orig, double* xbar, double* ybar,
-                                 double* thbar, int32_t* h2rep, int32_t* label_out, int lane) {
-    const unsigned lt = lanemask_lt();
-    const bool me = lane < c;
-    const double xi = s.x[lane], yi = s.y[lane];
+// sum of v over the lanes of mask m in ascending lane order, on every lane for its own mask; steps = warp-wide largest member count
+__device__ __forceinline__ double seg_sum(double v, unsigned m, int steps, int lane) {
+    double acc = 0.0;
+    for (int it = 0; it < steps; it++) {
+        const bool has = m != 0u;
+        const int src = has ? __ffs(m) - 1 : lane;
+        m &= m - 1u;
+        const double t = shfl_d(v, src);
+        if (has) acc += t;
+    }
+    return acc;
+}
+// EdgeClusterer.cpp:60-125 for the cluster whose member lanes are mm (cnt = popc(mm)), evaluated by every lane for its own cluster
+template <bool ORIENT_ONLY>
+__device__ __forceinline__ void gauss_avg_seg(unsigned mm, int cnt, int steps, double xi, double yi, double ti, double sigma, double sigma_inv, int lane,
+                                              double* gx, double* gy, double* gth) {
+    const int c1 = max(cnt, 1);
+    const double sx = seg_sum(xi, mm, steps, lane), sy = seg_sum(yi, mm, steps, lane);
+    const bool p2 = (c1 & (c1 - 1)) == 0;                                       // see gauss_avg_list_t
+    const double ic = __hiloint2double((1023 - (31 - __clz(c1))) << 20, 0);
+    const double cx = p2 ? sx * ic : sx / c1, cy = p2 ? sy * ic : sy / c1;
+    const double dx = xi - cx, dy = yi - cy;
+    const double di = sqrt(dx * dx + dy * dy);
+    const double tot = seg_sum(di, mm, steps, lane);
+    const double mean_shift = p2 ? tot * ic : tot / c1;
+    const double q = sigma_inv != 0.0 ? (di - mean_shift) * sigma_inv : (di - mean_shift) / sigma;
+    const double w = exp(-0.5 * (q * q));
+    const double wo = w * ti;
+    double swo = 0.0, tw = 0.0, swx = 0.0, swy = 0.0;
+    const double wx = w * xi, wy = w * yi;
+    unsigned m = mm;
+    for (int it = 0; it < steps; it++) {
+        const bool has = m != 0u;
+        const int src = has ? __ffs(m) - 1 : lane;
+        m &= m - 1u;
+        const double a = shfl_d(wo, src), b = shfl_d(w, src);
+        if (has) { swo += a; tw += b; }
+        if (!ORIENT_ONLY) {
+            const double c = shfl_d(wx, src), d = shfl_d(wy, src);
+            if (has) { swx += c; swy += d; }
+        }
+    }
+    if (!ORIENT_ONLY) { *gx = swx / tw; *gy = swy / tw; }
+    *gth = swo / tw;
+}
+__device__ void cluster_pack_warp(RunWarpSm& s, int nrows, bool run_start, int oi, double xi, double yi, double thn, const PassConst& pc,
+                                  const int32_t* __restrict__ h2orig, double* xbar, double* ybar, double* thbar, int32_t* h2rep, int32_t* label_out,
+                                  int lane) {
+    const bool me = lane < nrows;
+    // my run: lanes [lo, hi)
+    const unsigned starts = __ballot_sync(FULL, me && run_start) | 1u;
+    const unsigned le = lanemask_lt() | (1u << lane);
+    const int lo = 31 - __clz(starts & le);
+    const unsigned above = starts & ~le;
+    const int hi = above ? __ffs(above) - 1 : nrows;
+    const unsigned segmask = me ? (((hi >= 32) ? 0xffffffffu : ((1u << hi) - 1u)) & ~((1u << lo) - 1u)) : 0u;
     uint32_t adj = 0u;
-    for (int j = 0; j < c; j++) {
+    for (int j = 0; j < nrows; j++) {
         const double ddx = xi - s.x[j], ddy = yi - s.y[j];
         if (ddx * ddx + ddy * ddy < pc.cl_dist_sq && j != lane) adj |= 1u << j;   // == sqrt(.) < cl_dist, see cl_dist_sq
     }
-    if (!me) adj = 0u;
+    adj &= segmask;
     int label = lane;
+    const int maxdeg = __reduce_max_sync(FULL, __popc(adj));
     while (true) {
         // would my row merge now?  (EdgeClusterer.cpp:143-166; nearest row of another cluster, first minimum in ascending row order)
         int partner = -1;
@@ -1310,9 +1377,8 @@ __device__ void cluster_run_warp(RunWarpSm& s, int c, int oi, const PassConst& p
             const double o_i = s.orient[label];
             double bd = DBL_MAX, bs = DBL_MAX;
             uint32_t bits = adj;
-            const int maxdeg = __reduce_max_sync(FULL, __popc(adj));      // every lane walks its own neighbours, in step (the label of a
-            for (int it = 0; it < maxdeg; it++) {                         // neighbour is read from its lane: the shuffle needs all lanes)
-                const bool has = bits != 0u;
+            for (int it = 0; it < maxdeg; it++) {                         // every lane walks its own neighbours, in step (a neighbour's label
+                const bool has = bits != 0u;                              // is read from its lane: the shuffle needs all lanes)
                 const int j = has ? __ffs(bits) - 1 : lane;
                 bits &= bits - 1u;
                 const int lj = __shfl_sync(FULL, label, j);
@@ -1326,60 +1392,57 @@ __device__ void cluster_run_warp(RunWarpSm& s, int c, int oi, const PassConst& p
                 }
             }
         }
-        const int lpartner = __shfl_sync(FULL, label, partner >= 0 ? partner : 0);
+        const int lpartner = __shfl_sync(FULL, label, partner >= 0 ? partner : lane);
         if (partner >= 0 && int(s.size[lpartner]) + int(s.size[label]) > pc.max_cluster) partner = -1;   // :166
         const unsigned can = __ballot_sync(FULL, partner >= 0);
         if (!can) break;
-        const int mi = __ffs(can) - 1;
-        const int mj = __shfl_sync(FULL, partner, mi);
+        // the next merge of MY run: its first row that can merge (the row the reference's restarted scan reaches first)
+        const unsigned cseg = can & segmask;
+        const bool act = cseg != 0u;
+        const int mi = act ? __ffs(cseg) - 1 : lane;
+        const int pj = __shfl_sync(FULL, partner, mi);
+        const int mj = act ? pj : lane;
         const int new_l = __shfl_sync(FULL, label, mi), old_l = __shfl_sync(FULL, label, mj);
-        const bool in = me && (label == old_l || label == new_l);
-        const unsigned mm = __ballot_sync(FULL, in);
-        const int cnt = min(__popc(mm), 32);
-        if (in) s.mem[__popc(mm & lt)] = int16_t(lane);
-        __syncwarp();
+        const bool in = act && (label == old_l || label == new_l);
+        const unsigned mm = __ballot_sync(FULL, in) & segmask;           // members of the merged cluster of my run (0: my run rests)
+        const int cnt = __popc(mm);
+        const int steps = __reduce_max_sync(FULL, cnt);
         double gx, gy, gth;
-        gauss_avg_list_t<RunWarpSm, true>(s, s.mem, cnt, pc.cl_sigma, pc.cl_sigma_inv, lane, &gx, &gy, &gth);     // :168
+        gauss_avg_seg<true>(mm, cnt, steps, xi, yi, thn, pc.cl_sigma, pc.cl_sigma_inv, lane, &gx, &gy, &gth);   // :168
         __syncwarp();
-        if (lane == 0) { s.orient[new_l] = normalize_orientation(gth, pc.cl_wrap_deg); s.size[new_l] = int16_t(cnt); }   // :175-176
-        if (label == old_l) label = new_l;                                // :179-183
+        if (act && lane == new_l) { s.orient[new_l] = normalize_orientation(gth, pc.cl_wrap_deg); s.size[new_l] = int16_t(cnt); }   // :175-176
+        if (act && label == old_l) label = new_l;                         // :179-183
         __syncwarp();
     }
-    // :250-290 per cluster: Gaussian-weighted average written to every member, representative = member closest to it
-    const int my_size = s.size[label];
+    // :250-290 every cluster at once: Gaussian-weighted average written to every member, representative = member closest to it
+    const unsigned cm = __match_any_sync(FULL, me ? label : 32 + lane);
+    const int cnt = me ? __popc(cm) : 0;
+    const int steps = __reduce_max_sync(FULL, cnt);
     const int label_row = __shfl_sync(FULL, oi, label);                   // row (within the edge) of the label
+    double gx = xi, gy = yi, gth = thn;
+    int rep_oi = oi;
+    if (steps > 1) {
+        double ax, ay, ath;
+        gauss_avg_seg<false>(cm, cnt, steps, xi, yi, thn, pc.cl_sigma, pc.cl_sigma_inv, lane, &ax, &ay, &ath);
+        const double ddx = xi - ax, ddy = yi - ay;
+        const double d = sqrt(ddx * ddx + ddy * ddy);
+        double best = DBL_MAX;
+        int rep = lane;
+        unsigned m = cm;
+        for (int it = 0; it < steps; it++) {                              // first minimum in member order (:270)
+            const bool has = m != 0u;
+            const int src = has ? __ffs(m) - 1 : lane;
+            m &= m - 1u;
+            const double dv = shfl_d(d, src);
+            if (has && dv < best) { best = dv; rep = src; }
+        }
+        const int r_oi = __shfl_sync(FULL, oi, rep);
+        if (cnt > 1) { gx = ax; gy = ay; gth = ath; rep_oi = r_oi; }
+    }
     if (me) {
         label_out[oi] = label_row;
-        if (my_size == 1) { xbar[oi] = xi; ybar[oi] = yi; thbar[oi] = s.thn[lane]; h2rep[oi] = h2orig[oi]; }
-    }
-    unsigned roots = __ballot_sync(FULL, me && label == lane && my_size > 1);
-    while (roots) {
-        const int root = __ffs(roots) - 1;
-        roots &= roots - 1;
-        const bool in = me && label == root;
-        const unsigned mm = __ballot_sync(FULL, in);
-        const int cnt = min(__popc(mm), 32);
-        if (in) s.mem[__popc(mm & lt)] = int16_t(lane);
-        __syncwarp();
-        double gx, gy, gth;
-        gauss_avg_list_t<RunWarpSm, false>(s, s.mem, cnt, pc.cl_sigma, pc.cl_sigma_inv, lane, &gx, &gy, &gth);
-        double d = DBL_MAX;
-        int pos = lane;
-        if (lane < cnt) {
-            const int j = s.mem[lane];
-            const double ddx = s.x[j] - gx, ddy = s.y[j] - gy;
-            d = sqrt(ddx * ddx + ddy * ddy);
-        }
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {                                // first minimum in member order (:270)
-            const double od = __shfl_xor_sync(FULL, d, o);
-            const int op = __shfl_xor_sync(FULL, pos, o);
-            if (od < d || (od == d && op < pos)) { d = od; pos = op; }
-        }
-        const int rep_lane = s.mem[pos];
-        const int rep = h2orig[__shfl_sync(FULL, oi, rep_lane)];          // corrected(closest, 8), :282
-        if (in) { xbar[oi] = gx; ybar[oi] = gy; thbar[oi] = gth; h2rep[oi] = rep; }
-        __syncwarp();
+        xbar[oi] = gx; ybar[oi] = gy; thbar[oi] = gth;
+        h2rep[oi] = h2orig[rep_oi];                                       // corrected(closest, 8), :282
     }
 }
 __global__ void __launch_bounds__(RUN_WARPS * 32, 4) k_runs_cluster(const __grid_constant__ PassConst pc, const int64_t* __restrict__ row_off,
@@ -1387,24 +1450,27 @@ __global__ void __launch_bounds__(RUN_WARPS * 32, 4) k_runs_cluster(const __grid
     __shared__ RunWarpSm sm[RUN_WARPS];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     RunWarpSm& s = sm[warp];
-    const int n_short = rs.ctr[1];
+    const int n_packs = rs.ctr[1];
     const int32_t* run_ord = rt.urank;
     const int stride = gridDim.x * RUN_WARPS;
-    for (int r = blockIdx.x * RUN_WARPS + warp; r < n_short; r += stride) {
-        const int4 d = rs.desc_short[r];
+    for (int r = blockIdx.x * RUN_WARPS + warp; r < n_packs; r += stride) {
+        const int4 d = rs.desc_short[r];                                  // (view-1 edge, first compacted position, rows)
         const int64_t row0 = row_off[d.x];
         const int c = d.z;
         __syncwarp();
         int oi = 0;
+        bool start = false;
+        double xi = 0.0, yi = 0.0, t = 0.0;
         if (lane < c) {
-            oi = run_ord[row0 + d.y + lane];
-            const double t = normalize_orientation(rt.th[row0 + oi], pc.cl_wrap_deg);   // :131-135
-            s.x[lane] = rt.xc[row0 + oi]; s.y[lane] = rt.yc[row0 + oi]; s.thn[lane] = t; s.orient[lane] = t; s.size[lane] = 1;
-        } else {
-            s.x[lane] = 0.0; s.y[lane] = 0.0; s.thn[lane] = 0.0; s.orient[lane] = 0.0; s.size[lane] = 0;
+            const int e = run_ord[row0 + d.y + lane];
+            oi = e & (RUN_START_FLAG - 1); start = (e & RUN_START_FLAG) != 0;
+            t = normalize_orientation(rt.th[row0 + oi], pc.cl_wrap_deg);   // :131-135
+            xi = rt.xc[row0 + oi]; yi = rt.yc[row0 + oi];
         }
+        s.x[lane] = xi; s.y[lane] = yi; s.orient[lane] = t; s.size[lane] = lane < c ? 1 : 0;
         __syncwarp();
-        cluster_run_warp(s, c, oi, pc, rt.h2orig + row0, rt.xbar + row0, rt.ybar + row0, rt.thbar + row0, rt.h2rep + row0, rt.label + row0, lane);
+        cluster_pack_warp(s, c, start, oi, xi, yi, t, pc, rt.h2orig + row0, rt.xbar + row0, rt.ybar + row0, rt.thbar + row0, rt.h2rep + row0,
+                          rt.label + row0, lane);
     }
 }
 // results of the long runs (virtual edges of the scratch table) back to their rows: warp per run
