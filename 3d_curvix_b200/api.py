@@ -21,6 +21,8 @@ SYMBOLS = [
     "cvx_gather_post", "cvx_gather_wait", "cvx_gather_get", "cvx_gather_fetch", "cvx_gather_fetch_async", "cvx_gather_stats",
     "cvx_support_problem_create", "cvx_support_problem_run", "cvx_support_problem_stats", "cvx_support_problem_result",
     "cvx_support_problem_destroy",
+    "cvx_graph_create", "cvx_graph_build_links", "cvx_graph_prune", "cvx_graph_get_links", "cvx_graph_get_link_details", "cvx_graph_get_neighbors",
+    "cvx_graph_set_neighbors", "cvx_graph_align", "cvx_graph_destroy",
 ]
 
 
@@ -89,6 +91,16 @@ def load():
     lib.cvx_support_problem_stats.argtypes = [C.c_void_p] + [C.POINTER(C.c_int64)] * 4
     lib.cvx_support_problem_result.argtypes = [C.c_void_p, C.c_void_p]
     lib.cvx_support_problem_destroy.argtypes = [C.c_void_p]
+    lib.cvx_graph_create.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.POINTER(C.c_void_p)]
+    lib.cvx_graph_build_links.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.POINTER(C.c_int64)]
+    lib.cvx_graph_prune.argtypes = [C.c_void_p, C.c_double, C.c_double, C.c_double, C.c_double, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,
+                                    C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
+    lib.cvx_graph_get_links.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.POINTER(C.c_int64)]
+    lib.cvx_graph_get_link_details.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.cvx_graph_get_neighbors.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.cvx_graph_set_neighbors.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.cvx_graph_align.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_double, C.c_double, C.c_void_p, C.c_void_p, C.POINTER(C.c_float)]
+    lib.cvx_graph_destroy.argtypes = [C.c_void_p]
     lib.cvx_gather_post.argtypes = [C.c_void_p, C.c_int64, C.c_int]
     lib.cvx_gather_wait.argtypes = [C.c_void_p, C.c_int, C.c_int]
     lib.cvx_gather_get.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(CvxGatheredUnit)]
@@ -387,6 +399,72 @@ class EdgeSketch:
         r = CvxDeviceResults()
         self._ck(self.lib.cvx_get_device_results(self.h, C.byref(r)))
         return r
+
+
+class EdgeGraph:
+    """The 3-D edge graph of EdgeMapping::consolidate_3D_edges on the device (SURVEY.md 8 f3): links from curvelets, the two prunings, neighbour
+    lists, the alignment iterations.  Nodes are the caller's numbering of the distinct 3-D edges."""
+
+    def __init__(self, sketch, location, first_tangent):
+        self.sk, self.lib = sketch, sketch.lib
+        self.loc = np.ascontiguousarray(location, np.float64).reshape(-1, 3)
+        self.t0 = np.ascontiguousarray(first_tangent, np.float64).reshape(-1, 3)
+        self.n = len(self.loc)
+        self.p = C.c_void_p()
+        sketch._ck(self.lib.cvx_graph_create(sketch.h, self.n, _vp(self.loc), _vp(self.t0), C.byref(self.p)))
+
+    def build_links(self, key_off, key_nodes, cv_self, cv_neighbor):
+        ko = np.ascontiguousarray(key_off, np.int64); kn = np.ascontiguousarray(key_nodes, np.int32)
+        a = np.ascontiguousarray(cv_self, np.int32); b = np.ascontiguousarray(cv_neighbor, np.int32)
+        n = C.c_int64(0)
+        self.sk._ck(self.lib.cvx_graph_build_links(self.p, len(ko) - 1, _vp(ko), _vp(kn), len(a), _vp(a), _vp(b), C.byref(n)))
+        return int(n.value)
+
+    def prune(self, R, T, K, lambda1=1.0, lambda2=1.0, lambda3=1.0, proj_thresh=6.0):
+        R = np.ascontiguousarray(R, np.float64).reshape(-1, 9); T = np.ascontiguousarray(T, np.float64).reshape(-1, 3)
+        K = np.ascontiguousarray(np.asarray(K, np.float64).reshape(-1)[:9])
+        st = np.zeros(6); n1 = C.c_int64(0); n2 = C.c_int64(0)
+        self.sk._ck(self.lib.cvx_graph_prune(self.p, lambda1, lambda2, lambda3, proj_thresh, len(R), _vp(R), _vp(T), _vp(K), _vp(st), C.byref(n1), C.byref(n2)))
+        return dict(mu_t=st[0], sigma_t=st[1], mu_n=st[2], sigma_n=st[3], mu_theta=st[4], sigma_theta=st[5], n_after_3d=int(n1.value), n_after_projection=int(n2.value))
+
+    def links(self, stage):
+        n = C.c_int64(0)
+        self.sk._ck(self.lib.cvx_graph_get_links(self.p, stage, None, None, C.byref(n)))
+        a = np.zeros(max(n.value, 1), np.int32); b = np.zeros(max(n.value, 1), np.int32)
+        self.sk._ck(self.lib.cvx_graph_get_links(self.p, stage, _vp(a), _vp(b), C.byref(n)))
+        return a[:n.value], b[:n.value]
+
+    def link_details(self):
+        n = len(self.links(0)[0])
+        pos = np.zeros(max(n, 1), np.int64); k3 = np.zeros(max(n, 1), np.uint8); kp = np.zeros(max(n, 1), np.uint8)
+        self.sk._ck(self.lib.cvx_graph_get_link_details(self.p, _vp(pos), _vp(k3), _vp(kp)))
+        return pos[:n], k3[:n].astype(bool), kp[:n].astype(bool)
+
+    def neighbors(self, n_links2):
+        off = np.zeros(self.n + 1, np.int64); nb = np.zeros(max(2 * n_links2, 1), np.int32)
+        self.sk._ck(self.lib.cvx_graph_get_neighbors(self.p, _vp(off), _vp(nb)))
+        return off, nb[:off[-1]]
+
+    def set_neighbors(self, off, nb):
+        off = np.ascontiguousarray(off, np.int64); nb = np.ascontiguousarray(nb, np.int32)
+        self.sk._ck(self.lib.cvx_graph_set_neighbors(self.p, _vp(off), _vp(nb)))
+
+    def align(self, orientation, iterations=1000, step_force=0.01, step_torque=0.01):
+        o = np.ascontiguousarray(orientation, np.float64).reshape(-1, 3)
+        lo = np.zeros((self.n, 3)); oo = np.zeros((self.n, 3)); ms = C.c_float(0)
+        self.sk._ck(self.lib.cvx_graph_align(self.p, _vp(o), iterations, step_force, step_torque, _vp(lo), _vp(oo), C.byref(ms)))
+        return lo, oo, float(ms.value)
+
+    def close(self):
+        if self.p:
+            self.lib.cvx_graph_destroy(self.p)
+            self.p = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
 
 class SupportProblem:

@@ -34,7 +34,7 @@ def _cxx():
 
 
 def build_cuda(force=False, verbose=False):
-    srcs = [os.path.join(CSRC, f) for f in ("cvx_kernels.cu", "cvx_api.cu", "cvx_comm.cu")]
+    srcs = [os.path.join(CSRC, f) for f in ("cvx_kernels.cu", "cvx_api.cu", "cvx_comm.cu", "cvx_graph.cu")]
     deps = srcs + [os.path.join(CSRC, f) for f in ("cvx_kernels.cuh", "cvx_math.cuh", "cvx_internal.h")] + [os.path.join(ROOT, "include", "curvix_b200.h")]
     if not force and not _stale(LIB, deps):
         return LIB
@@ -52,7 +52,7 @@ def build_cuda(force=False, verbose=False):
 def build_host(force=False):
     """C++ host drop-in (EdgeSketch_Core shim + curvix_main) linked against libcurvix_b200.so."""
     hdir = os.path.join(HERE, "host")
-    srcs = [os.path.join(hdir, f) for f in ("EdgeSketch_Core.cpp", "main.cpp")]
+    srcs = [os.path.join(hdir, f) for f in ("EdgeSketch_Core.cpp", "edge_mapping.cpp", "main.cpp")]
     if not all(os.path.exists(s) for s in srcs):
         return None
     deps = srcs + [os.path.join(hdir, f) for f in os.listdir(hdir) if f.endswith(".hpp")]

@@ -48,7 +48,26 @@ class Scene:
             np.savetxt(os.path.join(base, "Edges", f"Edge_{i}_t{thresh}.txt"), e, fmt="%.17g", delimiter="\t")
         np.savetxt(os.path.join(base, "RnT", "R_matrix.txt"), self.R.reshape(-1, 3), fmt="%.17g", delimiter="\t")
         np.savetxt(os.path.join(base, "RnT", "T_matrix.txt"), self.T.reshape(-1, 1), fmt="%.17g")
+        cv = getattr(self, "curvelets", None)
+        if cv is not None:   # curvelets/Curvelets_<i>_t<thr>.txt: 4 ints per line (file_reader.cpp:81-110 reads them as a stream of triples)
+            os.makedirs(os.path.join(base, "curvelets"), exist_ok=True)
+            for i, c in enumerate(cv):
+                np.savetxt(os.path.join(base, "curvelets", f"Curvelets_{i}_t{thresh}.txt"), np.asarray(c, np.int64).reshape(-1, 4), fmt="%d")
         return base
+
+    def load_curvelets(self, path):
+        """Attach the curvelet files of the scene (npz made by tests/golden/make_abc_fixture.py): per view a flat int stream."""
+        z = np.load(path)
+        off = np.concatenate([[0], np.cumsum(z["counts"])])
+        self.curvelets = [z["flat"][off[i]:off[i + 1]] for i in range(len(off) - 1)]
+        return self
+
+    def curvelet_triples(self, view):
+        """(self edge, neighbour edge) per record as the reference's reader forms them: the int stream in triples, third value unused."""
+        f = np.asarray(self.curvelets[view], np.int64)
+        n = len(f) // 3
+        t = f[:3 * n].reshape(n, 3)
+        return t[:, 0].astype(np.int32), t[:, 1].astype(np.int32)
 
 
 def read_reference_scene(scene_dir, n_views, fx, fy, cx, cy, rows, cols, thresh=1, refined=False):

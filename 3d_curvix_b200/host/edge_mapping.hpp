@@ -1,19 +1,27 @@
-// edge_mapping.hpp -- the consumer-side interface of the edge-sketch path, host only.
+// edge_mapping.hpp -- the consumer of the edge-sketch path in the drop-in: the 3-D edge -> supporting 2-D edges table and the grouping of
+// the 3-D edges into curves, with the reference's class and member names (Edge_Reconst/edge_mapping.{hpp,cpp}).
 //
-// In the reference, EdgeMapping (Edge_Reconst/edge_mapping.{hpp,cpp}, 1.5 kLoC) receives every reconstructed 3-D edge
-// with its supporting 2-D edges through add3DToSupportingEdgesMapping (edge_mapping.cpp:20-33, called from
-// EdgeSketch_Core.cpp:682-726) and later groups them into curves (consolidate_3D_edges -> final_curves.txt).  The curve
-// grouping stays host code of the reference and is out of scope here (BASELINE.json north_star).
-// What the path itself needs from this class is the insertion API and the 3-D edge -> supporting edges table that
-// Calculate_Edge_Support_Ratios_And_Select_Next_Views walks (EdgeSketch_Core.cpp:785-797); this header provides exactly
-// that, with the reference's member names, so that the drop-in EdgeSketch_Core below compiles against either class.
+//   add3DToSupportingEdgesMapping   edge_mapping.cpp:20-33     host (insertions from Finalize_Edge_Pairs_and_Reconstruct_3D_Edges, :682-726)
+//   consolidate_3D_edges            edge_mapping.cpp:1056-1088 the data-parallel front half on the DEVICE through the C-ABI (cvx_graph_*: links from
+//                                   curvelets, the two prunings, the alignment iterations; csrc/cvx_graph.cu), the order-dependent back half
+//                                   (connectivity graph, curve tracing, merging, writers: :639-1164) on the host, edge_mapping.cpp of this directory
+//
+// The reference keys its maps on the exact doubles of a 3-D point and several of its stages depend on the ITERATION ORDER of those
+// unordered_maps (node numbering, neighbour order, the order in which curves are traced).  The drop-in reproduces those orders by keeping the
+// same kind of container with the same hash (value of std::hash<double> combined as HashEigenVector3d / HashEigenVector3dPair do,
+// edge_mapping.hpp:18-52) and the same insertion sequence, so that on identical inputs the nodes, neighbour lists and curves carry the
+// reference's indices and the output files can be compared line by line.
 #pragma once
 #include <cstdint>
 #include <cstdio>
 #include <cstring>
+#include <functional>
 #include <string>
 #include <unordered_map>
 #include <vector>
+
+struct cvx_ctx;
+namespace curvix_host { class FlatYaml; }
 
 class EdgeMapping {
 public:
@@ -28,13 +36,19 @@ public:
         double point[3];
         std::vector<SupportingEdgeData> supports;
     };
+    struct ConsolidationReport {      // what consolidate_3D_edges did (printed by curvix_main, read by the tests)
+        int64_t nodes = 0, records = 0, curvelets = 0, links = 0, links_after_3d = 0, links_after_projection = 0;
+        int64_t curves_from_graph = 0, final_curves = 0;
+        double stats[6] = {0, 0, 0, 0, 0, 0};   // mu_t, sigma_t, mu_n, sigma_n, mu_theta, sigma_theta (edge_mapping.cpp:291-294)
+        double graph_s = 0, align_s = 0, align_kernel_ms = 0, curves_s = 0, total_s = 0;
+    };
 
     // Same role and argument order as the reference method (rotation / translation of the image are a function of
     // image_number and are not stored again per record).
     void add3DToSupportingEdgesMapping(const double edge_3D[3], const double tangents_3D_world[3], const double supporting_edge[2],
                                        const double supporting_edge_uncorrected[3], int image_number, int edge_idx) {
         Key k;
-        std::memcpy(k.bits, edge_3D, 24);
+        std::memcpy(k.v, edge_3D, 24);
         auto it = index_.find(k);
         size_t slot;
         if (it == index_.end()) {   // the reference keys its unordered_map on the exact doubles of the 3-D point
@@ -54,8 +68,14 @@ public:
         edge_3D_to_supporting_edges[slot].supports.push_back(d);
     }
 
-    // 3-D edges in first-insertion order (the reference iterates an unordered_map; consumers must not rely on order).
+    // 3-D edges in first-insertion order; reference_order() lists them in the iteration order of the reference's map
     std::vector<Edge3D> edge_3D_to_supporting_edges;
+    std::vector<size_t> reference_order() const {
+        std::vector<size_t> o;
+        o.reserve(index_.size());
+        for (const auto& kv : index_) o.push_back(kv.second);
+        return o;
+    }
 
     size_t num_3D_edges() const { return edge_3D_to_supporting_edges.size(); }
     size_t num_support_links() const {
@@ -64,28 +84,43 @@ public:
         return n;
     }
 
-    // One line per link: X Y Z  image edge_idx  x y  tx ty tz   (input of the reference's host-side curve grouping)
-    bool write_support_links(const std::string& path) const {
-        FILE* f = std::fopen(path.c_str(), "w");
-        if (!f) return false;
-        for (const auto& e : edge_3D_to_supporting_edges)
-            for (const auto& s : e.supports)
-                std::fprintf(f, "%.17g %.17g %.17g %d %d %.17g %.17g %.17g %.17g %.17g\n", e.point[0], e.point[1], e.point[2], s.image_number,
-                             s.edge_idx, s.edge[0], s.edge[1], s.tangents_3D_world[0], s.tangents_3D_world[1], s.tangents_3D_world[2]);
-        return std::fclose(f) == 0;
+    // One line per link: X Y Z  image edge_idx  x y  tx ty tz  ux uy utheta (input of consolidate_3D_edges; read_support_links restores it)
+    bool write_support_links(const std::string& path) const;
+    bool read_support_links(const std::string& path);
+
+    // EdgeMapping::Setup_Data_Parameters (edge_mapping.cpp:64-70)
+    void Setup_Data_Parameters(const curvix_host::FlatYaml& settings);
+    // EdgeMapping::consolidate_3D_edges (edge_mapping.cpp:1056-1088).  all_R n x 9 row-major, all_T n x 3, K 9; files go to outputs_dir
+    // (the reference's ../../outputs): 3D_edges_before_smoothing.txt, 3D_edges_after_smoothing.txt, pruned_graph_aligned.txt,
+    // connectivity_graph.txt, curve_indices_for_merging.txt, curves_from_connectivity_graph.txt, final_curves.txt and, with
+    // write_edge_graphs, the three 3D_edge*graph*.txt files of WRITE_3D_EDGE_GRAPH (definitions.h:9).
+    bool consolidate_3D_edges(cvx_ctx* gpu, const std::vector<double>& all_R, const std::vector<double>& all_T, const double K[9],
+                              int Num_Of_Total_Imgs, const std::string& outputs_dir, bool write_edge_graphs = true, bool quiet = false);
+    ConsolidationReport report;
+    std::string last_error;
+
+    // parameters of the reference's definitions.h:28-38 (compile-time there)
+    double prune_lambda1 = 1, prune_lambda2 = 1, prune_lambda3 = 1, prune_by_proj_prox_thresh = 6;
+    int num_of_iterations = 1000;
+    double init_force_step_size = 0.01, init_torque_step_size = 0.01;
+
+    int thresh_EDG = 1, Num_Of_Images = 0;
+    std::string Dataset_Path, Dataset_Name, Scene_Name;
+
+    // HashEigenVector3d (edge_mapping.hpp:18-26 of the reference) on three doubles
+    static size_t hash_point(const double v[3]) {
+        size_t seed = 0;
+        for (int i = 0; i < 3; i++) seed ^= std::hash<double>()(v[i]) + 0x9e3779b9 + (seed << 6) + (seed >> 2);
+        return seed;
     }
 
 private:
     struct Key {
-        uint64_t bits[3];
-        bool operator==(const Key& o) const { return bits[0] == o.bits[0] && bits[1] == o.bits[1] && bits[2] == o.bits[2]; }
+        double v[3];
+        bool operator==(const Key& o) const { return v[0] == o.v[0] && v[1] == o.v[1] && v[2] == o.v[2]; }   // Eigen's operator==
     };
     struct KeyHash {
-        size_t operator()(const Key& k) const {
-            uint64_t h = 0x9e3779b97f4a7c15ull;
-            for (uint64_t b : k.bits) { h ^= b + 0x9e3779b97f4a7c15ull + (h << 6) + (h >> 2); }
-            return size_t(h);
-        }
+        size_t operator()(const Key& k) const { return hash_point(k.v); }
     };
     std::unordered_map<Key, size_t, KeyHash> index_;
 };

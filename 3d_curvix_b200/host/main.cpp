@@ -8,8 +8,11 @@
 //   --max-passes N      overrides Max_Num_Of_3D_Edge_Sketch_Passes
 //   --schedule FILE     one line per pass: what was run (views, hypotheses, validations, pairs, claimed ratio, timings)
 //   --keep-outputs      do not `rm -f` the 3D_edges_* / 3D_tangents_* files of the outputs folder first
-// The curve grouping that follows the sketch in the reference (EdgeMapping::consolidate_3D_edges -> final_curves.txt) is host
-// code of the reference and not part of this path; --support-links FILE dumps its input (3-D edge -> supporting 2-D edges).
+//   --no-consolidate    stop after the sketch passes (skip EdgeMapping::consolidate_3D_edges, cmd/main.cpp:157-163)
+//   --support-links FILE     dump the 3-D edge -> supporting 2-D edges table (the input of the consolidation)
+//   --consolidate-links FILE skip the sketch: read such a dump and run only the consolidation on it
+// After the passes the 3-D edges are grouped into curves as in the reference (cmd/main.cpp:157-163): links / prunings / alignment on the
+// device (cvx_graph_*), curve tracing on the host; final_curves.txt and the intermediate files go to the outputs folder.
 #include <sys/stat.h>
 
 #include <cstdio>
@@ -27,7 +30,8 @@ static void usage() {
 }
 
 int main(int argc, char** argv) {
-    std::string config, schedule_path, links_path;
+    std::string config, schedule_path, links_path, consolidate_from;
+    bool consolidate = true;
     curvix_host::HostOptions opt;
     std::string dataset_override;
     int max_passes = -1;
@@ -49,6 +53,8 @@ int main(int argc, char** argv) {
         else if (a == "--max-passes") max_passes = std::atoi(next().c_str());
         else if (a == "--schedule") schedule_path = next();
         else if (a == "--support-links") links_path = next();
+        else if (a == "--consolidate-links") consolidate_from = next();
+        else if (a == "--no-consolidate") consolidate = false;
         else if (a == "--keep-outputs") keep_outputs = true;
         else if (a == "--refined") opt.use_refined_poses = std::atoi(next().c_str());
         else if (a == "--quiet") opt.quiet = true;
@@ -90,6 +96,10 @@ int main(int argc, char** argv) {
     FILE* sched = schedule_path.empty() ? nullptr : std::fopen(schedule_path.c_str(), "w");
 
     int edge_sketch_pass_count = 0;
+    if (!consolidate_from.empty()) {
+        if (!edgeMapping->read_support_links(consolidate_from)) { std::cerr << "ERROR: cannot read " << consolidate_from << std::endl; return 1; }
+        MWV_Edge_Rec.Max_3D_Edge_Sketch_Passes = 0;
+    }
     while (edge_sketch_pass_count < MWV_Edge_Rec.Max_3D_Edge_Sketch_Passes) {   // cmd/main.cpp:123-155
         const int v1 = MWV_Edge_Rec.hyp01_view_indx, v2 = MWV_Edge_Rec.hyp02_view_indx;
         if (!opt.quiet) std::cout << "Selected views for hypotheses are " << v1 << " and " << v2 << std::endl;
@@ -113,6 +123,22 @@ int main(int argc, char** argv) {
     }
     if (sched) std::fclose(sched);
     if (!links_path.empty()) edgeMapping->write_support_links(links_path);
+
+    if (consolidate) {   // cmd/main.cpp:157-163
+        if (!opt.quiet) std::cout << "Start to merge edges from 3D-2D edge links and 2D-2D edge links ..." << std::endl;
+        edgeMapping->Setup_Data_Parameters(settings);
+        if (!edgeMapping->consolidate_3D_edges(MWV_Edge_Rec.gpu(), MWV_Edge_Rec.All_R, MWV_Edge_Rec.All_T, MWV_Edge_Rec.K, MWV_Edge_Rec.Num_Of_Total_Imgs,
+                                               opt.outputs_dir, true, opt.quiet)) {
+            std::cerr << "ERROR: " << edgeMapping->last_error << std::endl;
+            return 1;
+        }
+        const EdgeMapping::ConsolidationReport& r = edgeMapping->report;
+        std::cout << "     - (untimed in the reference) consolidation: " << r.total_s << " (s): " << r.nodes << " 3D edges, " << r.records << " 3D-2D links, "
+                  << r.curvelets << " curvelets -> " << r.links << " / " << r.links_after_3d << " / " << r.links_after_projection
+                  << " graph links (built / pruned in 3D / pruned by projection); graph " << r.graph_s << " s, " << edgeMapping->num_of_iterations
+                  << " alignment iterations " << r.align_s << " s (kernels " << r.align_kernel_ms << " ms), curves " << r.curves_s << " s -> "
+                  << r.curves_from_graph << " traced, " << r.final_curves << " final curves" << std::endl;
+    }
 
     const double total_time = MWV_Edge_Rec.pair_edges_time + MWV_Edge_Rec.finalize_edge_pair_time + MWV_Edge_Rec.find_next_hypothesis_view_time;
     std::cout << "Total computation time: " << total_time << " (s)" << std::endl;   // cmd/main.cpp:165-170

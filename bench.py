@@ -713,6 +713,9 @@ def sec_per_object(local_rank):
     if not exe or not os.path.exists(fixture):
         return {"error": "curvix_main or the ABC-NEF fixture is missing"}
     scene = data.Scene.load_npz(fixture, "ABC-NEF/00000006")
+    cvf = os.path.join(ROOT, "tests", "golden", "abc_nef_00000006_curvelets_t1.npz")
+    if os.path.exists(cvf):
+        scene.load_curvelets(cvf)
     out = {}
     with tempfile.TemporaryDirectory() as tmp:
         scene.write_reference_layout(tmp, dataset="ABC-NEF", scene="00000006", thresh=1)
@@ -738,6 +741,12 @@ def sec_per_object(local_rank):
                         tm[name] = float(l.replace("(s)", " ").split(":")[-1].split()[0])
                     except ValueError:
                         pass
+            if "consolidation:" in l:      # EdgeMapping::consolidate_3D_edges of the drop-in (links / prunings / alignment on the device, curves on the host)
+                try:
+                    tm["consolidation_s"] = float(l.split("consolidation:")[1].split()[0])
+                    tm["consolidation"] = l.split("(s):", 1)[1].strip()
+                except (ValueError, IndexError):
+                    pass
         rows = [l.split() for l in open(sched).read().splitlines()] if os.path.exists(sched) else []
         out["b200"] = dict(tm, passes=len(rows), process_wall_s=round(wall, 3),
                            sec_per_object=tm.get("pair_edges_s", 0.0) + tm.get("finalize_s", 0.0) + tm.get("stack_s", 0.0),

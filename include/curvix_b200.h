@@ -269,6 +269,44 @@ int cvx_support_problem_stats(cvx_support_problem* p, int64_t* n_inliers, int64_
 int cvx_support_problem_result(cvx_support_problem* p, int32_t* support);
 int cvx_support_problem_destroy(cvx_support_problem* p);
 
+/* ---- 3-D edge graph: the data-parallel front half of EdgeMapping::consolidate_3D_edges -------------------------------
+ * The reference keys its maps on the exact doubles of a 3-D point; across this ABI a 3-D edge is a NODE INDEX in [0, n_nodes) chosen
+ * by the caller (3d_curvix_b200/host/edge_mapping.cpp numbers the distinct 3-D points in first-insertion order), a 2-D edge is a KEY
+ * INDEX in [0, n_keys) (view offset + edge index), and a link is a pair of node indices.  Host stages that stay on the host (connectivity
+ * graph, curve tracing, merging, writers: edge_mapping.cpp:639-1164) consume cvx_graph_get_neighbors + cvx_graph_align.
+ *
+ * cvx_graph_create        nodes: location (world) and tangents_3D_world of the FIRST support of every 3-D edge (what the link statistics use,
+ *                         edge_mapping.cpp:259-260), n_nodes x 3 doubles each (host pointers; copied)
+ * cvx_graph_build_links   build3DEdgeWeightedGraph (edge_mapping.cpp:107-192).  key_off / key_nodes: for every 2-D edge the 3-D edges it supports
+ *                         (CSR, the records of map_Uncorrected2DEdge_To_SupportingData :36-62, duplicates kept); curvelet c names the 2-D edges
+ *                         cv_self_key[c], cv_neighbor_key[c] (-1: none).  Every pair of records of a curvelet links its two 3-D edges unless the two
+ *                         points share a coordinate (:182).  Result: the distinct links (the reference's weights are never read).
+ * cvx_graph_prune         pruneEdgeGraph_by_3DProximityAndOrientation (:229-335: normal distance, point distance and tangent angle of a link below
+ *                         mean + lambda x standard deviation over all links) then pruneEdgeGraphbyProjections (:337-405: the two points project within
+ *                         proj_thresh pixels of each other in EVERY view; R n_views x 9 row-major, T n_views x 3, K 9), then the neighbour lists of
+ *                         buildEdgeNodeGraph (:440-455).  stats6 = {mu_t, sigma_t, mu_n, sigma_n, mu_theta, sigma_theta} as the reference prints them.
+ * cvx_graph_get_links     links of stage 0 (built), 1 (after the 3-D pruning), 2 (after the projection pruning); node_a < node_b, ascending
+ * cvx_graph_get_neighbors CSR neighbour lists of stage 2 (offsets n_nodes + 1, neighbours 2 x links), ascending neighbour index
+ * cvx_graph_align         align3DEdgesUsingEdgeNodes (:460-620): `iterations` synchronous updates of every node's location (Gaussian-weighted
+ *                         pull onto its neighbours' tangent lines) and orientation (weighted Euler-angle alignment), from the node locations and
+ *                         `orientation` (n_nodes x 3: normalised sum of the supports' tangents, :426-433); one kernel launch per iteration */
+typedef struct cvx_graph cvx_graph;
+int cvx_graph_create(cvx_ctx* ctx, int64_t n_nodes, const double* location, const double* first_tangent, cvx_graph** out);
+int cvx_graph_build_links(cvx_graph* g, int64_t n_keys, const int64_t* key_off, const int32_t* key_nodes, int64_t n_curvelets,
+                          const int32_t* cv_self_key, const int32_t* cv_neighbor_key, int64_t* n_links);
+int cvx_graph_prune(cvx_graph* g, double lambda1, double lambda2, double lambda3, double proj_thresh, int n_views, const double* R,
+                    const double* T, const double* K, double* stats6, int64_t* n_after_3d, int64_t* n_after_projection);
+int cvx_graph_get_links(cvx_graph* g, int stage, int32_t* node_a, int32_t* node_b, int64_t* n);
+/* per stage-0 link (order of cvx_graph_get_links(0)): position of its first occurrence in the curvelet-order stream of candidate pairs (the
+ * insertion order of the reference's graph map, edge_mapping.cpp:183) and whether it survives the 3-D pruning / the projection test */
+int cvx_graph_get_link_details(cvx_graph* g, int64_t* first_occurrence, uint8_t* keep_3d, uint8_t* keep_projection);
+int cvx_graph_get_neighbors(cvx_graph* g, int64_t* offsets, int32_t* neighbors);
+/* replaces the neighbour lists (a caller that wants the reference's neighbour ORDER, which follows its hash-map iteration, builds them itself) */
+int cvx_graph_set_neighbors(cvx_graph* g, const int64_t* offsets, const int32_t* neighbors);
+int cvx_graph_align(cvx_graph* g, const double* orientation, int iterations, double step_force, double step_torque, double* location_out,
+                    double* orientation_out, float* kernel_ms);
+int cvx_graph_destroy(cvx_graph* g);
+
 #ifdef __cplusplus
 }
 #endif

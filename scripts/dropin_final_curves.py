@@ -51,7 +51,8 @@ else:
 
 n_links = 0
 t0 = time.time()
-for (h1, h2) in [tuple(int(x) for x in p) for p in gold["schedule"]]:
+n_passes = int(os.environ.get("DROPIN_PASSES", "0")) or len(gold["schedule"])
+for (h1, h2) in [tuple(int(x) for x in p) for p in gold["schedule"]][:n_passes]:
     prod.set_pair(h1, h2)
     prod.run() if use_gpu else prod.run(mode=1)
     p, f = prod.pairs(), prod.finalize()
@@ -81,6 +82,10 @@ for (h1, h2) in [tuple(int(x) for x in p) for p in gold["schedule"]]:
             if s != -2:
                 add(scene.edges[v][s, :2], scene.edges[v][s, :3], v, s)
     ref.mapping_add_many(np.array(rec), img, idx)
+    if os.environ.get("DROPIN_LINKS"):     # the same records in curvix_main's --support-links / --consolidate-links format
+        with open(os.environ["DROPIN_LINKS"], "a") as lf:
+            for r, im, ix in zip(rec, img, idx):
+                lf.write(" ".join(repr(float(x)) for x in (*r[0:3], im, ix, *r[6:8], *r[3:6], *r[8:11])) + "\n")
     n_links += len(rec)
     print(f"pass ({h1},{h2}): {len(order)} accepted rows, {len(rec)} links", flush=True)
 print(f"{ref.n_3d_keys()} distinct 3-D edges, {n_links} links, producer {'CUDA path' if use_gpu else 'port oracle'}, {time.time() - t0:.1f} s; "

@@ -44,7 +44,11 @@ def abc_scene(data_mod):
     p = os.path.join(ROOT, "tests", "golden", "abc_nef_00000006_t1.npz")
     if not os.path.exists(p):
         pytest.skip("ABC-NEF fixture missing")
-    return data_mod.Scene.load_npz(p, "ABC-NEF/00000006")
+    sc = data_mod.Scene.load_npz(p, "ABC-NEF/00000006")
+    cv = os.path.join(ROOT, "tests", "golden", "abc_nef_00000006_curvelets_t1.npz")   # curvelets/Curvelets_<i>_t1.txt of the same object
+    if os.path.exists(cv):
+        sc.load_curvelets(cv)
+    return sc
 
 
 def make_oracle(oracle_mod, scene, **cfg_kw):

@@ -15,3 +15,12 @@ if __name__ == "__main__":
     out = os.path.join(ROOT, "tests", "golden", "abc_nef_00000006_t1.npz")
     sc.save_npz(out)
     print(out, os.path.getsize(out) / 1e6, "MB", sum(len(e) for e in sc.edges), "edges")
+    # curvelets/Curvelets_<i>_t1.txt (consumed by EdgeMapping::build3DEdgeWeightedGraph): the int stream of every file
+    import numpy as np
+    flat, counts = [], []
+    for i in range(50):
+        f = np.loadtxt(f"/root/reference/datasets/ABC-NEF/00000006/curvelets/Curvelets_{i}_t1.txt", dtype=np.int64).reshape(-1)
+        flat.append(f.astype(np.int32)); counts.append(len(f))
+    out = os.path.join(ROOT, "tests", "golden", "abc_nef_00000006_curvelets_t1.npz")
+    np.savez_compressed(out, flat=np.concatenate(flat), counts=np.asarray(counts, np.int64))
+    print(out, os.path.getsize(out) / 1e6, "MB", sum(counts) // 4, "lines")
