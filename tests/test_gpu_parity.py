@@ -78,6 +78,21 @@ def test_abc_nef_first_pass_parity(oracle_mod, abc_scene):
     assert rep["n_pairs_compared"] >= 0.97 * rep["n_pairs_oracle"]
 
 
+@pytest.mark.parametrize("pair", [(1, 4), (31, 8), (9, 6), (19, 17)])
+def test_abc_later_passes_of_the_reference_schedule_parity(oracle_mod, abc_scene, pair):
+    """The other four pairs the reference's own run of ABC-NEF 00000006 visits (tests/golden/ref_abc_full_run.npz): every stage against the port
+    oracle, disagreements only within 1e-9 of a threshold (asserted by compare) and counted."""
+    o = make_oracle(oracle_mod, abc_scene)
+    g = _gpu(abc_scene)
+    o.set_pair(*pair); o.run(mode=1, keep=True)
+    g.set_pair(*pair); g.run()
+    rep = compare(o, g, check_intermediates=True)
+    _report(f"abc_{pair[0]}_{pair[1]}", rep)
+    c = rep["counts_gpu"]
+    assert rep["threshold_disagreements_form"] <= 0.03 * c["n_h1_processed"] and rep["threshold_disagreements_support"] <= 5
+    assert rep["n_pairs_compared"] >= 0.96 * rep["n_pairs_oracle"]
+
+
 @pytest.mark.parametrize("pair", [(47, 42), (28, 48)])
 def test_abc_against_reference_goldens(abc_scene, pair):
     """The CUDA path against vectors written by the REFERENCE ITSELF (tests/golden/ref_abc_*.npz: its unmodified sources built against

@@ -129,7 +129,10 @@ def test_curvix_main_full_run_matches_the_reference(abc_scene, abc_on_disk):
     n_diff_rows = 0
     for i, row in enumerate(rows):
         a, b = int(row[1]), int(row[2])
-        assert abs(float(row[7]) - g["avg_ratio"][i]) < 1e-6
+        # claimed ratio: the golden holds the reference's printed 6 digits; one claimed edge of one view is 4e-6 to 9e-6 of the average, and a tied
+        # cluster representative (below) changes which H2_Clusters key the claim walks (EdgeSketch_Core.hpp:193-202, the mis-indexed key of
+        # EdgeClusterer.cpp:216-236), i.e. at most a few edges per pass
+        assert abs(float(row[7]) - g["avg_ratio"][i]) < 2e-5
         name = f"ABC-NEF_00000006_hypo1_{a}_hypo2_{b}.txt"
         E = np.loadtxt(out / ("3D_edges_" + name)).reshape(-1, 3)
         T = np.loadtxt(out / ("3D_tangents_" + name)).reshape(-1, 3)
@@ -145,12 +148,33 @@ def test_curvix_main_full_run_matches_the_reference(abc_scene, abc_on_disk):
         # distance of the reference row (scene radius ~1, image 800 px)
         assert np.linalg.norm(E[~same] - Eo[~same], axis=1).max(initial=0.0) < 0.05
     print("rows that differ from the reference run (tied cluster representatives):", n_diff_rows)
+    # the run ends with the curve consolidation (cmd/main.cpp:157-163): final_curves.txt against the file of the REFERENCE's own run
+    # (tests/golden/ref_final_curves_abc.txt.gz).  The two runs differ by the tied representatives above, so the comparison is by content:
+    # the same number of 3-D edge nodes, nearly all node positions in common, a curve count within a few per cent (the reference's own
+    # consolidation gives 766 curves on the port oracle's edges and 780 on its own; test_consolidate.py compares like with like, exactly).
+    import gzip
+
+    def curve_rows(lines):
+        return np.array([[float(x) for x in l.split()] for l in lines[2:] if l.strip()])
+    mine = (out / "final_curves.txt").read_text().splitlines()
+    theirs = gzip.open(os.path.join(ROOT, "tests", "golden", "ref_final_curves_abc.txt.gz"), "rt").read().splitlines()
+    assert mine[:2] == theirs[:2]
+    A, B = curve_rows(mine), curve_rows(theirs)
+    assert A.shape == B.shape and A.shape[1] == 8                      # CurveID NodeIndex x y z tx ty tz, one row per 3-D edge
+    ka, kb = {tuple(np.round(r[2:5], 3)) for r in A}, {tuple(np.round(r[2:5], 3)) for r in B}
+    assert len(ka & kb) > 0.99 * len(kb), (len(ka & kb), len(kb))
+    ca, cb = len(set(A[:, 0])), len(set(B[:, 0]))
+    assert abs(ca - cb) < 0.05 * cb, (ca, cb)
+    for f in ("curves_from_connectivity_graph.txt", "connectivity_graph.txt", "3D_edges_after_smoothing.txt", "curve_indices_for_merging.txt"):
+        assert (out / f).stat().st_size > 0
     # second run from the binary edge cache gives byte-identical outputs
     first = {f: (out / f).read_bytes() for f in os.listdir(out)}
-    r = subprocess.run([exe, "-c", str(cfg), "--outputs", str(out), "--max-passes", "2", "--edge-cache", str(root), "--quiet"],
+    r = subprocess.run([exe, "-c", str(cfg), "--outputs", str(out), "--max-passes", "2", "--edge-cache", str(root), "--quiet", "--no-consolidate"],
                        capture_output=True, text=True, timeout=600)
     assert r.returncode == 0
-    for f in os.listdir(out):
+    again = [f for f in os.listdir(out) if "_hypo1_" in f]
+    assert len(again) == 4                                            # 3D_edges_* / 3D_tangents_* of the first two passes
+    for f in again:
         assert (out / f).read_bytes() == first[f]
 
 
