@@ -73,27 +73,6 @@ bool in_first_or_last_two(const std::vector<int>& v, int num) {   // edge_mappin
 
 }  // namespace
 
-bool EdgeMapping::write_support_links(const std::string& path) const {
-    FILE* f = std::fopen(path.c_str(), "w");
-    if (!f) return false;
-    for (const auto& e : edge_3D_to_supporting_edges)
-        for (const auto& s : e.supports)
-            std::fprintf(f, "%.17g %.17g %.17g %d %d %.17g %.17g %.17g %.17g %.17g %.17g %.17g %.17g\n", e.point[0], e.point[1], e.point[2], s.image_number,
-                         s.edge_idx, s.edge[0], s.edge[1], s.tangents_3D_world[0], s.tangents_3D_world[1], s.tangents_3D_world[2],
-                         s.edge_uncorrected[0], s.edge_uncorrected[1], s.edge_uncorrected[2]);
-    return std::fclose(f) == 0;
-}
-
-bool EdgeMapping::read_support_links(const std::string& path) {
-    std::vector<double> v;
-    if (!curvix_host::read_doubles(path, &v) || v.size() % 13 != 0) return false;
-    for (size_t i = 0; i + 13 <= v.size(); i += 13) {
-        const double* r = &v[i];
-        add3DToSupportingEdgesMapping(r, r + 7, r + 5, r + 10, int(r[3]), int(r[4]));
-    }
-    return true;
-}
-
 void EdgeMapping::Setup_Data_Parameters(const curvix_host::FlatYaml& y) {
     thresh_EDG = y.as_int("TOED_Thresh");
     Dataset_Path = y.str("Dataset_Path");

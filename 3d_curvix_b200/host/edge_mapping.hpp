@@ -85,8 +85,26 @@ public:
     }
 
     // One line per link: X Y Z  image edge_idx  x y  tx ty tz  ux uy utheta (input of consolidate_3D_edges; read_support_links restores it)
-    bool write_support_links(const std::string& path) const;
-    bool read_support_links(const std::string& path);
+    bool write_support_links(const std::string& path) const {
+        FILE* f = std::fopen(path.c_str(), "w");
+        if (!f) return false;
+        for (const auto& e : edge_3D_to_supporting_edges)
+            for (const auto& s : e.supports)
+                std::fprintf(f, "%.17g %.17g %.17g %d %d %.17g %.17g %.17g %.17g %.17g %.17g %.17g %.17g\n", e.point[0], e.point[1], e.point[2],
+                             s.image_number, s.edge_idx, s.edge[0], s.edge[1], s.tangents_3D_world[0], s.tangents_3D_world[1], s.tangents_3D_world[2],
+                             s.edge_uncorrected[0], s.edge_uncorrected[1], s.edge_uncorrected[2]);
+        return std::fclose(f) == 0;
+    }
+    bool read_support_links(const std::string& path) {
+        FILE* f = std::fopen(path.c_str(), "r");
+        if (!f) return false;
+        double r[13];
+        while (std::fscanf(f, "%lf %lf %lf %lf %lf %lf %lf %lf %lf %lf %lf %lf %lf", r, r + 1, r + 2, r + 3, r + 4, r + 5, r + 6, r + 7, r + 8, r + 9, r + 10,
+                           r + 11, r + 12) == 13)
+            add3DToSupportingEdgesMapping(r, r + 7, r + 5, r + 10, int(r[3]), int(r[4]));
+        std::fclose(f);
+        return true;
+    }
 
     // EdgeMapping::Setup_Data_Parameters (edge_mapping.cpp:64-70)
     void Setup_Data_Parameters(const curvix_host::FlatYaml& settings);
