@@ -747,11 +747,6 @@ def sec_per_object(local_rank):
                     tm["consolidation"] = l.split("(s):", 1)[1].strip()
                 except (ValueError, IndexError):
                     pass
-            if "consolidation:" in l:      # EdgeMapping::consolidate_3D_edges of the drop-in (links / prunings / alignment on the device, curves on the host)
-                try:
-                    tm["consolidation_s"] = float(l.split("consolidation:")[1].split()[0])
-                except (ValueError, IndexError):
-                    pass
         rows = [l.split() for l in open(sched).read().splitlines()] if os.path.exists(sched) else []
         out["b200"] = dict(tm, passes=len(rows), process_wall_s=round(wall, 3),
                            sec_per_object=tm.get("pair_edges_s", 0.0) + tm.get("finalize_s", 0.0) + tm.get("stack_s", 0.0),
