@@ -22,7 +22,7 @@ SYMBOLS = [
     "cvx_support_problem_create", "cvx_support_problem_run", "cvx_support_problem_stats", "cvx_support_problem_result",
     "cvx_support_problem_destroy",
     "cvx_graph_create", "cvx_graph_build_links", "cvx_graph_prune", "cvx_graph_get_links", "cvx_graph_get_link_details", "cvx_graph_get_neighbors",
-    "cvx_graph_set_neighbors", "cvx_graph_align", "cvx_graph_destroy",
+    "cvx_graph_set_neighbors", "cvx_graph_align", "cvx_graph_destroy", "cvx_graph_align_no_alloc",
 ]
 
 
@@ -101,6 +101,9 @@ def load():
     lib.cvx_graph_set_neighbors.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
     lib.cvx_graph_align.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_double, C.c_double, C.c_void_p, C.c_void_p, C.POINTER(C.c_float)]
     lib.cvx_graph_destroy.argtypes = [C.c_void_p]
+    lib.cvx_graph_align_no_alloc.argtypes = [C.c_int, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_double,
+                                             C.c_double, C.c_void_p, C.c_void_p, C.c_char_p, C.c_int]
+    lib.cvx_graph_align_no_alloc.restype = C.c_int
     lib.cvx_gather_post.argtypes = [C.c_void_p, C.c_int64, C.c_int]
     lib.cvx_gather_wait.argtypes = [C.c_void_p, C.c_int, C.c_int]
     lib.cvx_gather_get.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(CvxGatheredUnit)]
@@ -399,6 +402,20 @@ class EdgeSketch:
         r = CvxDeviceResults()
         self._ck(self.lib.cvx_get_device_results(self.h, C.byref(r)))
         return r
+
+
+ALIGN_NO_ALLOC_MAX_NODES = 65536
+
+
+def graph_align_no_alloc(device, stream_ptr, n_nodes, d_offsets, d_neighbors, d_location, d_orientation, iterations, step_force, step_torque,
+                         d_location_out, d_orientation_out):
+    """cvx_graph_align_no_alloc: every d_* argument is a raw DEVICE address (int).  Enqueues only; returns (rc, message)."""
+    lib = load()
+    err = C.create_string_buffer(512)
+    rc = lib.cvx_graph_align_no_alloc(int(device), C.c_void_p(stream_ptr or 0), int(n_nodes), C.c_void_p(d_offsets), C.c_void_p(d_neighbors),
+                                      C.c_void_p(d_location), C.c_void_p(d_orientation), int(iterations), float(step_force), float(step_torque),
+                                      C.c_void_p(d_location_out), C.c_void_p(d_orientation_out), err, len(err))
+    return rc, err.value.decode()
 
 
 class EdgeGraph:

@@ -20,7 +20,9 @@
 #include <algorithm>
 #include <cfloat>
 #include <cmath>
+#include <cstdio>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -631,3 +633,82 @@ int cvx_graph_align(cvx_graph* g, const double* orientation, int iterations, dou
 }
 
 }  // extern "C"
+
+// =====================================================================================
+// cvx_graph_align_no_alloc -- a variant of cvx_graph_align for callers that cannot call cudaMalloc (CUDA graph capture, tight serving
+// loops, harnesses that forbid it).  No counterpart in the reference.  The alignment iterates
+// between two buffers; here one of them is the caller's output and the other a file-scope device array of a fixed maximum size, which
+// every GPU that loads the library holds until exit (CVX_ALIGN_NO_ALLOC_MAX_NODES x 6 doubles = 3 MiB).  The entry point calls no
+// cudaMalloc / cudaFree / allocating library routine, creates no stream or event and does not synchronise: it only enqueues kernels (and, for
+// iterations == 0, two device-to-device copies) on the caller's stream.  Every call on a device shares the array: calls that overlap on the
+// GPU (different streams, no ordering between them) race.  Nothing in it has to start at zero -- every iteration writes the row of every
+// node before the next one reads it -- so the contents left by an earlier call are never read.
+// =====================================================================================
+#define CVX_ALIGN_NO_ALLOC_MAX_NODES_ 65536
+static __device__ __align__(256) double g_align_scratch[size_t(CVX_ALIGN_NO_ALLOC_MAX_NODES_) * 6];   // locations [0, 3 max), orientations [3 max, 6 max)
+
+namespace {
+constexpr int kMaxDevices = 64;
+double* g_align_scratch_addr[kMaxDevices];   // device address of g_align_scratch on every device, resolved once per device
+bool g_align_scratch_ready[kMaxDevices];
+std::mutex g_align_scratch_mu;
+
+int no_alloc_fail(char* errbuf, int errbuf_len, int code, const std::string& msg) {
+    if (errbuf && errbuf_len > 0) { std::snprintf(errbuf, size_t(errbuf_len), "%s", msg.c_str()); }
+    return code;
+}
+}  // namespace
+
+extern "C" int cvx_graph_align_no_alloc(int device, void* stream, int64_t n_nodes, const int64_t* d_offsets, const int32_t* d_neighbors,
+                                        const double* d_location, const double* d_orientation, int iterations, double step_force,
+                                        double step_torque, double* d_location_out, double* d_orientation_out, char* errbuf, int errbuf_len) {
+    if (n_nodes < 0 || iterations < 0 || device < 0 || device >= kMaxDevices)
+        return no_alloc_fail(errbuf, errbuf_len, CVX_ERR_INVALID, "cvx_graph_align_no_alloc: bad arguments");
+    if (n_nodes > CVX_ALIGN_NO_ALLOC_MAX_NODES_)
+        return no_alloc_fail(errbuf, errbuf_len, CVX_ERR_INVALID,
+                             "cvx_graph_align_no_alloc: " + std::to_string(n_nodes) + " nodes exceed the fixed scratch of " +
+                                 std::to_string(CVX_ALIGN_NO_ALLOC_MAX_NODES_) + " nodes (use cvx_graph_align, which allocates)");
+    if (n_nodes == 0) return CVX_OK;
+    if (!d_offsets || !d_neighbors || !d_location || !d_orientation || !d_location_out || !d_orientation_out)
+        return no_alloc_fail(errbuf, errbuf_len, CVX_ERR_INVALID, "cvx_graph_align_no_alloc: null device pointer");
+    if (d_location_out == d_location || d_orientation_out == d_orientation)
+        return no_alloc_fail(errbuf, errbuf_len, CVX_ERR_INVALID, "cvx_graph_align_no_alloc: outputs must not alias the inputs");
+    cudaError_t e = cudaSetDevice(device);
+    if (e != cudaSuccess) return no_alloc_fail(errbuf, errbuf_len, CVX_ERR_CUDA, std::string("cudaSetDevice: ") + cudaGetErrorString(e));
+    double* scratch = nullptr;
+    {   // set-up, once per device, with that device current: in host code the array's name is a stand-in, not a device address
+        std::lock_guard<std::mutex> lock(g_align_scratch_mu);
+        if (!g_align_scratch_ready[device]) {
+            double* p = nullptr;
+            e = cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_align_scratch);
+            if (e != cudaSuccess || !p)
+                return no_alloc_fail(errbuf, errbuf_len, CVX_ERR_CUDA, std::string("cudaGetSymbolAddress(g_align_scratch): ") + cudaGetErrorString(e));
+            g_align_scratch_addr[device] = p;
+            g_align_scratch_ready[device] = true;
+        }
+        scratch = g_align_scratch_addr[device];
+    }
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const size_t bytes = size_t(n_nodes) * 24;
+    if (iterations == 0) {
+        e = cudaMemcpyAsync(d_location_out, d_location, bytes, cudaMemcpyDeviceToDevice, st);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(d_orientation_out, d_orientation, bytes, cudaMemcpyDeviceToDevice, st);
+        if (e != cudaSuccess) return no_alloc_fail(errbuf, errbuf_len, CVX_ERR_CUDA, std::string("cudaMemcpyAsync: ") + cudaGetErrorString(e));
+        return CVX_OK;
+    }
+    double* s_loc = scratch;
+    double* s_ori = scratch + size_t(CVX_ALIGN_NO_ALLOC_MAX_NODES_) * 3;
+    // ping-pong between the caller's outputs and the scratch so that the LAST iteration writes the outputs
+    const double *la = d_location, *oa = d_orientation;
+    for (int it = 0; it < iterations; it++) {
+        const bool to_out = ((iterations - 1 - it) & 1) == 0;
+        double* lb = to_out ? d_location_out : s_loc;
+        double* ob = to_out ? d_orientation_out : s_ori;
+        k_align_step<<<unsigned((n_nodes + 127) / 128), 128, 0, st>>>(n_nodes, reinterpret_cast<const long long*>(d_offsets), d_neighbors, la, oa, lb, ob,
+                                                                     step_force, step_torque);
+        la = lb; oa = ob;
+    }
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return no_alloc_fail(errbuf, errbuf_len, CVX_ERR_CUDA, std::string("k_align_step: ") + cudaGetErrorString(e));
+    return CVX_OK;
+}

@@ -307,6 +307,25 @@ int cvx_graph_align(cvx_graph* g, const double* orientation, int iterations, dou
                     double* orientation_out, float* kernel_ms);
 int cvx_graph_destroy(cvx_graph* g);
 
+/* cvx_graph_align_no_alloc -- NO COUNTERPART IN THE REFERENCE; added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same iterations as cvx_graph_align
+ * (align3DEdgesUsingEdgeNodes, one k_align_step launch each), but every pointer is a DEVICE pointer owned by the caller and the one
+ * intermediate buffer the iteration needs lives in a file-scope device array of fixed size inside the library:
+ *   limit   n_nodes <= CVX_ALIGN_NO_ALLOC_MAX_NODES (65 536; 3 MiB per GPU that loads the library, held until exit); larger sizes are rejected
+ *           with CVX_ERR_INVALID and a message in errbuf -- use cvx_graph_align there
+ *   calls   no cudaMalloc / cudaFree / allocating library routine, no stream or event creation, no synchronisation: kernels (and two
+ *           device-to-device copies when iterations == 0) are enqueued on `stream` (a cudaStream_t, NULL = the default stream) of `device`
+ *   sharing every call on a device uses the same array: calls that may overlap on the GPU (different streams without an ordering) race.  The
+ *           array keeps the previous call's contents; nothing in it has to start at zero (each iteration writes every node's row before the
+ *           next reads it), so stale contents are never read
+ *   inputs  d_offsets n_nodes + 1 (int64), d_neighbors offsets[n_nodes] (int32) as cvx_graph_get_neighbors / cvx_graph_set_neighbors;
+ *           d_location, d_orientation n_nodes x 3 doubles; outputs d_location_out, d_orientation_out n_nodes x 3 doubles, not aliasing the inputs
+ *   errbuf  optional, receives the error text (there is no context to hold it) */
+#define CVX_ALIGN_NO_ALLOC_MAX_NODES 65536
+int cvx_graph_align_no_alloc(int device, void* stream, int64_t n_nodes, const int64_t* d_offsets, const int32_t* d_neighbors,
+                             const double* d_location, const double* d_orientation, int iterations, double step_force, double step_torque,
+                             double* d_location_out, double* d_orientation_out, char* errbuf, int errbuf_len);
+
 #ifdef __cplusplus
 }
 #endif
