@@ -324,7 +324,7 @@ def ncu_notes(kernel):
     return json.load(open(p)).get(kernel, {}).get("ncu") if os.path.exists(p) else None
 
 
-def traffic(kernel, views=0):
+def traffic(kernel, views=0, workload="", launches=0):
     """dram__bytes_read.sum + dram__bytes_write.sum of one launch of `kernel`, from the committed ncu --set full capture
     (profiles/traffic.json, written by scripts/ncu_summary.py from the .ncu-rep of the same bench command), else None."""
     p = os.path.join(ROOT, "profiles", "traffic.json")
@@ -332,7 +332,9 @@ def traffic(kernel, views=0):
         e = json.load(open(p)).get(kernel, {})
         if "bytes_per_view" in e and views:
             return e["bytes_per_view"] * views
-        return e.get("bytes")
+        if workload == "cfg4":          # a step = `launches` launches of the kernel (one per unit of this rank): per-launch capture x launches
+            return e["cfg4_bytes_per_launch"] * launches if "cfg4_bytes_per_launch" in e and launches else None
+        return e.get("bytes") if workload in ("", "cfg2") else None
     return None
 
 
@@ -590,7 +592,7 @@ def run_schedule(args, rank, world, local_rank):
     form_bytes = 100 * csum["n_hypotheses"] + 40 * csum["n_candidates"]
     abytes = fused if dom == "validate" else form_bytes
     ach = abytes / (ph[dom] * 1e-3) / 1e9
-    roof = {"bound": "hbm", "kernel": kname, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": traffic(kname),
+    roof = {"bound": "hbm", "kernel": kname, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": traffic(kname, workload=args.workload, launches=len(mine)),
             "peak_source": peak_src, "kernel_ms": ph[dom], "algorithmic_bytes": abytes,
             "bytes_formula": ("4 x validations + 48 x hypotheses + 32 x staged validation edges (SURVEY.md 8d, fused kernel)" if dom == "validate"
                               else "100 B per hypothesis row written + 40 B per raw candidate read (DESIGN.md section 4)"),
