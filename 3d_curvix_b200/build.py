@@ -36,17 +36,23 @@ def _cxx():
 def build_cuda(force=False, verbose=False):
     srcs = [os.path.join(CSRC, f) for f in ("cvx_kernels.cu", "cvx_api.cu", "cvx_comm.cu", "cvx_graph.cu")]
     deps = srcs + [os.path.join(CSRC, f) for f in ("cvx_kernels.cuh", "cvx_math.cuh", "cvx_internal.h")] + [os.path.join(ROOT, "include", "curvix_b200.h")]
-    if not force and not _stale(LIB, deps):
-        return LIB
-    nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
     out = os.environ.get("CVX_LIB_OUT", LIB)            # experiments: alternative output name + extra -D flags
+    if not force and not _stale(out, deps):
+        return out
+    nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
     extra = os.environ.get("CVX_NVCC_EXTRA", "").split()
-    cmd = [nvcc] + NVCC_FLAGS + extra + ["-ccbin", _cxx(), "-shared", "-o", out] + srcs + ["-ldl"]   # NCCL is dlopen-ed (cvx_comm.cu)
+    tmp = out + f".tmp{os.getpid()}"                    # written aside and renamed: another process never dlopens a half-written library
+    cmd = [nvcc] + NVCC_FLAGS + extra + ["-ccbin", _cxx(), "-shared", "-o", tmp] + srcs + ["-ldl"]   # NCCL is dlopen-ed (cvx_comm.cu)
     if verbose:
         cmd.insert(1, "-Xptxas=-v")
         print(" ".join(cmd))
-    subprocess.run(cmd, check=True)
-    return LIB
+    try:
+        subprocess.run(cmd, check=True)
+        os.replace(tmp, out)
+    finally:
+        if os.path.exists(tmp):
+            os.remove(tmp)
+    return out
 
 
 def build_host(force=False):
