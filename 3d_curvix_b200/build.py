@@ -35,7 +35,7 @@ def _cxx():
 
 def build_cuda(force=False, verbose=False):
     srcs = [os.path.join(CSRC, f) for f in ("cvx_kernels.cu", "cvx_api.cu", "cvx_comm.cu", "cvx_graph.cu")]
-    deps = srcs + [os.path.join(CSRC, f) for f in ("cvx_kernels.cuh", "cvx_math.cuh", "cvx_internal.h")] + [os.path.join(ROOT, "include", "curvix_b200.h")]
+    deps = srcs + [os.path.join(CSRC, f) for f in ("cvx_kernels.cuh", "cvx_math.cuh", "cvx_graph_math.cuh", "cvx_internal.h")] + [os.path.join(ROOT, "include", "curvix_b200.h")]
     out = os.environ.get("CVX_LIB_OUT", LIB)            # experiments: alternative output name + extra -D flags
     if not force and not _stale(out, deps):
         return out

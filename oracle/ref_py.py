@@ -335,6 +335,28 @@ def triangulate(p1, p2, R21, T21, K, variant="strict"):
     return out
 
 
+def closest_vector_to_line(P1, d1, P2, variant="strict"):
+    out = np.empty(3)
+    f = lambda x: _d(np.ascontiguousarray(x, np.float64).reshape(-1))
+    load(variant).ref_closest_vector_to_line(f(P1), f(d1), f(P2), _d(out))
+    return out
+
+
+def shortest_align_euler_deg(v1, v2, variant="strict"):
+    out = np.empty(3)
+    f = lambda x: _d(np.ascontiguousarray(x, np.float64).reshape(-1))
+    load(variant).ref_shortest_align_euler_deg(f(v1), f(v2), _d(out))
+    return out
+
+
+def euler_to_rotation(roll, pitch, yaw, variant="strict"):
+    out = np.empty(9)
+    lib = load(variant)
+    lib.ref_euler_to_rotation.argtypes = [C.c_double, C.c_double, C.c_double, C.c_void_p]
+    lib.ref_euler_to_rotation(float(roll), float(pitch), float(yaw), _d(out))
+    return out.reshape(3, 3)
+
+
 def tangent3d(e1, e2, K1, K2, R1, T1, R2, T2, variant="strict"):
     out = np.empty(3)
     f = lambda x: _d(np.ascontiguousarray(x, np.float64).reshape(-1))

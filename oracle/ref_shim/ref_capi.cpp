@@ -337,5 +337,19 @@ void ref_tangent3d(const double* e1, const double* e2, const double* K1, const d
     MultiviewGeometryUtil::multiview_geometry_util util;
     out3(util.get3DTangentFromTwo2Dtangents(v3(e1), v3(e2), m3(K1), m3(K2), m3(R1), v3(T1), m3(R2), v3(T2)), o);   // EdgeSketch_Core.cpp:675
 }
+// ---- the helpers of the curve consolidation (edge_mapping.cpp:262, 541-575)
+void ref_closest_vector_to_line(const double* P1, const double* d1, const double* P2, double* o) {
+    MultiviewGeometryUtil::multiview_geometry_util util;
+    out3(util.findClosestVectorFromPointToLine(v3(P1), v3(d1), v3(P2)), o);
+}
+void ref_shortest_align_euler_deg(const double* a, const double* b, double* o) {
+    MultiviewGeometryUtil::multiview_geometry_util util;
+    out3(util.getShortestAlignEulerAnglesDegrees(v3(a), v3(b)), o);
+}
+void ref_euler_to_rotation(double roll, double pitch, double yaw, double* o9) {
+    MultiviewGeometryUtil::multiview_geometry_util util;
+    const Eigen::Matrix3d R = util.euler_to_rotation_matrix(roll, pitch, yaw);
+    for (int i = 0; i < 3; i++) for (int j = 0; j < 3; j++) o9[3 * i + j] = R(i, j);
+}
 
 }  // extern "C"

@@ -87,4 +87,8 @@ int ref_support_idx(double delta_theta_deg, const double* tgt /*2*/, int e3, con
 void ref_triangulate(const double* p1, const double* p2, const double* R21, const double* T21, const double* K, double* out3);
 void ref_tangent3d(const double* e1 /*x y th*/, const double* e2, const double* K1, const double* K2, const double* R1, const double* T1,
                    const double* R2, const double* T2, double* out3);
+// helpers of the curve consolidation: util.cpp:123-131, 186-213, 241-252 (called from edge_mapping.cpp:262, 541-575)
+void ref_closest_vector_to_line(const double* P1, const double* d1, const double* P2, double* out3);
+void ref_shortest_align_euler_deg(const double* v1, const double* v2, double* out3);
+void ref_euler_to_rotation(double roll, double pitch, double yaw, double* out9 /*row-major*/);
 }

@@ -66,8 +66,8 @@ def host_harness():
     import ctypes as C
     so = os.path.join(ROOT, "tests", "libhost_harness.so")
     src = os.path.join(ROOT, "tests", "host_harness.cpp")
-    hdr = os.path.join(ROOT, "3d_curvix_b200", "csrc", "cvx_math.cuh")
-    if not os.path.exists(so) or os.path.getmtime(so) < max(os.path.getmtime(src), os.path.getmtime(hdr)):
+    hdrs = [os.path.join(ROOT, "3d_curvix_b200", "csrc", h) for h in ("cvx_math.cuh", "cvx_graph_math.cuh")]
+    if not os.path.exists(so) or os.path.getmtime(so) < max([os.path.getmtime(src)] + [os.path.getmtime(h) for h in hdrs]):
         cxx = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++"
         subprocess.run([cxx, "-O2", "-ffp-contract=off", "-fPIC", "-shared", "-std=c++17", "-o", so, src], check=True)
     return C.CDLL(so)

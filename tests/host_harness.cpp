@@ -3,6 +3,7 @@
 // product never runs this math on the CPU.
 #include <cstring>
 
+#include "../3d_curvix_b200/csrc/cvx_graph_math.cuh"
 #include "../3d_curvix_b200/csrc/cvx_math.cuh"
 
 using namespace cvx;
@@ -41,5 +42,18 @@ void hh_tangent3d(const double* e1, const double* e2, const double* K1inv, const
     std::memset(&pc, 0, sizeof(pc));
     std::memcpy(pc.K1inv, K1inv, 72); std::memcpy(pc.K2inv, K2inv, 72); std::memcpy(pc.R21, R21, 72); std::memcpy(pc.R1, R1, 72);
     tangent3d_world(e1[0], e1[1], e1[2], e2[0], e2[1], e2[2], pc, out3);
+}
+// ---- 3-D edge graph arithmetic (cvx_graph_math.cuh): the helpers of align3DEdgesUsingEdgeNodes / the link metrics
+void hh_closest_vector_to_line(const double* P1, const double* d1, const double* P2, double* o) {
+    const cvxg::D3 r = cvxg::closest_vector_to_line(cvxg::ld3(P1, 0), cvxg::ld3(d1, 0), cvxg::ld3(P2, 0));
+    o[0] = r.x; o[1] = r.y; o[2] = r.z;
+}
+void hh_shortest_align_euler_deg(const double* a, const double* b, double* o) {
+    const cvxg::D3 r = cvxg::shortest_align_euler_deg(cvxg::ld3(a, 0), cvxg::ld3(b, 0));
+    o[0] = r.x; o[1] = r.y; o[2] = r.z;
+}
+void hh_euler_to_rotation(double roll, double pitch, double yaw, double* o9) {
+    const cvxg::M33 R = cvxg::euler_to_rotation(roll, pitch, yaw);
+    for (int i = 0; i < 3; i++) for (int j = 0; j < 3; j++) o9[3 * i + j] = R.m[i][j];
 }
 }

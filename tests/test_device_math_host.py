@@ -157,3 +157,38 @@ def test_triangulation_tangent_bit_exact_and_kat(oracle_mod, host_harness):
         host_harness.hh_tangent3d(_p(e1), _p(e2), _p(Kinv), _p(Kinv), _p(R1), _p(R21o), _p(t2))
         assert np.array_equal(t1, t2)
         assert abs(np.linalg.norm(t1) - 1.0) < 1e-6   # R1 is given to 6 digits only
+
+
+def test_graph_alignment_arithmetic_equals_the_reference(host_harness):
+    """cvx_graph_math.cuh (what k_align_step / k_link_metrics run) against the REFERENCE's own util.cpp functions in oracle/_ref, both on the host
+    with glibc: findClosestVectorFromPointToLine, getShortestAlignEulerAnglesDegrees (Rodrigues rotation, Eigen's eulerAngles(0,1,2), the
+    shortest-path rule incl. nearly opposite directions) and euler_to_rotation_matrix (AngleAxis -> quaternion product -> matrix): bit for bit."""
+    import ctypes as C
+    from oracle import ref_py
+    if not ref_py.available():
+        pytest.skip("oracle/_ref not built and /root/reference absent")
+    rng = np.random.default_rng(3)
+    P = lambda a: np.ascontiguousarray(a, np.float64).ctypes.data_as(C.c_void_p)
+    host_harness.hh_euler_to_rotation.argtypes = [C.c_double, C.c_double, C.c_double, C.c_void_p]
+    n_large = 0
+    for k in range(4000):
+        a = rng.normal(size=3); b = rng.normal(size=3)
+        if k % 4 == 1:
+            b = a + 0.05 * rng.normal(size=3)                  # neighbouring orientations (the common case of the alignment)
+        if k % 4 == 2:
+            b = -a + 0.05 * rng.normal(size=3)                 # nearly opposite: the reversed-direction branch (util.cpp:193-203)
+        if k % 2 == 0:
+            a /= np.linalg.norm(a); b /= np.linalg.norm(b)
+        got = np.empty(3)
+        host_harness.hh_shortest_align_euler_deg(P(a), P(b), P(got))
+        want = ref_py.shortest_align_euler_deg(a, b)
+        assert np.array_equal(got, want), (k, a, b, got, want)
+        n_large += int(np.abs(want).max() > 45)
+        p1, p2 = rng.uniform(-1, 1, 3), rng.uniform(-1, 1, 3)
+        host_harness.hh_closest_vector_to_line(P(p1), P(a), P(p2), P(got))
+        assert np.array_equal(got, ref_py.closest_vector_to_line(p1, a, p2))
+        e = rng.uniform(-0.2, 0.2, 3) if k % 3 else rng.uniform(-3.1, 3.1, 3)
+        R = np.empty(9)
+        host_harness.hh_euler_to_rotation(float(e[0]), float(e[1]), float(e[2]), P(R))
+        assert np.array_equal(R.reshape(3, 3), ref_py.euler_to_rotation(*e)), (k, e)
+    assert n_large > 100                                       # the large-angle branches were exercised
