@@ -215,6 +215,53 @@ def test_support_problem_against_oracle(oracle_mod):
     sp.close()
 
 
+def test_support_problem_cfg5_width(oracle_mod):
+    """BASELINE.json config 5 at full width per view (200 000 edges, ~1 M pre-formed hypothesis rows in 50 000 groups, delta_theta 2 deg) over 20
+    validation views: (1) the oracle's Theta(E3) scans on a bounded sample of groups in two views, exact; (2) size-independent properties of EVERY
+    answer of two whole views, checked in numpy: a returned edge lies strictly inside both wedges and reaches the orientation threshold, and no
+    inlier of the row beats it; (3) a second run returns the same matrix."""
+    api = pkg("api"); synth = pkg("support_synth")
+    prob = synth.make_support_problem(n_views=20, edges_per_view=200000, n_groups=50000, rows_per_group=20, seed=20251109, delta_theta_deg=2.0)
+    g = api.EdgeSketch(api.default_config(n_views=22), 0)
+    sp = api.SupportProblem(g, prob["group_off"], prob["view_off"], prob["ang31"], prob["ang32"], prob["cs"], prob["sn"],
+                            prob["wedge31"], prob["wedge32"], prob["tgt"], prob["thr"], prob["parallel_deg"])
+    sp.run()
+    got = sp.result()
+    H, E = int(prob["group_off"][-1]), 200000
+    assert got.shape == (20, H) and H > 900000
+    sp.run()
+    assert np.array_equal(sp.result(), got)
+    grp = np.repeat(np.arange(50000), np.diff(prob["group_off"]))
+    for v in (0, 13):
+        gs = 300                                                        # (1) oracle on the first groups of this view
+        hs = int(prob["group_off"][gs])
+        sl = slice(v * E, (v + 1) * E)
+        sub = dict(group_off=prob["group_off"][:gs + 1], view_off=np.array([0, E], np.int64), ang31=prob["ang31"][sl], ang32=prob["ang32"][sl],
+                   cs=prob["cs"][sl], sn=prob["sn"][sl], wedge31=prob["wedge31"][v:v + 1, :gs], wedge32=prob["wedge32"][v:v + 1, :hs],
+                   tgt=prob["tgt"][v:v + 1, :hs], thr=prob["thr"], parallel_deg=prob["parallel_deg"])
+        exp = oracle_mod.support_test(**sub)
+        assert np.array_equal(exp[0], got[v, :hs])
+        a31, a32, cs, sn = prob["ang31"][sl], prob["ang32"][sl], prob["cs"][sl], prob["sn"][sl]   # (2) properties of every row of the view
+        w1, w2, tg, r = prob["wedge31"][v][grp], prob["wedge32"][v], prob["tgt"][v], got[v]
+        hit = r != -2
+        assert 0.05 * H < hit.sum() < 0.95 * H
+        e = r[hit]
+        assert np.all((a31[e] > w1[hit, 0]) & (a31[e] < w1[hit, 1]) & (a32[e] > w2[hit, 0]) & (a32[e] < w2[hit, 1]))
+        d = np.abs(tg[hit, 0] * cs[e] + tg[hit, 1] * sn[e])
+        assert np.all(d >= prob["thr"])
+        # rows without support: brute force over a random subset, no edge of the view qualifies
+        miss = np.nonzero(~hit)[0]
+        for h in np.random.default_rng(v).choice(miss, 200, replace=False):
+            inl = (a31 > w1[h, 0]) & (a31 < w1[h, 1]) & (a32 > w2[h, 0]) & (a32 < w2[h, 1])
+            par = max(abs(w1[h, 0] - w2[h, 0]), abs(w1[h, 0] - w2[h, 1]), abs(w1[h, 1] - w2[h, 0]), abs(w1[h, 1] - w2[h, 1])) <= prob["parallel_deg"]
+            assert par or not np.any(np.abs(tg[h, 0] * cs[inl] + tg[h, 1] * sn[inl]) >= prob["thr"])
+        for h in np.random.default_rng(v + 1).choice(np.nonzero(hit)[0], 200, replace=False):   # supported rows: the returned edge is the first maximum
+            inl = np.nonzero((a31 > w1[h, 0]) & (a31 < w1[h, 1]) & (a32 > w2[h, 0]) & (a32 < w2[h, 1]))[0]
+            dd = np.abs(tg[h, 0] * cs[inl] + tg[h, 1] * sn[inl])
+            assert r[h] == inl[np.argmax(dd)]
+    sp.close(); g.close()
+
+
 def test_abc_against_committed_goldens(abc_scene):
     """CUDA path vs tests/golden/oracle_abc_47_42.npz (no oracle run involved).  Index work must be identical; the only
     tolerated difference is the representative of tied 2-member clusters (see test_abc_nef_first_pass_parity)."""
