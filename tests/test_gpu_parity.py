@@ -297,11 +297,13 @@ def test_abc_against_committed_goldens(abc_scene):
     assert np.max(np.abs(a - b)) <= 1e-6
 
 
-def test_full_size_properties_cfg4(oracle_mod, data_mod):
-    """BASELINE.json config 4 at full size (100 views x 50k edges/view, one pair): the oracle cannot finish this in seconds, so
+@pytest.mark.parametrize("name", ["cfg4", "cfg3"])
+def test_full_size_properties(oracle_mod, data_mod, name):
+    """BASELINE.json configs 4 and 3 at full size (100 views x 50k edges/view; DTU-shaped 49 views x 100k edges/view 1600x1200 with the DTU
+    parameters; one pair each): the oracle cannot finish this in seconds, so
     the size-independent properties are checked instead -- determinism (two runs identical), exact view-1-range sharding,
     vote consistency of every accepted pair, finite unit tangents -- and a bounded view-1 range is compared with the oracle."""
-    w = data_mod.workload("cfg4")
+    w = data_mod.workload(name)
     scene = data_mod.make_synthetic_scene(**w["scene"])
     api = pkg("api")
     cfg = api.default_config(n_views=scene.n_views, img_rows=scene.rows, img_cols=scene.cols, max_support_views=w["max_support_views"])
@@ -338,7 +340,7 @@ def test_full_size_properties_cfg4(oracle_mod, data_mod):
     g.keep_intermediates(True)
     g.run(0, 24)
     rep = compare(o, g, check_intermediates=True)
-    _report("cfg4_0_1_h1_0_24", rep)
+    _report(f"{name}_0_1_h1_0_24", rep)
     g.close()
 
 
